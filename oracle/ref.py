@@ -1,0 +1,150 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes binding of oracle/_ref/libmio_ref_*.so.
+
+That library is the UNMODIFIED reference hot path (miocodec_decode + istft, compiled from
+/root/reference by oracle/build_ref.sh).  Only tests/, __graft_entry__.smoke() and the
+cpu_baseline / --impl reference legs of bench.py may import this module; the product
+(miocodec_b200) never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _cpu_flags() -> set[str]:
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    return set(line.split(":", 1)[1].split())
+    except OSError:
+        pass
+    return set()
+
+
+def lib_path() -> str | None:
+    flags = _cpu_flags()
+    order = []
+    if {"avx512f", "avx512bw", "avx512dq", "avx512vl", "avx512cd"} <= flags:
+        order.append("v4")
+    if {"avx2", "fma", "f16c", "bmi2"} <= flags:
+        order.append("v3")
+    forced = os.environ.get("MIO_REF_VARIANT")
+    if forced:
+        order = [forced]
+    for tag in order:
+        p = os.path.join(_HERE, "_ref", f"libmio_ref_{tag}.so")
+        if os.path.exists(p):
+            return p
+    return None
+
+
+def available() -> bool:
+    return lib_path() is not None
+
+
+class Reference:
+    """One reference miocodec context (4 ggml threads, like the reference always uses)."""
+
+    def __init__(self, gguf_path: str):
+        p = lib_path()
+        if p is None:
+            raise RuntimeError("oracle/_ref not built (run oracle/build_ref.sh where /root/reference exists)")
+        self.lib = L = C.CDLL(p)
+        self.variant = os.path.basename(p)
+        L.mio_ref_load.restype = C.c_void_p
+        L.mio_ref_load.argtypes = [C.c_char_p]
+        L.mio_ref_free.argtypes = [C.c_void_p]
+        for n in ("sample_rate", "n_fft", "hop_length", "samples_per_token"):
+            getattr(L, "mio_ref_" + n).argtypes = [C.c_void_p]
+            getattr(L, "mio_ref_" + n).restype = C.c_int
+        L.mio_ref_decode.restype = C.c_long
+        L.mio_ref_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_long,
+                                     C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        L.mio_ref_istft.restype = C.c_long
+        L.mio_ref_istft.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_long,
+                                    C.POINTER(C.c_double)]
+        L.mio_ref_decode_wave.restype = C.c_long
+        L.mio_ref_decode_wave.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_long,
+                                          C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.mio_ref_load_voice.restype = C.c_int
+        L.mio_ref_load_voice.argtypes = [C.c_char_p, C.c_void_p, C.c_int]
+        self.ctx = L.mio_ref_load(gguf_path.encode())
+        if not self.ctx:
+            raise RuntimeError("reference miocodec_load failed: " + gguf_path)
+        self.n_fft = L.mio_ref_n_fft(self.ctx)
+        self.hop = L.mio_ref_hop_length(self.ctx)
+        self.samples_per_token = L.mio_ref_samples_per_token(self.ctx)
+        self.sample_rate = L.mio_ref_sample_rate(self.ctx)
+        self.last_codec_sec = 0.0
+        self.last_istft_sec = 0.0
+
+    def close(self):
+        if self.ctx:
+            self.lib.mio_ref_free(self.ctx)
+            self.ctx = None
+
+    def decode_spec(self, codes: np.ndarray, emb: np.ndarray) -> np.ndarray:
+        codes = np.ascontiguousarray(codes, dtype=np.int32)
+        emb = np.ascontiguousarray(emb, dtype=np.float32)
+        n_frames_guess = 18 * len(codes)
+        out = np.empty(n_frames_guess * (self.n_fft + 2) + 16, dtype=np.float32)
+        nf = C.c_int(0)
+        sec = C.c_double(0)
+        n = self.lib.mio_ref_decode(self.ctx, codes.ctypes.data, len(codes), emb.ctypes.data,
+                                    out.ctypes.data, out.size, C.byref(nf), C.byref(sec))
+        if n < 0:
+            raise RuntimeError("reference decode failed (%d)" % n)
+        self.last_codec_sec = sec.value
+        return out[:n].reshape(nf.value, -1).copy()
+
+    def istft(self, spec: np.ndarray) -> np.ndarray:
+        spec = np.ascontiguousarray(spec, dtype=np.float32)
+        nf = spec.shape[0]
+        out = np.empty((nf + 4) * self.hop + self.n_fft, dtype=np.float32)
+        sec = C.c_double(0)
+        n = self.lib.mio_ref_istft(spec.ctypes.data, nf, self.n_fft, self.hop, out.ctypes.data, out.size,
+                                   C.byref(sec))
+        if n < 0:
+            raise RuntimeError("reference istft failed")
+        self.last_istft_sec = sec.value
+        return out[:n].copy()
+
+    def decode_wave(self, codes: np.ndarray, emb: np.ndarray) -> np.ndarray:
+        codes = np.ascontiguousarray(codes, dtype=np.int32)
+        emb = np.ascontiguousarray(emb, dtype=np.float32)
+        out = np.empty(len(codes) * self.samples_per_token + 4096, dtype=np.float32)
+        cs, is_ = C.c_double(0), C.c_double(0)
+        n = self.lib.mio_ref_decode_wave(self.ctx, codes.ctypes.data, len(codes), emb.ctypes.data,
+                                         out.ctypes.data, out.size, C.byref(cs), C.byref(is_))
+        if n < 0:
+            raise RuntimeError("reference decode_wave failed")
+        self.last_codec_sec, self.last_istft_sec = cs.value, is_.value
+        return out[:n].copy()
+
+    def load_voice(self, path: str) -> np.ndarray:
+        out = np.empty(4096, dtype=np.float32)
+        n = self.lib.mio_ref_load_voice(path.encode(), out.ctypes.data, out.size)
+        if n < 0:
+            raise RuntimeError("reference load_voice_embedding failed")
+        return out[:n].copy()
+
+
+def ref_istft_only(spec: np.ndarray, n_fft: int = 392, hop: int = 98) -> np.ndarray:
+    """istft() of the reference without a codec context."""
+    p = lib_path()
+    if p is None:
+        raise RuntimeError("oracle/_ref not built")
+    L = C.CDLL(p)
+    L.mio_ref_istft.restype = C.c_long
+    L.mio_ref_istft.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_long, C.POINTER(C.c_double)]
+    spec = np.ascontiguousarray(spec, dtype=np.float32)
+    nf = spec.shape[0]
+    out = np.empty((nf + 4) * hop + n_fft, dtype=np.float32)
+    n = L.mio_ref_istft(spec.ctypes.data, nf, n_fft, hop, out.ctypes.data, out.size, None)
+    if n < 0:
+        return np.empty(0, dtype=np.float32)
+    return out[:n].copy()

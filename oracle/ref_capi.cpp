@@ -1,0 +1,115 @@
+// TEST INFRASTRUCTURE ONLY — not part of the product path.
+//
+// Thin extern "C" wrapper around the UNMODIFIED reference implementation of the
+// hot path: miocodec_decode() (/root/reference/src/miocodec.cpp:519-810) and
+// istft() (/root/reference/src/istft.cpp:68-108).  The reference sources are
+// compiled where they lie under /root/reference by oracle/build_ref.sh; nothing
+// from them is copied into this repository.  The resulting shared object lives
+// in oracle/_ref/ (git-ignored) and is used by tests/, __graft_entry__.smoke()
+// and bench.py's cpu_baseline / --impl reference arm as the checker and the
+// timed CPU baseline.
+#include "miocodec.h"   // reference header, found via -I/root/reference/src
+#include "istft.h"      // reference header
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <unistd.h>
+#include <fcntl.h>
+
+namespace {
+// The reference logs several lines to stderr on every decode
+// (src/miocodec.cpp:551,747,784-785); silence them unless MIO_REF_VERBOSE is set.
+struct stderr_mute {
+    int saved = -1;
+    stderr_mute() {
+        if (getenv("MIO_REF_VERBOSE")) return;
+        fflush(stderr);
+        saved = dup(2);
+        int nul = open("/dev/null", O_WRONLY);
+        if (nul >= 0) { dup2(nul, 2); close(nul); }
+    }
+    ~stderr_mute() {
+        if (saved >= 0) { fflush(stderr); dup2(saved, 2); close(saved); }
+    }
+};
+}  // namespace
+
+extern "C" {
+
+void * mio_ref_load(const char * gguf_path) {
+    stderr_mute m;
+    return (void *) miocodec_load(std::string(gguf_path));
+}
+
+void mio_ref_free(void * ctx) { miocodec_free((miocodec_context *) ctx); }
+
+int mio_ref_sample_rate(void * ctx)       { return miocodec_sample_rate((miocodec_context *) ctx); }
+int mio_ref_n_fft(void * ctx)             { return miocodec_n_fft((miocodec_context *) ctx); }
+int mio_ref_hop_length(void * ctx)        { return miocodec_hop_length((miocodec_context *) ctx); }
+int mio_ref_samples_per_token(void * ctx) { return miocodec_samples_per_token((miocodec_context *) ctx); }
+
+// Returns number of floats written (n_frames * 394) or -1. spec_out may be NULL to query.
+long mio_ref_decode(void * ctx, const int * codes, int n_codes, const float * emb,
+                    float * spec_out, long spec_cap, int * n_frames, double * seconds) {
+    stderr_mute m;
+    int nf = 0;
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<float> spec = miocodec_decode((miocodec_context *) ctx, codes, n_codes, emb, 0, &nf);
+    auto t1 = std::chrono::steady_clock::now();
+    if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+    if (n_frames) *n_frames = nf;
+    if (spec.empty()) return -1;
+    if (spec_out) {
+        if ((long) spec.size() > spec_cap) return -2;
+        memcpy(spec_out, spec.data(), spec.size() * sizeof(float));
+    }
+    return (long) spec.size();
+}
+
+// istft() with the reference's own cache (win_length == n_fft as in
+// src/test-to-speech.cpp:67). Returns samples written or -1.
+long mio_ref_istft(const float * spec, int n_frames, int n_fft, int hop, float * out, long out_cap,
+                   double * seconds) {
+    static istft_cache * cache = nullptr;
+    static int cache_n = 0;
+    if (!cache || cache_n != n_fft) { delete cache; cache = new istft_cache(n_fft, n_fft); cache_n = n_fft; }
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<float> a = istft(spec, n_frames, hop, *cache);
+    auto t1 = std::chrono::steady_clock::now();
+    if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+    if (a.empty()) return -1;
+    if ((long) a.size() > out_cap) return -2;
+    memcpy(out, a.data(), a.size() * sizeof(float));
+    return (long) a.size();
+}
+
+// codes -> waveform, exactly what decode_codes_to_audio times
+// (src/test-to-speech.cpp:264-287), peak normalisation off.
+long mio_ref_decode_wave(void * ctx, const int * codes, int n_codes, const float * emb,
+                         float * out, long out_cap, double * codec_sec, double * istft_sec) {
+    int nf = 0;
+    std::vector<float> spec;
+    {
+        stderr_mute m;
+        auto t0 = std::chrono::steady_clock::now();
+        spec = miocodec_decode((miocodec_context *) ctx, codes, n_codes, emb, 0, &nf);
+        auto t1 = std::chrono::steady_clock::now();
+        if (codec_sec) *codec_sec = std::chrono::duration<double>(t1 - t0).count();
+    }
+    if (spec.empty()) return -1;
+    miocodec_context * c = (miocodec_context *) ctx;
+    return mio_ref_istft(spec.data(), nf, miocodec_n_fft(c), miocodec_hop_length(c), out, out_cap, istft_sec);
+}
+
+int mio_ref_load_voice(const char * path, float * out, int cap) {
+    stderr_mute m;
+    std::vector<float> e = load_voice_embedding(std::string(path));
+    if (e.empty() || (int) e.size() > cap) return -1;
+    memcpy(out, e.data(), e.size() * sizeof(float));
+    return (int) e.size();
+}
+
+}  // extern "C"
