@@ -1,0 +1,139 @@
+/*
+ * miocodec_b200 — C ABI of the B200-native codec back half (codes -> spectrogram -> waveform).
+ *
+ * This is the drop-in boundary for the hot path of espresso3389/MioTTS-llama.cpp.  Every entry
+ * point below cites the reference interface it replaces (paths relative to the reference root).
+ * Plain pointers and sizes only; all buffers are HOST memory unless the name says `_device`.
+ * Every function returns MIO_OK (0) or a negative error code; mio_last_error() gives the text.
+ * There is no CPU fallback: without a CUDA device mio_ctx_create fails with MIO_ERR_CUDA.
+ *
+ * Row/sample conventions (identical to the reference):
+ *   spec  : [n_frames][n_fft/2+1][2] float, spec[t*394 + 2*f + {0:re,1:im}], n_frames = 18*n_codes
+ *   wave  : float mono at sample_rate, exactly hop_length*n_frames = 1764*n_codes samples
+ */
+#ifndef MIOCODEC_B200_H
+#define MIOCODEC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MIO_OK             0
+#define MIO_ERR_ARG       -1   /* bad argument (null pointer, negative size, capacity too small) */
+#define MIO_ERR_IO        -2   /* file missing / unreadable */
+#define MIO_ERR_FORMAT    -3   /* not a GGUF v2/v3 file, missing tensor, unsupported dtype */
+#define MIO_ERR_CUDA      -4   /* no device, CUDA error, kernel fault */
+#define MIO_ERR_RANGE     -5   /* a code index outside [0, vocab) (the reference aborts in ggml) */
+#define MIO_ERR_STATE     -6   /* call sequence error (e.g. fetch before run) */
+
+typedef struct mio_ctx mio_ctx;
+typedef struct mio_stream mio_stream;
+
+/* ---- context: replaces miocodec_load / miocodec_free (src/miocodec.h:10-16, src/miocodec.cpp:426-512)
+ * Parses the GGUF, reads the 22 KV hyper-parameters with the reference's defaults, uploads all weights
+ * to HBM once (pre-split for the tensor-core kernels) and builds the ISTFT tables (istft_cache,
+ * src/istft.cpp:7-32).  `device` is a CUDA ordinal. */
+int  mio_ctx_create(const char * gguf_path, int device, mio_ctx ** out_ctx);
+void mio_ctx_destroy(mio_ctx * ctx);
+
+/* accessors: miocodec_sample_rate / n_fft / hop_length / samples_per_token (src/miocodec.h:34-37) */
+int  mio_ctx_sample_rate(const mio_ctx * ctx);
+int  mio_ctx_n_fft(const mio_ctx * ctx);
+int  mio_ctx_hop_length(const mio_ctx * ctx);
+int  mio_ctx_samples_per_token(const mio_ctx * ctx);
+int  mio_ctx_frames_per_code(const mio_ctx * ctx);   /* 2 * prod(upsampler factors) = 18 */
+int  mio_ctx_vocab(const mio_ctx * ctx);
+int  mio_ctx_device(const mio_ctx * ctx);
+
+/* options: "gemm" = "tc" (tcgen05, default) | "simt" (fp32 CUDA-core validation path, still on the GPU);
+ *          "max_chunk_codes" = integer, workspace rows at code resolution (default 16384).
+ * Must be called before the first decode. */
+int  mio_ctx_set_option(mio_ctx * ctx, const char * key, const char * value);
+/* run all kernels of this context on an existing CUDA stream (cudaStream_t as void*), e.g. torch's */
+int  mio_ctx_set_stream(mio_ctx * ctx, void * cuda_stream);
+
+/* ---- voice embedding: replaces load_voice_embedding (src/miocodec.h:41, src/miocodec.cpp:816-853).
+ * Reads the FIRST tensor of the file, F32 only. Returns the number of floats (128) or <0. */
+int  mio_voice_load(const char * emb_gguf_path, float * out, int cap);
+
+/* ---- debug listing: replaces miocodec_print_tensors (src/miocodec.h:43, src/miocodec.cpp:859-877) */
+int  mio_print_tensors(const char * gguf_path);
+
+/* ---- single utterance: replaces miocodec_decode (src/miocodec.h:26-32, src/miocodec.cpp:519-810).
+ * spec_out may be NULL to query sizes. *out_n_frames = 18*n_codes. */
+int  mio_decode_spec(mio_ctx * ctx, const int32_t * codes, int n_codes, const float * global_emb,
+                     float * spec_out, int64_t spec_cap_floats, int * out_n_frames);
+
+/* ---- replaces istft() (src/istft.h:38-42, src/istft.cpp:68-108) with win_length == n_fft as the
+ * reference always constructs it (src/test-to-speech.cpp:67).  Writes hop*n_frames samples. */
+int  mio_istft(mio_ctx * ctx, const float * spec, int n_frames, float * wave_out, int64_t wave_cap,
+               int64_t * out_n_samples);
+
+/* ---- fused codes -> waveform: replaces decode_codes_to_audio (src/test-to-speech.cpp:248-303).
+ * peak_normalize != 0 applies the reference's 0.95/max|s| gain (src/test-to-speech.cpp:289-300). */
+int  mio_decode_wave(mio_ctx * ctx, const int32_t * codes, int n_codes, const float * global_emb,
+                     int peak_normalize, float * wave_out, int64_t wave_cap, int64_t * out_n_samples);
+
+/* ---- batch of independent utterances (the data-parallel form of the same call).
+ * codes_concat[cu_seqlens[b] .. cu_seqlens[b+1]) are utterance b's codes; voice_table is
+ * [n_voices][128]; voice_ids[b] selects a row.  Utterance b's samples are written at
+ * wave_out + samples_per_token*cu_seqlens[b].  wave_cap >= samples_per_token*cu_seqlens[B]. */
+int  mio_decode_wave_batch(mio_ctx * ctx, const int32_t * codes_concat, const int32_t * cu_seqlens, int n_utts,
+                           const float * voice_table, int n_voices, const int32_t * voice_ids,
+                           int peak_normalize, float * wave_out, int64_t wave_cap);
+
+/* Same work split in three so a caller can time the device part alone (bench.py `value`):
+ *   upload: H2D of codes / layout metadata / voice table into context-owned device buffers
+ *   run   : kernels only, asynchronous on the context stream, result stays in HBM
+ *   fetch : D2H of the waveform (synchronises the stream) */
+int  mio_batch_upload(mio_ctx * ctx, const int32_t * codes_concat, const int32_t * cu_seqlens, int n_utts,
+                      const float * voice_table, int n_voices, const int32_t * voice_ids);
+int  mio_batch_run(mio_ctx * ctx, int peak_normalize);
+int  mio_batch_fetch(mio_ctx * ctx, float * wave_out, int64_t wave_cap);
+int  mio_batch_sync(mio_ctx * ctx);                       /* cudaStreamSynchronize + device error flag check */
+int64_t mio_batch_kernel_launches(const mio_ctx * ctx);   /* kernels launched by the last mio_batch_run */
+/* device pointer of the resident waveform of the last batch (float, samples_per_token*sum(T)) */
+void * mio_batch_wave_device(mio_ctx * ctx);
+
+/* ---- streaming policy on top of the decoder: replaces the LLM-branch of
+ * TestToSpeech::synthesize_stream_profiled (src/test-to-speech.cpp:430-625): commit holdback (32 codes),
+ * min commit step (24), check cadence (every 20 pushed codes), full-prefix re-decode, llround() sample
+ * indexing, 1323-sample linear crossfade and chunked emission (emit_range, :367-417).
+ * Many streams are advanced together: mio_streams_step re-decodes, in ONE batched device pass, every
+ * stream whose cadence fired since the last step. */
+typedef struct mio_stream_config {
+    int check_interval;      /* 20   (src/test-to-speech.cpp:499) */
+    int holdback_codes;      /* 32   (:500) */
+    int min_commit_codes;    /* 24   (:501) */
+    int crossfade_samples;   /* min(sample_rate*3/100, 4096) = 1323 (:364); <0 = derive */
+    int chunk_samples;       /* 4096 (src/test-to-speech.h:94) */
+} mio_stream_config;
+void mio_stream_default_config(const mio_ctx * ctx, mio_stream_config * cfg);
+int  mio_stream_open(mio_ctx * ctx, const float * global_emb, const mio_stream_config * cfg, mio_stream ** out);
+void mio_stream_close(mio_stream * s);
+/* append generated codes (one per LLM token in the reference); cadence is evaluated per code */
+int  mio_stream_push_codes(mio_stream * s, const int32_t * codes, int n);
+/* mark end of generation: the next step flushes everything (maybe_emit(true), :616-618) */
+int  mio_stream_finish(mio_stream * s);
+/* advance all given streams: one batched decode for those with a pending emit */
+int  mio_streams_step(mio_ctx * ctx, mio_stream ** streams, int n_streams);
+/* pop emitted audio (already crossfaded, in emission order). Returns samples copied. *is_last is set when
+ * the stream has finished and its queue is drained. */
+int64_t mio_stream_read(mio_stream * s, float * out, int64_t cap, int * is_last);
+/* counters mirroring StreamProfile (src/test-to-speech.h:28-38): decode_calls, decoded_codes, emitted_samples */
+int  mio_stream_stats(const mio_stream * s, int64_t * decode_calls, int64_t * decoded_codes, int64_t * emitted_samples);
+
+/* ---- introspection for parity tests: copy a named intermediate of the LAST decode to the host.
+ * Returns number of floats written or <0.  Names: see csrc/decode.cu (e.g. "prenet_out", "spec"). */
+int64_t mio_debug_read(mio_ctx * ctx, const char * name, float * out, int64_t cap);
+
+const char * mio_last_error(void);
+const char * mio_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MIOCODEC_B200_H */

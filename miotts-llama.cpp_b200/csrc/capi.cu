@@ -1,0 +1,274 @@
+// extern "C" boundary (include/miocodec_b200.h).  No exceptions cross it; errors are codes + mio_last_error().
+#include "../../include/miocodec_b200.h"
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "engine.h"
+#include "stream.h"
+
+using namespace mio;
+
+struct mio_ctx { engine E; };
+struct mio_stream { stream_state * S = nullptr; };
+
+static thread_local std::string g_err;
+
+static int fail(int code, const std::string & msg) {
+    g_err = msg;
+    return code;
+}
+static int classify(const std::string & e) {
+    if (e.rfind("RANGE:", 0) == 0) return MIO_ERR_RANGE;
+    if (e.find("cannot open") != std::string::npos) return MIO_ERR_IO;
+    if (e.find("GGUF") != std::string::npos || e.find("tensor") != std::string::npos || e.find("unsupported") != std::string::npos)
+        return MIO_ERR_FORMAT;
+    if (e.find("bad argument") != std::string::npos || e.find("capacity") != std::string::npos || e.find("out of range") != std::string::npos ||
+        e.find("exceeds") != std::string::npos || e.find("too many") != std::string::npos)
+        return MIO_ERR_ARG;
+    if (e.find("before") != std::string::npos) return MIO_ERR_STATE;
+    return MIO_ERR_CUDA;
+}
+#define TRY(expr)                                          \
+    do {                                                   \
+        std::string _e = (expr);                           \
+        if (!_e.empty()) return fail(classify(_e), _e);    \
+    } while (0)
+
+extern "C" {
+
+const char * mio_last_error(void) { return g_err.c_str(); }
+const char * mio_version(void) { return "miocodec_b200 0.1 (sm_100a)"; }
+
+int mio_ctx_create(const char * gguf_path, int device, mio_ctx ** out_ctx) {
+    if (!gguf_path || !out_ctx) return fail(MIO_ERR_ARG, "bad argument");
+    *out_ctx = nullptr;
+    {   // file problems are reported before any CUDA call so the error is meaningful on machines without a GPU
+        gguf_file probe;
+        std::string e = probe.open(gguf_path);
+        if (!e.empty()) return fail(classify(e), e);
+    }
+    mio_ctx * c = new (std::nothrow) mio_ctx();
+    if (!c) return fail(MIO_ERR_ARG, "out of host memory");
+    std::string e = c->E.load(gguf_path, device);
+    if (!e.empty()) {
+        delete c;
+        return fail(classify(e), e);
+    }
+    if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "simt")) c->E.use_simt = true;
+    *out_ctx = c;
+    return MIO_OK;
+}
+
+void mio_ctx_destroy(mio_ctx * ctx) { delete ctx; }
+
+int mio_ctx_sample_rate(const mio_ctx * c) { return c ? c->E.hp.sample_rate : 0; }
+int mio_ctx_n_fft(const mio_ctx * c) { return c ? c->E.hp.n_fft : 0; }
+int mio_ctx_hop_length(const mio_ctx * c) { return c ? c->E.hp.hop : 0; }
+int mio_ctx_samples_per_token(const mio_ctx * c) { return c ? c->E.hp.samples_per_token : 0; }
+int mio_ctx_frames_per_code(const mio_ctx * c) { return c ? c->E.hp.frames_per_code : 0; }
+int mio_ctx_vocab(const mio_ctx * c) { return c ? c->E.hp.vocab : 0; }
+int mio_ctx_device(const mio_ctx * c) { return c ? c->E.device : -1; }
+
+int mio_ctx_set_option(mio_ctx * c, const char * key, const char * value) {
+    if (!c || !key || !value) return fail(MIO_ERR_ARG, "bad argument");
+    if (!strcmp(key, "gemm")) {
+        if (!strcmp(value, "tc")) c->E.use_simt = false;
+        else if (!strcmp(value, "simt")) c->E.use_simt = true;
+        else return fail(MIO_ERR_ARG, "bad argument: gemm must be tc or simt");
+        return MIO_OK;
+    }
+    if (!strcmp(key, "max_chunk_codes")) {
+        if (c->E.ws_ready) return fail(MIO_ERR_STATE, "max_chunk_codes must be set before the first decode");
+        const long v = strtol(value, nullptr, 10);
+        if (v < 64 || v > (1 << 20)) return fail(MIO_ERR_ARG, "bad argument: max_chunk_codes out of range");
+        c->E.max_rows1 = (int) v + (int) v / 32 + 64;
+        return MIO_OK;
+    }
+    if (!strcmp(key, "debug_snapshots")) {
+        c->E.debug_snap = strcmp(value, "0") != 0;
+        return MIO_OK;
+    }
+    return fail(MIO_ERR_ARG, std::string("bad argument: unknown option ") + key);
+}
+
+int mio_ctx_set_stream(mio_ctx * c, void * cuda_stream) {
+    if (!c) return fail(MIO_ERR_ARG, "bad argument");
+    cudaSetDevice(c->E.device);
+    if (c->E.stream && c->E.own_stream) {
+        cudaStreamSynchronize(c->E.stream);
+        cudaStreamDestroy(c->E.stream);
+    }
+    c->E.stream = (cudaStream_t) cuda_stream;
+    c->E.own_stream = false;
+    return MIO_OK;
+}
+
+int mio_voice_load(const char * path, float * out, int cap) {
+    if (!path || !out) return fail(MIO_ERR_ARG, "bad argument");
+    gguf_file g;
+    std::string e = g.open(path);
+    if (!e.empty()) return fail(classify(e), e);
+    if (g.tensors.empty()) return fail(MIO_ERR_FORMAT, std::string("no tensors in ") + path);
+    const gguf_tensor & t = g.tensors[0];               // "the first tensor", src/miocodec.cpp:825
+    if (t.dtype != GT_F32) return fail(MIO_ERR_FORMAT, "unsupported voice embedding type (F32 only)");   // :840-847
+    const int64_t n = t.nelements();
+    if (n > cap) return fail(MIO_ERR_ARG, "capacity too small");
+    if (!g.read_raw(t, out, (size_t) n * sizeof(float))) return fail(MIO_ERR_IO, "short read");
+    return (int) n;
+}
+
+int mio_print_tensors(const char * path) {
+    if (!path) return fail(MIO_ERR_ARG, "bad argument");
+    gguf_file g;
+    std::string e = g.open(path);
+    if (!e.empty()) return fail(classify(e), e);
+    printf("Tensors in %s: %lld\n", path, (long long) g.tensors.size());
+    for (const gguf_tensor & t : g.tensors)
+        printf("  %-60s [%5lld, %5lld, %5lld, %5lld] type=%d\n", t.name.c_str(), (long long) t.ne[0], (long long) t.ne[1],
+               (long long) t.ne[2], (long long) t.ne[3], (int) t.dtype);
+    return MIO_OK;
+}
+
+static int upload_one(mio_ctx * c, const int32_t * codes, int n_codes, const float * emb) {
+    if (!c || !codes || !emb || n_codes <= 0) return fail(MIO_ERR_ARG, "bad argument");
+    const int32_t cu[2] = {0, n_codes};
+    const int32_t vid = 0;
+    TRY(c->E.upload(codes, cu, 1, emb, 1, &vid));
+    return MIO_OK;
+}
+
+int mio_decode_spec(mio_ctx * c, const int32_t * codes, int n_codes, const float * emb, float * spec_out, int64_t cap,
+                    int * out_n_frames) {
+    if (!c) return fail(MIO_ERR_ARG, "bad argument");
+    const int nf = n_codes * c->E.hp.frames_per_code;
+    if (out_n_frames) *out_n_frames = nf;
+    if (!spec_out) return MIO_OK;
+    if (cap < (int64_t) nf * 2 * c->E.hp.n_freq) return fail(MIO_ERR_ARG, "capacity too small");
+    int r = upload_one(c, codes, n_codes, emb);
+    if (r != MIO_OK) return r;
+    TRY(c->E.run(false));
+    TRY(c->E.fetch_spec(0, spec_out, cap));
+    return MIO_OK;
+}
+
+int mio_istft(mio_ctx * c, const float * spec, int n_frames, float * wave_out, int64_t cap, int64_t * out_n) {
+    if (!c || !spec || !wave_out || n_frames <= 0) return fail(MIO_ERR_ARG, "bad argument");
+    const int64_t n = (int64_t) n_frames * c->E.hp.hop;
+    if (out_n) *out_n = n;
+    if (cap < n) return fail(MIO_ERR_ARG, "capacity too small");
+    TRY(c->E.run_istft_only(spec, n_frames));
+    TRY(c->E.fetch_wave(wave_out, cap));
+    return MIO_OK;
+}
+
+int mio_decode_wave(mio_ctx * c, const int32_t * codes, int n_codes, const float * emb, int peak_normalize,
+                    float * wave_out, int64_t cap, int64_t * out_n) {
+    if (!c || !wave_out) return fail(MIO_ERR_ARG, "bad argument");
+    if (n_codes == 0) { if (out_n) *out_n = 0; return MIO_OK; }     // decode_codes_to_audio: n_codes <= 0 -> empty, true
+    const int64_t n = (int64_t) n_codes * c->E.hp.samples_per_token;
+    if (out_n) *out_n = n;
+    if (cap < n) return fail(MIO_ERR_ARG, "capacity too small");
+    int r = upload_one(c, codes, n_codes, emb);
+    if (r != MIO_OK) return r;
+    TRY(c->E.run(peak_normalize != 0));
+    TRY(c->E.fetch_wave(wave_out, cap));
+    return MIO_OK;
+}
+
+int mio_batch_upload(mio_ctx * c, const int32_t * codes, const int32_t * cu, int n_utts, const float * vt, int nv,
+                     const int32_t * vids) {
+    if (!c) return fail(MIO_ERR_ARG, "bad argument");
+    TRY(c->E.upload(codes, cu, n_utts, vt, nv, vids));
+    return MIO_OK;
+}
+int mio_batch_run(mio_ctx * c, int peak_normalize) {
+    if (!c) return fail(MIO_ERR_ARG, "bad argument");
+    TRY(c->E.run(peak_normalize != 0));
+    return MIO_OK;
+}
+int mio_batch_sync(mio_ctx * c) {
+    if (!c) return fail(MIO_ERR_ARG, "bad argument");
+    TRY(c->E.sync());
+    return MIO_OK;
+}
+int mio_batch_fetch(mio_ctx * c, float * out, int64_t cap) {
+    if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
+    TRY(c->E.fetch_wave(out, cap));
+    return MIO_OK;
+}
+int64_t mio_batch_kernel_launches(const mio_ctx * c) { return c ? c->E.launches : 0; }
+void * mio_batch_wave_device(mio_ctx * c) { return c ? (void *) c->E.d_wave : nullptr; }
+
+int mio_decode_wave_batch(mio_ctx * c, const int32_t * codes, const int32_t * cu, int n_utts, const float * vt, int nv,
+                          const int32_t * vids, int peak_normalize, float * out, int64_t cap) {
+    int r = mio_batch_upload(c, codes, cu, n_utts, vt, nv, vids);
+    if (r != MIO_OK) return r;
+    r = mio_batch_run(c, peak_normalize);
+    if (r != MIO_OK) return r;
+    return mio_batch_fetch(c, out, cap);
+}
+
+// ---- streaming
+void mio_stream_default_config(const mio_ctx * c, mio_stream_config * cfg) {
+    if (c && cfg) stream_default_config(c->E, cfg);
+}
+int mio_stream_open(mio_ctx * c, const float * emb, const mio_stream_config * cfg, mio_stream ** out) {
+    if (!c || !emb || !out) return fail(MIO_ERR_ARG, "bad argument");
+    *out = nullptr;
+    stream_state * s = nullptr;
+    std::string e = stream_open(c->E, emb, cfg, &s);
+    if (!e.empty()) return fail(classify(e), e);
+    mio_stream * h = new mio_stream();
+    h->S = s;
+    *out = h;
+    return MIO_OK;
+}
+void mio_stream_close(mio_stream * s) {
+    if (!s) return;
+    delete s->S;
+    delete s;
+}
+int mio_stream_push_codes(mio_stream * s, const int32_t * codes, int n) {
+    if (!s || (!codes && n > 0) || n < 0) return fail(MIO_ERR_ARG, "bad argument");
+    TRY(stream_push(*s->S, codes, n));
+    return MIO_OK;
+}
+int mio_stream_finish(mio_stream * s) {
+    if (!s) return fail(MIO_ERR_ARG, "bad argument");
+    TRY(stream_finish(*s->S));
+    return MIO_OK;
+}
+int mio_streams_step(mio_ctx * c, mio_stream ** streams, int n) {
+    if (!c || (!streams && n > 0) || n < 0) return fail(MIO_ERR_ARG, "bad argument");
+    std::vector<stream_state *> v(n);
+    for (int i = 0; i < n; i++) v[i] = streams[i] ? streams[i]->S : nullptr;
+    TRY(streams_step(c->E, v.data(), n));
+    return MIO_OK;
+}
+int64_t mio_stream_read(mio_stream * s, float * out, int64_t cap, int * is_last) {
+    if (!s || (!out && cap > 0)) return fail(MIO_ERR_ARG, "bad argument");
+    return stream_read(*s->S, out, cap, is_last);
+}
+int mio_stream_stats(const mio_stream * s, int64_t * dc, int64_t * codes, int64_t * emitted) {
+    if (!s) return fail(MIO_ERR_ARG, "bad argument");
+    if (dc) *dc = s->S->decode_calls;
+    if (codes) *codes = s->S->decoded_codes;
+    if (emitted) *emitted = s->S->emitted_samples;
+    return MIO_OK;
+}
+
+int64_t mio_debug_read(mio_ctx * c, const char * name, float * out, int64_t cap) {
+    if (!c || !name) return fail(MIO_ERR_ARG, "bad argument");
+    auto it = c->E.snaps.find(name);
+    if (it == c->E.snaps.end()) return fail(MIO_ERR_ARG, std::string("bad argument: no snapshot named ") + name);
+    const int64_t n = (int64_t) it->second.size();
+    if (!out) return n;
+    if (cap < n) return fail(MIO_ERR_ARG, "capacity too small");
+    memcpy(out, it->second.data(), (size_t) n * sizeof(float));
+    return n;
+}
+
+}  // extern "C"

@@ -1,0 +1,908 @@
+#include "engine.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+namespace mio {
+
+#define CK(expr)                                                                                       \
+    do {                                                                                               \
+        cudaError_t _e = (expr);                                                                       \
+        if (_e != cudaSuccess) return std::string(#expr) + ": " + cudaGetErrorString(_e);              \
+    } while (0)
+
+constexpr int GN_SLOTS = 16;
+
+// ---------------------------------------------------------------------------------------------
+// TMA descriptors (driver entry point fetched at run time: the library has no link-time libcuda dependency, so it
+// loads — and its symbol table can be checked — on machines without a driver)
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static encode_tiled_fn g_encode = nullptr;
+
+static std::string get_encode() {
+    if (g_encode) return {};
+    void * fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+    if (!fn || q != cudaDriverEntryPointSuccess) return "cuTensorMapEncodeTiled not available";
+    g_encode = (encode_tiled_fn) fn;
+    return {};
+}
+
+// 2-D fp16 [rows][cols] row-major, box {64, box_rows}, SWIZZLE_128B, OOB -> zeros
+static std::string make_map(CUtensorMap * tm, const __half * base, int rows, int cols, int box_rows) {
+    std::string e = get_encode();
+    if (!e.empty()) return e;
+    cuuint64_t dims[2] = {(cuuint64_t) cols, (cuuint64_t) rows};
+    cuuint64_t strides[1] = {(cuuint64_t) cols * sizeof(__half)};
+    cuuint32_t box[2] = {64u, (cuuint32_t) box_rows};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (void *) base, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return "cuTensorMapEncodeTiled failed (" + std::to_string((int) r) + ")";
+    return {};
+}
+
+// ---------------------------------------------------------------------------------------------
+// small device helpers used at load time
+// ---------------------------------------------------------------------------------------------
+__global__ void split_weights_kernel(const float * __restrict__ w, size_t n, float scale, __half * __restrict__ hi,
+                                     __half * __restrict__ lo) {
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x) {
+        const float x = w[i] * scale;
+        const __half h = __float2half_rn(x);
+        hi[i] = h;
+        if (lo) lo[i] = __float2half_rn(x - __half2float(h));
+    }
+}
+
+template <class T>
+static std::string dev_alloc(T ** p, size_t n) {
+    CK(cudaMalloc((void **) p, std::max<size_t>(n, 1) * sizeof(T)));
+    return {};
+}
+
+static std::string upload_f32(const std::vector<float> & h, float ** d) {
+    std::string e = dev_alloc(d, h.size());
+    if (!e.empty()) return e;
+    CK(cudaMemcpy(*d, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
+    return {};
+}
+
+engine::~engine() {
+    // process-lifetime allocations are released with the context; individual frees omitted for weights created
+    // through cudaMalloc are handled here for the big buffers
+    cudaSetDevice(device);
+    if (stream && own_stream) cudaStreamSynchronize(stream);
+    auto F = [](void * p) { if (p) cudaFree(p); };
+    F(x768); F(qkv); F(x512); F(y512); F(x256); F(y256); F(x128); F(y128); F(spec); F(mod); F(peak);
+    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_stats); F(err_flag);
+    F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_out_off); F(d_voice_table); F(d_wave);
+    for (void * p : w_allocs) F(p);
+    F(d_emit); F(d_emit_jobs);
+    if (h_emit) cudaFreeHost(h_emit);
+    if (h_stage) cudaFreeHost(h_stage);
+    if (stream && own_stream) cudaStreamDestroy(stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// load: GGUF -> HBM.  KV keys and defaults follow miocodec_load (src/miocodec.cpp:447-481).
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct loader {
+    engine & E;
+    gguf_file & g;
+    std::string err;
+    loader(engine & e, gguf_file & gg) : E(e), g(gg) {}
+
+    bool get(const std::string & name, std::vector<float> & out, std::vector<int64_t> * ne = nullptr) {
+        const gguf_tensor * t = g.find(name);
+        if (!t) { err = "missing tensor: " + name; return false; }
+        if (!g.read_f32(*t, out)) { err = "unsupported dtype / short read for tensor " + name; return false; }
+        if (ne) ne->assign(t->ne, t->ne + 4);
+        return true;
+    }
+    bool is_f16(const std::string & name) {
+        const gguf_tensor * t = g.find(name);
+        return t && (t->dtype == GT_F16 || t->dtype == GT_BF16);
+    }
+    float * vec(const std::string & name, size_t expect) {
+        std::vector<float> h;
+        if (!get(name, h)) return nullptr;
+        if (h.size() != expect) { err = "tensor " + name + " has wrong size"; return nullptr; }
+        float * d = nullptr;
+        std::string e = upload_f32(h, &d);
+        if (!e.empty()) { err = e; return nullptr; }
+        E.w_allocs.push_back(d);
+        return d;
+    }
+    float * vec_host(const std::vector<float> & h) {
+        float * d = nullptr;
+        std::string e = upload_f32(h, &d);
+        if (!e.empty()) { err = e; return nullptr; }
+        E.w_allocs.push_back(d);
+        return d;
+    }
+    // B[N][Ktot] fp32 on the host -> split fp16 on the device (+ tensor maps)
+    bool pack(gemm_weight & W, const std::vector<float> & B, int N, int K, int taps, int npass) {
+        W.N = N; W.K = K; W.taps = taps; W.npass = npass;
+        const size_t n = (size_t) N * K * taps;
+        if (B.size() != n) { err = "internal: weight size mismatch"; return false; }
+        float scale = 1.f;
+        if (npass == 3) {   // power-of-two pre-scale keeps the lo parts in fp16's normal range (exact to undo)
+            float mx = 0.f;
+            for (float v : B) mx = std::max(mx, std::fabs(v));
+            if (mx > 0.f && std::isfinite(mx)) {
+                int e = (int) std::floor(std::log2(256.0 / (double) mx));
+                e = std::max(-8, std::min(20, e));
+                scale = std::ldexp(1.0f, e);
+            }
+        }
+        W.out_scale = 1.0f / scale;
+        float * tmp = nullptr;
+        if (cudaMalloc(&tmp, n * sizeof(float)) != cudaSuccess) { err = "cudaMalloc failed (weight staging)"; return false; }
+        cudaMemcpy(tmp, B.data(), n * sizeof(float), cudaMemcpyHostToDevice);
+        if (cudaMalloc(&W.hi, n * sizeof(__half)) != cudaSuccess) { err = "cudaMalloc failed (weights)"; return false; }
+        E.w_allocs.push_back(W.hi);
+        if (npass == 3) {
+            if (cudaMalloc(&W.lo, n * sizeof(__half)) != cudaSuccess) { err = "cudaMalloc failed (weights)"; return false; }
+            E.w_allocs.push_back(W.lo);
+        }
+        split_weights_kernel<<<296, 256>>>(tmp, n, scale, W.hi, W.lo);
+        cudaError_t ce = cudaDeviceSynchronize();
+        cudaFree(tmp);
+        if (ce != cudaSuccess) { err = std::string("split_weights_kernel: ") + cudaGetErrorString(ce); return false; }
+        W.box_n = (N % 256 == 0) ? 256 : 128;
+        std::string e = make_map(&W.tm_hi, W.hi, N, K * taps, W.box_n);
+        if (e.empty() && W.lo) e = make_map(&W.tm_lo, W.lo, N, K * taps, W.box_n);
+        if (e.empty() && !W.lo) W.tm_lo = W.tm_hi;
+        if (!e.empty()) { err = e; return false; }
+        return true;
+    }
+    // Linear weight(s): ggml ne [in, out] == row-major [out][in]; several are stacked along N
+    bool linear(gemm_weight & W, const std::vector<std::string> & names, int K, bool interleave2 = false) {
+        std::vector<std::vector<float>> parts(names.size());
+        int N = 0;
+        bool f16 = true;
+        for (size_t i = 0; i < names.size(); i++) {
+            std::vector<int64_t> ne;
+            if (!get(names[i], parts[i], &ne)) return false;
+            if (ne[0] != K) { err = "tensor " + names[i] + ": unexpected input width"; return false; }
+            N += (int) ne[1];
+            f16 = f16 && is_f16(names[i]);
+        }
+        std::vector<float> B((size_t) N * K);
+        if (interleave2) {   // two equally sized matrices, rows interleaved (gate/up)
+            const int half = N / 2;
+            for (int j = 0; j < half; j++) {
+                memcpy(&B[(size_t) (2 * j) * K], &parts[0][(size_t) j * K], K * sizeof(float));
+                memcpy(&B[(size_t) (2 * j + 1) * K], &parts[1][(size_t) j * K], K * sizeof(float));
+            }
+        } else {
+            size_t off = 0;
+            for (auto & p : parts) { memcpy(&B[off], p.data(), p.size() * sizeof(float)); off += p.size(); }
+        }
+        // F16/BF16-stored matrices: the reference rounds the activations to that type too (ggml-cpu.c:1291-1326);
+        // we keep the split-precision activations (closer to exact) and the stored weight values exactly.
+        (void) f16;
+        return pack(W, B, N, K, 1, 3);
+    }
+    // Conv1d k=3: ggml ne [3, IC, OC] == row-major [OC][IC][3] -> B[oc][tap*IC + ic]; operands rounded to fp16 (npass 1)
+    bool conv3(gemm_weight & W, const std::string & name, int C) {
+        std::vector<float> h; std::vector<int64_t> ne;
+        if (!get(name, h, &ne)) return false;
+        if (ne[0] != 3 || ne[1] != C || ne[2] != C) { err = "tensor " + name + ": expected [3," + std::to_string(C) + "," + std::to_string(C) + "]"; return false; }
+        std::vector<float> B((size_t) C * 3 * C);
+        for (int oc = 0; oc < C; oc++)
+            for (int ic = 0; ic < C; ic++)
+                for (int t = 0; t < 3; t++) B[(size_t) oc * 3 * C + (size_t) t * C + ic] = h[((size_t) oc * C + ic) * 3 + t];
+        return pack(W, B, C, C, 3, 1);
+    }
+    // ConvTranspose1d: ggml ne [k, Cout, Cin] == row-major [Cin][Cout][k]; stride f, trim (k-f)/2 per side.
+    //   y[f*q + r][co] = b[co] + sum_{d=-1..1} sum_ci x[q+d][ci] * W[ci][co][r + trim - f*d]      (k == 3f)
+    //   y[f*q + r][co] = b[co] + sum_ci x[q][ci] * W[ci][co][r]                                   (k == f)
+    bool convT(gemm_weight & W, const std::string & name, int Cin, int Cout, int k, int f) {
+        std::vector<float> h; std::vector<int64_t> ne;
+        if (!get(name, h, &ne)) return false;
+        if (ne[0] != k || ne[1] != Cout || ne[2] != Cin) { err = "tensor " + name + ": unexpected ConvTranspose shape"; return false; }
+        int taps;
+        if (k == f) taps = 1;
+        else if (k == 3 * f) taps = 3;
+        else { err = "ConvTranspose1d with kernel " + std::to_string(k) + " / stride " + std::to_string(f) + " is not supported (need k == f or k == 3f)"; return false; }
+        const int trim = (k - f) / 2;
+        const int N = f * Cout;
+        std::vector<float> B((size_t) N * taps * Cin, 0.f);
+        for (int r = 0; r < f; r++)
+            for (int co = 0; co < Cout; co++)
+                for (int t = 0; t < taps; t++) {
+                    const int d = (taps == 3) ? t - 1 : 0;
+                    const int kk = r + trim - f * d;
+                    if (kk < 0 || kk >= k) continue;
+                    float * dst = &B[((size_t) (r * Cout + co) * taps + t) * Cin];
+                    for (int ci = 0; ci < Cin; ci++) dst[ci] = h[((size_t) ci * Cout + co) * k + kk];
+                }
+        const bool f16 = is_f16(name);
+        (void) f16;
+        return pack(W, B, N, Cin, taps, 3);
+    }
+    bool resblock(resblock_w & R, const std::string & p, int C) {
+        R.C = C;
+        R.n1w = vec(p + "norm1.weight", C); R.n1b = vec(p + "norm1.bias", C);
+        R.n2w = vec(p + "norm2.weight", C); R.n2b = vec(p + "norm2.bias", C);
+        R.c1b = vec(p + "conv1.bias", C);   R.c2b = vec(p + "conv2.bias", C);
+        if (!R.n1w || !R.n1b || !R.n2w || !R.n2b || !R.c1b || !R.c2b) return false;
+        return conv3(R.c1, p + "conv1.weight", C) && conv3(R.c2, p + "conv2.weight", C);
+    }
+};
+}  // namespace
+
+std::string engine::load(const std::string & path, int dev) {
+    device = dev;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) return "no CUDA device available (this library has no CPU fallback)";
+    if (dev < 0 || dev >= n_dev) return "invalid CUDA device ordinal";
+    CK(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major != 10) return std::string("device '") + prop.name + "' is not sm_100 (B200); this build contains sm_100a code only";
+
+    gguf_file g;
+    std::string e = g.open(path);
+    if (!e.empty()) return e;
+    // hyper-parameters (src/miocodec.cpp:447-474)
+    hp.sample_rate = g.u32_or("miocodec.sample_rate", 44100);
+    hp.n_fft = g.u32_or("miocodec.n_fft", 392);
+    hp.hop = g.u32_or("miocodec.hop_length", 98);
+    hp.n_freq = hp.n_fft / 2 + 1;
+    hp.samples_per_token = g.u32_or("miocodec.samples_per_token", 1764);
+    hp.head_out = g.u32_or("embedding_length_out", 394);
+    hp.prenet_layers = g.u32_or("miocodec.prenet_layers", 6);
+    hp.prenet_dim = g.u32_or("miocodec.prenet_dim", 768);
+    hp.prenet_heads = g.u32_or("miocodec.prenet_heads", 12);
+    hp.prenet_ff = g.u32_or("miocodec.prenet_ff", 2048);
+    hp.prenet_window = g.u32_or("miocodec.prenet_window", 65);
+    hp.dec_layers = g.u32_or("miocodec.decoder_layers", 8);
+    hp.dec_dim = g.u32_or("miocodec.decoder_dim", 512);
+    hp.dec_heads = g.u32_or("miocodec.decoder_heads", 8);
+    hp.dec_ff = g.u32_or("miocodec.decoder_ff", 1536);
+    hp.dec_window = g.u32_or("miocodec.decoder_window", 65);
+    hp.adaln_dim = g.u32_or("miocodec.decoder_adanorm_dim", 128);
+    hp.resnet_blocks = g.u32_or("miocodec.resnet_blocks", 2);
+    hp.resnet_groups = g.u32_or("miocodec.resnet_groups", 32);
+    hp.up_stages = g.u32_or("miocodec.wave_upsampler_layers", 2);
+    hp.rope_theta = g.f32_or("miocodec.rope_theta", 10000.0f);
+    hp.norm_eps = g.f32_or("miocodec.norm_eps", 1e-5f);
+    hp.gn_eps = g.f32_or("miocodec.group_norm_eps", 1e-6f);
+
+    // shapes this build has kernels for (the reference's fixed architecture)
+    if (hp.n_fft != 392 || hp.hop != 98 || hp.head_out != 394) return "unsupported STFT geometry (kernels are built for n_fft=392, hop=98)";
+    if (hp.prenet_dim != 768 || hp.dec_dim != 512 || hp.prenet_dim / hp.prenet_heads != 64 || hp.dec_dim / hp.dec_heads != 64)
+        return "unsupported transformer widths (kernels are built for 768/512 channels, head_dim 64)";
+    if (hp.prenet_window != 65 || hp.dec_window != 65) return "unsupported attention window (kernels are built for 65)";
+    if (hp.resnet_groups != 32 || hp.up_stages != 2) return "unsupported resnet groups / upsampler depth";
+    if (hp.prenet_ff % 64 || hp.dec_ff % 64 || hp.adaln_dim % 4) return "unsupported feed-forward / conditioning widths";
+
+    loader L(*this, g);
+    // upsampler geometry from the I32 tensors (src/miocodec.cpp:476-481)
+    {
+        const gguf_tensor * tf = g.find("miocodec.wave_upsampler.factors");
+        const gguf_tensor * tk = g.find("miocodec.wave_upsampler.kernel_sizes");
+        if (!tf || !tk || tf->dtype != GT_I32 || tk->dtype != GT_I32 || tf->nelements() < hp.up_stages || tk->nelements() < hp.up_stages)
+            return "missing/invalid miocodec.wave_upsampler.factors / kernel_sizes";
+        int32_t f[4] = {0}, k[4] = {0};
+        if (!g.read_raw(*tf, f, sizeof(int32_t) * hp.up_stages) || !g.read_raw(*tk, k, sizeof(int32_t) * hp.up_stages)) return "short read (upsampler geometry)";
+        int total = 2;
+        for (int s = 0; s < hp.up_stages; s++) { hp.up_factor[s] = f[s]; hp.up_kernel[s] = k[s]; total *= f[s]; }
+        hp.frames_per_code = total;
+        if (hp.up_factor[0] != 3 || hp.up_factor[1] != 3) return "unsupported upsampler factors (row-space resolutions are built for 2 x 3 x 3)";
+        if (hp.frames_per_code * hp.hop != hp.samples_per_token) return "inconsistent samples_per_token";
+    }
+    {
+        const gguf_tensor * te = g.find("token_embd");
+        if (!te) return "missing tensor: token_embd";
+        if (te->ne[0] != hp.prenet_dim) return "token_embd has the wrong width";
+        hp.vocab = (int) te->ne[1];
+        w.token_embd = L.vec("token_embd", (size_t) hp.vocab * hp.prenet_dim);
+        if (!w.token_embd) return L.err;
+    }
+    const int D = hp.prenet_dim, C = hp.dec_dim;
+    w.prenet.resize(hp.prenet_layers);
+    for (int i = 0; i < hp.prenet_layers; i++) {
+        const std::string p = "wave_prenet.blk." + std::to_string(i) + ".";
+        prenet_layer_w & l = w.prenet[i];
+        l.an_w = L.vec(p + "attn_norm.weight", D); l.an_b = L.vec(p + "attn_norm.bias", D);
+        l.fn_w = L.vec(p + "ffn_norm.weight", D);  l.fn_b = L.vec(p + "ffn_norm.bias", D);
+        if (!l.an_w || !l.an_b || !l.fn_w || !l.fn_b) return L.err;
+        if (!L.linear(l.qkv, {p + "attn_q.weight", p + "attn_k.weight", p + "attn_v.weight"}, D)) return L.err;
+        if (!L.linear(l.wo, {p + "attn_output.weight"}, D)) return L.err;
+        if (!L.linear(l.gu, {p + "ffn_gate.weight", p + "ffn_up.weight"}, D, true)) return L.err;
+        if (!L.linear(l.down, {p + "ffn_down.weight"}, hp.prenet_ff)) return L.err;
+    }
+    w.pre_norm_w = L.vec("wave_prenet.norm.weight", D); w.pre_norm_b = L.vec("wave_prenet.norm.bias", D);
+    w.pre_out_b = L.vec("wave_prenet.output.bias", C);
+    if (!w.pre_norm_w || !w.pre_norm_b || !w.pre_out_b) return L.err;
+    if (!L.linear(w.pre_out, {"wave_prenet.output.weight"}, D)) return L.err;
+    if (!L.convT(w.up0, "wave_upsample.weight", C, C, 2, 2)) return L.err;
+    w.up0_b = L.vec("wave_upsample.bias", C);
+    if (!w.up0_b) return L.err;
+    w.prior.resize(hp.resnet_blocks); w.post.resize(hp.resnet_blocks);
+    for (int b = 0; b < hp.resnet_blocks; b++) {
+        if (!L.resblock(w.prior[b], "wave_prior." + std::to_string(b) + ".", C)) return L.err;
+        if (!L.resblock(w.post[b], "wave_post." + std::to_string(b) + ".", C)) return L.err;
+    }
+    // decoder + stacked conditioning
+    w.dec.resize(hp.dec_layers);
+    w.cond_rows = hp.dec_layers * 2 * 3 * C + 2 * C;
+    std::vector<float> cw((size_t) w.cond_rows * hp.adaln_dim), cb(w.cond_rows);
+    for (int i = 0; i < hp.dec_layers; i++) {
+        const std::string p = "wave_decoder.blk." + std::to_string(i) + ".";
+        dec_layer_w & l = w.dec[i];
+        if (!L.linear(l.qkv, {p + "attn_q.weight", p + "attn_k.weight", p + "attn_v.weight"}, C)) return L.err;
+        if (!L.linear(l.wo, {p + "attn_output.weight"}, C)) return L.err;
+        if (!L.linear(l.gu, {p + "ffn_gate.weight", p + "ffn_up.weight"}, C, true)) return L.err;
+        if (!L.linear(l.down, {p + "ffn_down.weight"}, hp.dec_ff)) return L.err;
+        const char * nm[2] = {"attn_cond", "ffn_cond"};
+        for (int j = 0; j < 2; j++) {
+            std::vector<float> hw, hb;
+            if (!L.get(p + nm[j] + ".weight", hw) || !L.get(p + nm[j] + ".bias", hb)) return L.err;
+            if (hw.size() != (size_t) 3 * C * hp.adaln_dim || hb.size() != (size_t) 3 * C) return "bad cond tensor size in " + p;
+            const size_t row0 = (size_t) (i * 2 + j) * 3 * C;
+            memcpy(&cw[row0 * hp.adaln_dim], hw.data(), hw.size() * sizeof(float));
+            memcpy(&cb[row0], hb.data(), hb.size() * sizeof(float));
+        }
+    }
+    {
+        std::vector<float> hw, hb;
+        if (!L.get("wave_decoder.norm_cond.weight", hw) || !L.get("wave_decoder.norm_cond.bias", hb)) return L.err;
+        if (hw.size() != (size_t) 2 * C * hp.adaln_dim || hb.size() != (size_t) 2 * C) return "bad norm_cond tensor size";
+        const size_t row0 = (size_t) hp.dec_layers * 2 * 3 * C;
+        memcpy(&cw[row0 * hp.adaln_dim], hw.data(), hw.size() * sizeof(float));
+        memcpy(&cb[row0], hb.data(), hb.size() * sizeof(float));
+    }
+    w.cond_w = L.vec_host(cw); w.cond_b = L.vec_host(cb);
+    if (!w.cond_w || !w.cond_b) return L.err;
+
+    // upsampler stages
+    w.upT.resize(hp.up_stages); w.upT_b.resize(hp.up_stages); w.snake_ea.resize(hp.up_stages); w.snake_eb.resize(hp.up_stages);
+    w.up_res.resize(hp.up_stages);
+    int cin = C;
+    for (int s = 0; s < hp.up_stages; s++) {
+        const std::string un = "wave_upsampler.up." + std::to_string(s);
+        const gguf_tensor * t = g.find(un + ".weight");
+        if (!t) return "missing tensor: " + un + ".weight";
+        const int cout = (int) t->ne[1];
+        hp.up_ch[s] = cout;
+        if (cout != (s == 0 ? 256 : 128)) return "unsupported upsampler widths (kernels are built for 512 -> 256 -> 128)";
+        if (!L.convT(w.upT[s], un + ".weight", cin, cout, hp.up_kernel[s], hp.up_factor[s])) return L.err;
+        w.upT_b[s] = L.vec(un + ".bias", cout);
+        std::vector<float> a, b;
+        if (!w.upT_b[s] || !L.get("wave_upsampler.snake." + std::to_string(s) + ".alpha", a) ||
+            !L.get("wave_upsampler.snake." + std::to_string(s) + ".beta", b)) return L.err;
+        if ((int) a.size() != cout || (int) b.size() != cout) return "bad snake parameter size";
+        for (auto & v : a) v = expf(v);
+        for (auto & v : b) v = expf(v);
+        w.snake_ea[s] = L.vec_host(a); w.snake_eb[s] = L.vec_host(b);
+        if (!L.resblock(w.up_res[s], "wave_upsampler.resblk." + std::to_string(s) + ".", cout)) return L.err;
+        cin = cout;
+    }
+    {
+        const gguf_tensor * t = g.find("wave_upsampler.out_proj.weight");
+        if (!t) return "missing tensor: wave_upsampler.out_proj.weight";
+        hp.out_proj_dim = (int) t->ne[1];
+        if (hp.out_proj_dim != 512) return "unsupported out_proj width (kernels are built for 512)";
+        if (!L.linear(w.out_proj, {"wave_upsampler.out_proj.weight"}, cin)) return L.err;
+        w.out_proj_b = L.vec("wave_upsampler.out_proj.bias", hp.out_proj_dim);
+        std::vector<float> a, b;
+        if (!w.out_proj_b || !L.get("wave_upsampler.out_snake.alpha", a) || !L.get("wave_upsampler.out_snake.beta", b)) return L.err;
+        for (auto & v : a) v = expf(v);
+        for (auto & v : b) v = expf(v);
+        w.out_snake_ea = L.vec_host(a); w.out_snake_eb = L.vec_host(b);
+    }
+    {   // head: interleave (log-mag f, phase f) so the epilogue sees pairs; output column 2f/2f+1 = re/im of bin f
+        std::vector<float> hw, hb;
+        if (!L.get("istft_head.out.weight", hw) || !L.get("istft_head.out.bias", hb)) return L.err;
+        const int P = hp.out_proj_dim, NF = hp.n_freq;
+        if (hw.size() != (size_t) 2 * NF * P || hb.size() != (size_t) 2 * NF) return "bad istft_head tensor size";
+        std::vector<float> B((size_t) 2 * NF * P), bb(2 * NF);
+        for (int f = 0; f < NF; f++) {
+            memcpy(&B[(size_t) (2 * f) * P], &hw[(size_t) f * P], P * sizeof(float));
+            memcpy(&B[(size_t) (2 * f + 1) * P], &hw[(size_t) (NF + f) * P], P * sizeof(float));
+            bb[2 * f] = hb[f]; bb[2 * f + 1] = hb[NF + f];
+        }
+        if (!L.pack(w.head, B, 2 * NF, P, 1, 3)) return L.err;
+        w.head_b = L.vec_host(bb);
+    }
+    // RoPE table: theta_i = pos * s^i built by repeated multiplication in f32, cosf/sinf of libm — exactly the
+    // reference's cache (ggml_rope_cache_init, ggml-cpu/ops.cpp:5612-5626; theta_scale = powf(base, -2/n_dims))
+    {
+        w.rope_max_pos = 8192;
+        std::vector<float> r((size_t) w.rope_max_pos * 64);
+        const float theta_scale = powf(hp.rope_theta, -2.0f / 64.0f);
+        for (int pos = 0; pos < w.rope_max_pos; pos++) {
+            float theta = (float) pos;
+            for (int i = 0; i < 32; i++) {
+                r[((size_t) pos * 32 + i) * 2] = cosf(theta);
+                r[((size_t) pos * 32 + i) * 2 + 1] = sinf(theta);
+                theta *= theta_scale;
+            }
+        }
+        w.rope_pre = L.vec_host(r);
+    }
+    {   // periodic Hann window (istft_cache, src/istft.cpp:29-31)
+        std::vector<float> hn(hp.n_fft);
+        for (int i = 0; i < hp.n_fft; i++) hn[i] = 0.5f * (1.0f - cosf(2.0f * (float) M_PI * i / hp.n_fft));
+        w.hann = L.vec_host(hn);
+    }
+    if (!L.err.empty()) return L.err;
+    CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    own_stream = true;
+    CK(attention_init());
+    CK(cudaDeviceSynchronize());
+    return {};
+}
+
+// ---------------------------------------------------------------------------------------------
+// workspace
+// ---------------------------------------------------------------------------------------------
+static std::string make_view(a_view & v, __half * hi, __half * lo, int rows, int K) {
+    v.hi = hi; v.lo = lo; v.rows = rows; v.K = K;
+    std::string e = make_map(&v.tm_hi, hi, rows, K, 128);
+    if (e.empty() && lo) e = make_map(&v.tm_lo, lo, rows, K, 128);
+    if (e.empty() && !lo) v.tm_lo = v.tm_hi;
+    return e;
+}
+
+std::string engine::ensure_workspace() {
+    if (ws_ready) return {};
+    CK(cudaSetDevice(device));
+    const size_t R1 = (size_t) max_rows1, R2 = 2 * R1, R6 = 6 * R1, R18 = 18 * R1;
+    std::string e;
+#define A(ptr, n) if (!(e = dev_alloc(&ptr, (size_t) (n))).empty()) return e;
+    A(x768, R1 * 768); A(qkv, std::max(R1 * 2304, R2 * 1536));
+    A(x512, R2 * 512); A(y512, R2 * 512); A(x256, R6 * 256); A(y256, R6 * 256); A(x128, R18 * 128); A(y128, R18 * 128);
+    A(spec, R18 * 394);
+    A(aA_hi, R1 * 1024); A(aA_lo, R1 * 1024); A(aFF_hi, R1 * 3072); A(aFF_lo, R1 * 3072);
+    A(c16, R1 * 2304); A(h512_hi, R18 * 512); A(h512_lo, R18 * 512);
+    A(gn_stats, (size_t) GN_SLOTS * max_utts * 64);
+    A(mod, (size_t) max_voices * w.cond_rows);
+    A(peak, (size_t) max_utts);
+    A(err_flag, 1);
+#undef A
+    CK(cudaMemset(err_flag, 0, sizeof(int)));
+    // stale rows beyond the current batch are only ever multiplied into masked outputs, but start finite
+    CK(cudaMemset(aA_hi, 0, R1 * 1024 * 2)); CK(cudaMemset(aA_lo, 0, R1 * 1024 * 2));
+    CK(cudaMemset(aFF_hi, 0, R1 * 3072 * 2)); CK(cudaMemset(aFF_lo, 0, R1 * 3072 * 2));
+    CK(cudaMemset(c16, 0, R1 * 2304 * 2));
+    CK(cudaMemset(h512_hi, 0, R18 * 512 * 2)); CK(cudaMemset(h512_lo, 0, R18 * 512 * 2));
+    if (!(e = make_view(vA768, aA_hi, aA_lo, (int) R1, 768)).empty()) return e;
+    if (!(e = make_view(vA512, aA_hi, aA_lo, (int) R2, 512)).empty()) return e;
+    if (!(e = make_view(vFF2048, aFF_hi, aFF_lo, (int) R1, 2048)).empty()) return e;
+    if (!(e = make_view(vFF1536, aFF_hi, aFF_lo, (int) R2, 1536)).empty()) return e;
+    if (!(e = make_view(vFF256, aFF_hi, aFF_lo, (int) R6, 256)).empty()) return e;
+    if (!(e = make_view(vFF128, aFF_hi, aFF_lo, (int) R18, 128)).empty()) return e;
+    if (!(e = make_view(vC512, c16, nullptr, (int) R2, 512)).empty()) return e;
+    if (!(e = make_view(vC256, c16, nullptr, (int) R6, 256)).empty()) return e;
+    if (!(e = make_view(vC128, c16, nullptr, (int) R18, 128)).empty()) return e;
+    if (!(e = make_view(vH512, h512_hi, h512_lo, (int) R18, 512)).empty()) return e;
+    ws_ready = true;
+    return {};
+}
+
+row_map engine::rmap() const {
+    row_map r;
+    r.row_utt = d_row_utt + cur_row0; r.start = d_start + cur_utt0; r.len = d_len + cur_utt0; r.voice = d_voice + cur_utt0;
+    r.rows1 = cur_rows1; r.n_utts = cur_n_utts;
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// batch upload: builds the padded row space, split into chunks of whole utterances that fit the workspace
+// ---------------------------------------------------------------------------------------------
+std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts, const float * voice_table, int nv,
+                           const int32_t * voice_ids) {
+    batch_uploaded = false; batch_ran = false;
+    if (n_utts < 0 || (n_utts > 0 && (!codes || !cu || !voice_table || !voice_ids)) || nv <= 0) return "bad argument";
+    if (nv > max_voices) return "too many voices (max " + std::to_string(max_voices) + ")";
+    std::string e = ensure_workspace();
+    if (!e.empty()) return e;
+    CK(cudaSetDevice(device));
+    lay = batch_layout();
+    lay.n_utts = n_utts;
+    chunks.clear();
+    const int fpc = hp.frames_per_code;
+    int64_t rows_total = 0;
+    std::vector<int32_t> chunk_cu_all;   // per chunk: local prefix of istft chunk counts (n+1 entries each)
+    int u = 0;
+    while (u < n_utts) {
+        chunk_info c;
+        c.utt0 = u; c.row0 = (int) rows_total; c.cu0 = (int) chunk_cu_all.size();
+        int rows = 0, blocks = 0;
+        chunk_cu_all.push_back(0);
+        while (u < n_utts) {
+            const int T = cu[u + 1] - cu[u];
+            if (T < 0) return "cu_seqlens must be non-decreasing";
+            if (T + 1 > max_rows1) return "utterance of " + std::to_string(T) + " codes exceeds max_chunk_codes";
+            if (voice_ids[u] < 0 || voice_ids[u] >= nv) return "voice id out of range";
+            if (rows + T + 1 > max_rows1 || (u - c.utt0) >= max_utts) break;
+            lay.start.push_back(rows); lay.len.push_back(T); lay.voice.push_back(voice_ids[u]);
+            lay.out_off.push_back((int64_t) cu[u] * hp.samples_per_token);
+            for (int i = 0; i < T; i++) { lay.codes_padded.push_back(codes[cu[u] + i]); lay.row_utt.push_back(u - c.utt0); }
+            lay.codes_padded.push_back(-1); lay.row_utt.push_back(-1);
+            rows += T + 1;
+            blocks += (T * fpc + ISTFT_SEG_PER_BLOCK - 1) / ISTFT_SEG_PER_BLOCK;
+            chunk_cu_all.push_back(blocks);
+            u++;
+        }
+        c.n_utts = u - c.utt0; c.rows1 = rows; c.istft_blocks = blocks;
+        rows_total += rows;
+        chunks.push_back(c);
+    }
+    lay.rows1 = (int) rows_total;
+    lay.total_codes = n_utts ? cu[n_utts] : 0;
+    wave_samples = lay.total_codes * hp.samples_per_token;
+
+    // device arrays (grown on demand)
+    auto grow = [&](auto ** p, size_t & cap, size_t need) -> std::string {
+        if (need <= cap && *p) return {};
+        if (*p) cudaFree(*p);
+        *p = nullptr;
+        cap = need + need / 4 + 64;
+        return dev_alloc(p, cap);
+    };
+    if (!(e = grow(&d_codes, cap_rows, (size_t) rows_total)).empty()) return e;
+    if (!(e = grow(&d_row_utt, cap_rows_ru, (size_t) rows_total)).empty()) return e;
+    if ((size_t) n_utts + 1 > cap_utts) {
+        for (void * p : {(void *) d_start, (void *) d_len, (void *) d_voice, (void *) d_out_off}) if (p) cudaFree(p);
+        cap_utts = (size_t) n_utts + n_utts / 4 + 64;
+        if (!(e = dev_alloc(&d_start, cap_utts)).empty() || !(e = dev_alloc(&d_len, cap_utts)).empty() ||
+            !(e = dev_alloc(&d_voice, cap_utts)).empty() || !(e = dev_alloc(&d_out_off, cap_utts)).empty()) return e;
+    }
+    if (!(e = grow(&d_chunk_cu, cap_ccu, chunk_cu_all.size())).empty()) return e;
+    if (!(e = grow(&d_voice_table, cap_vt, (size_t) nv * hp.adaln_dim)).empty()) return e;
+    if ((int64_t) wave_cap < wave_samples) {
+        if (d_wave) cudaFree(d_wave);
+        d_wave = nullptr;
+        wave_cap = wave_samples + 64;
+        if (!(e = dev_alloc(&d_wave, (size_t) wave_cap)).empty()) return e;
+    }
+    // one pinned staging buffer, async copies on the context stream
+    const size_t b_codes = (size_t) rows_total * 4, b_utts = (size_t) n_utts * 4, b_off = (size_t) n_utts * 8,
+                 b_ccu = chunk_cu_all.size() * 4, b_vt = (size_t) nv * hp.adaln_dim * 4;
+    const size_t need = 2 * b_codes + 3 * b_utts + b_off + b_ccu + b_vt + 256;
+    if (need > h_stage_bytes) {
+        if (h_stage) cudaFreeHost(h_stage);
+        h_stage = nullptr;
+        h_stage_bytes = need + need / 4;
+        CK(cudaMallocHost(&h_stage, h_stage_bytes));
+    }
+    CK(cudaStreamSynchronize(stream));   // previous async copies out of the staging buffer are done
+    uint8_t * hs = (uint8_t *) h_stage;
+    size_t off = 0;
+    auto put = [&](void * dst, const void * src, size_t bytes) -> cudaError_t {
+        if (bytes == 0) return cudaSuccess;
+        memcpy(hs + off, src, bytes);
+        cudaError_t ce = cudaMemcpyAsync(dst, hs + off, bytes, cudaMemcpyHostToDevice, stream);
+        off += (bytes + 15) / 16 * 16;
+        return ce;
+    };
+    CK(put(d_codes, lay.codes_padded.data(), b_codes));
+    CK(put(d_row_utt, lay.row_utt.data(), b_codes));
+    CK(put(d_start, lay.start.data(), b_utts));
+    CK(put(d_len, lay.len.data(), b_utts));
+    CK(put(d_voice, lay.voice.data(), b_utts));
+    CK(put(d_out_off, lay.out_off.data(), b_off));
+    CK(put(d_chunk_cu, chunk_cu_all.data(), b_ccu));
+    CK(put(d_voice_table, voice_table, b_vt));
+    n_voices = nv;
+    h2d_bytes = 2 * b_codes + 3 * b_utts + b_off + b_ccu + b_vt;
+    batch_uploaded = true;
+    return {};
+}
+
+// ---------------------------------------------------------------------------------------------
+// debug snapshots
+// ---------------------------------------------------------------------------------------------
+void engine::snap_f32(const char * name, const float * d, size_t n) {
+    if (!debug_snap) return;
+    cudaStreamSynchronize(stream);
+    std::vector<float> & v = snaps[name];
+    v.resize(n);
+    cudaMemcpy(v.data(), d, n * sizeof(float), cudaMemcpyDeviceToHost);
+}
+void engine::snap_f16(const char * name, const __half * hi, const __half * lo, size_t n) {
+    if (!debug_snap) return;
+    cudaStreamSynchronize(stream);
+    std::vector<uint16_t> a(n), b(n);
+    cudaMemcpy(a.data(), hi, n * 2, cudaMemcpyDeviceToHost);
+    if (lo) cudaMemcpy(b.data(), lo, n * 2, cudaMemcpyDeviceToHost);
+    std::vector<float> & v = snaps[name];
+    v.resize(n);
+    for (size_t i = 0; i < n; i++) v[i] = fp16_bits_to_float(a[i]) + (lo ? fp16_bits_to_float(b[i]) : 0.f);
+}
+
+// ---------------------------------------------------------------------------------------------
+// GEMM dispatch
+// ---------------------------------------------------------------------------------------------
+cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_params p) {
+    p.M = M; p.N = W.N; p.K = W.K; p.taps = W.taps; p.npass = W.npass; p.out_scale = W.out_scale;
+    if (p.bias_mod <= 1) p.bias_mod = W.N;
+    p.a_hi = A.hi; p.a_lo = A.lo; p.lda = A.K; p.a_rows = A.rows;
+    p.b_hi = W.hi; p.b_lo = W.lo;
+    if (A.K != W.K) return cudaErrorInvalidValue;
+    launches++;
+    if (use_simt) return launch_gemm_simt(p, stream);
+    return launch_gemm_tc(p, A.tm_hi, A.tm_lo, W.tm_hi, W.tm_lo, W.box_n, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// the decoder forward of one chunk + ISTFT (stage numbers follow src/miocodec.cpp:598-740)
+// ---------------------------------------------------------------------------------------------
+#define CKR(expr)                                                                                      \
+    do {                                                                                               \
+        cudaError_t _e = (expr);                                                                       \
+        launches++;                                                                                    \
+        if (_e != cudaSuccess) return std::string(#expr) + ": " + cudaGetErrorString(_e);              \
+    } while (0)
+#define CKG(expr)                                                                                      \
+    do {                                                                                               \
+        cudaError_t _e = (expr);                                                                       \
+        if (_e != cudaSuccess) return std::string(#expr) + ": " + cudaGetErrorString(_e);              \
+    } while (0)
+
+std::string engine::run_resblock(const resblock_w & R, float * x, float * y, const a_view & vc, int rows, int row_div,
+                                 int & gn_slot) {
+    const row_map rm = rmap();
+    const int C = R.C;
+    double * st1 = gn_stats + (size_t) (gn_slot++) * max_utts * 64;
+    double * st2 = gn_stats + (size_t) (gn_slot++) * max_utts * 64;
+    if (gn_slot > GN_SLOTS) return "internal: GroupNorm slot overflow";
+    gemm_params p;
+    // GN -> SiLU -> conv1 + bias
+    CKR(launch_gn_stats(x, rows, C, rm, row_div, st1, stream));
+    CKR(launch_gn_apply_silu(x, rows, C, rm, row_div, st1, hp.gn_eps, R.n1w, R.n1b, vc.hi, stream));
+    p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = y; p.ld_out = C; p.bias = R.c1b;
+    CKG(gemm(R.c1, vc, rows, p));
+    // GN -> SiLU -> conv2 + bias + residual
+    CKR(launch_gn_stats(y, rows, C, rm, row_div, st2, stream));
+    CKR(launch_gn_apply_silu(y, rows, C, rm, row_div, st2, hp.gn_eps, R.n2w, R.n2b, vc.hi, stream));
+    p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x; p.ld_out = C; p.bias = R.c2b;
+    CKG(gemm(R.c2, vc, rows, p));
+    return {};
+}
+
+std::string engine::run_chunk(const chunk_info & c) {
+    cur_row0 = c.row0; cur_utt0 = c.utt0; cur_rows1 = c.rows1; cur_n_utts = c.n_utts;
+    const row_map rm = rmap();
+    const int R1 = c.rows1, R2 = 2 * R1, R6 = 6 * R1, R18 = 18 * R1;
+    const int D = hp.prenet_dim, C = hp.dec_dim;
+    gemm_params p;
+    std::string e;
+    CKG(cudaMemsetAsync(gn_stats, 0, (size_t) GN_SLOTS * max_utts * 64 * sizeof(double), stream));
+    int gn_slot = 0;
+
+    // 1. token gather
+    CKR(launch_gather(w.token_embd, d_codes + c.row0, x768, R1, D, hp.vocab, err_flag, stream));
+    snap_f32("embed", x768, (size_t) R1 * D);
+    // 2. prenet
+    for (int i = 0; i < hp.prenet_layers; i++) {
+        const prenet_layer_w & l = w.prenet[i];
+        CKR(launch_layernorm(x768, R1, D, hp.norm_eps, l.an_w, l.an_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
+        p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = qkv; p.ld_out = 3 * D;
+        CKG(gemm(l.qkv, vA768, R1, p));
+        if (i == 0) snap_f32("pre0_qkv", qkv, (size_t) R1 * 3 * D);
+        CKR(launch_attention(qkv, R1, D, hp.prenet_heads, hp.prenet_window, w.rope_pre, w.rope_max_pos, rm, 1, vA768.hi, vA768.lo, stream));
+        if (i == 0) snap_f16("pre0_attn", vA768.hi, vA768.lo, (size_t) R1 * D);
+        p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
+        CKG(gemm(l.wo, vA768, R1, p));
+        if (i == 0) snap_f32("pre0_x_attn", x768, (size_t) R1 * D);
+        CKR(launch_layernorm(x768, R1, D, hp.norm_eps, l.fn_w, l.fn_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
+        p = gemm_params(); p.epi = EPI_SWIGLU; p.out_hi = vFF2048.hi; p.out_lo = vFF2048.lo; p.ld_h = hp.prenet_ff;
+        CKG(gemm(l.gu, vA768, R1, p));
+        p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
+        CKG(gemm(l.down, vFF2048, R1, p));
+        if (i == 0) snap_f32("pre0_out", x768, (size_t) R1 * D);
+    }
+    snap_f32("prenet_x", x768, (size_t) R1 * D);
+    CKR(launch_layernorm(x768, R1, D, hp.norm_eps, w.pre_norm_w, w.pre_norm_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
+    // 2b. 768 -> 512 (+bias) written straight as the split operand of the ConvTranspose GEMM
+    p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = vA512.hi; p.out_lo = vA512.lo; p.ld_h = C; p.bias = w.pre_out_b;
+    // the prenet LN output lives in aA viewed as [R1][768]; the 512-wide result must not overwrite it while other
+    // CTAs still read it -> stage through aFF
+    p.out_hi = aFF_hi; p.out_lo = aFF_lo;
+    CKG(gemm(w.pre_out, vA768, R1, p));
+    snap_f16("prenet_out", aFF_hi, aFF_lo, (size_t) R1 * C);
+    // 3. wave_upsample ConvTranspose1d(k=2, s=2): [R1][2*512] == [R2][512]
+    {
+        a_view v = vFF1536;   // aFF viewed as [.][512]
+        if (!(e = view512_ff(v)).empty()) return e;
+        p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = x512; p.ld_out = 2 * C; p.bias = w.up0_b; p.bias_mod = C;
+        CKG(gemm(w.up0, v, R1, p));
+    }
+    snap_f32("upsample", x512, (size_t) R2 * C);
+    // 4. prior resnet blocks
+    for (int b = 0; b < hp.resnet_blocks; b++)
+        if (!(e = run_resblock(w.prior[b], x512, y512, vC512, R2, 2, gn_slot)).empty()) return e;
+    snap_f32("prior", x512, (size_t) R2 * C);
+    // 5. decoder: 8 AdaLN-Zero layers (conditioning vectors per voice were computed once in run())
+    for (int i = 0; i < hp.dec_layers; i++) {
+        const dec_layer_w & l = w.dec[i];
+        const int oa = (i * 2 + 0) * 3 * C, of = (i * 2 + 1) * 3 * C;     // shift | scale | gate
+        CKR(launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, oa, oa + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream));
+        p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = qkv; p.ld_out = 3 * C;
+        CKG(gemm(l.qkv, vA512, R2, p));
+        CKR(launch_attention(qkv, R2, C, hp.dec_heads, hp.dec_window, w.rope_pre, w.rope_max_pos, rm, 2, vA512.hi, vA512.lo, stream));
+        p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x512; p.ld_out = C;
+        p.gate = mod + oa + 2 * C; p.gate_ld = w.cond_rows; p.row_utt = rm.row_utt; p.row_div = 2; p.gate_voice = rm.voice;
+        CKG(gemm(l.wo, vA512, R2, p));
+        CKR(launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, of, of + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream));
+        p = gemm_params(); p.epi = EPI_SWIGLU; p.out_hi = vFF1536.hi; p.out_lo = vFF1536.lo; p.ld_h = hp.dec_ff;
+        CKG(gemm(l.gu, vA512, R2, p));
+        p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x512; p.ld_out = C;
+        p.gate = mod + of + 2 * C; p.gate_ld = w.cond_rows; p.row_utt = rm.row_utt; p.row_div = 2; p.gate_voice = rm.voice;
+        CKG(gemm(l.down, vFF1536, R2, p));
+        if (i == 0) snap_f32("dec0_out", x512, (size_t) R2 * C);
+    }
+    snap_f32("decoder_x", x512, (size_t) R2 * C);
+    // 6. final AdaLN (shift, scale only) -> fp32 in place
+    {
+        const int on = hp.dec_layers * 2 * 3 * C;
+        CKR(launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, on, on + C, rm, 2, nullptr, nullptr, x512, stream));
+    }
+    snap_f32("final_norm", x512, (size_t) R2 * C);
+    // 7. post resnet blocks
+    for (int b = 0; b < hp.resnet_blocks; b++)
+        if (!(e = run_resblock(w.post[b], x512, y512, vC512, R2, 2, gn_slot)).empty()) return e;
+    snap_f32("post", x512, (size_t) R2 * C);
+    // 8. upsampler stage 0: ConvT(512->256, k9 s3) + bias + trim + Snake, then resblock
+    CKR(launch_split(x512, R2, C, rm, 2, vA512.hi, vA512.lo, stream));
+    p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = x256; p.ld_out = 3 * 256; p.bias = w.upT_b[0]; p.bias_mod = 256;
+    p.snake_ea = w.snake_ea[0]; p.snake_eb = w.snake_eb[0];
+    CKG(gemm(w.upT[0], vA512, R2, p));
+    snap_f32("up0_snake", x256, (size_t) R6 * 256);
+    if (!(e = run_resblock(w.up_res[0], x256, y256, vC256, R6, 6, gn_slot)).empty()) return e;
+    snap_f32("up0", x256, (size_t) R6 * 256);
+    //    stage 1: ConvT(256->128, k9 s3)
+    CKR(launch_split(x256, R6, 256, rm, 6, vFF256.hi, vFF256.lo, stream));
+    p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = x128; p.ld_out = 3 * 128; p.bias = w.upT_b[1]; p.bias_mod = 128;
+    p.snake_ea = w.snake_ea[1]; p.snake_eb = w.snake_eb[1];
+    CKG(gemm(w.upT[1], vFF256, R6, p));
+    if (!(e = run_resblock(w.up_res[1], x128, y128, vC128, R18, 18, gn_slot)).empty()) return e;
+    snap_f32("up1", x128, (size_t) R18 * 128);
+    // 8b. out_proj 128 -> 512 + bias + Snake -> split operand of the head
+    CKR(launch_split(x128, R18, 128, rm, 18, vFF128.hi, vFF128.lo, stream));
+    p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = vH512.hi; p.out_lo = vH512.lo; p.ld_h = 512; p.bias = w.out_proj_b;
+    p.snake_ea = w.out_snake_ea; p.snake_eb = w.out_snake_eb;
+    CKG(gemm(w.out_proj, vFF128, R18, p));
+    // 9. head: 512 -> 394, exp/clamp/cos/sin -> interleaved (re, im)
+    p = gemm_params(); p.epi = EPI_HEAD; p.out_f32 = spec; p.ld_out = 2 * hp.n_freq; p.bias = w.head_b;
+    CKG(gemm(w.head, vH512, R18, p));
+    snap_f32("spec", spec, (size_t) R18 * 2 * hp.n_freq);
+    // ISTFT
+    if (!(e = run_istft(c, spec)).empty()) return e;
+    return {};
+}
+
+std::string engine::run_istft(const chunk_info & c, const float * spec_dev) {
+    istft_params ip;
+    ip.spec = spec_dev; ip.wave = d_wave;
+    ip.start = d_start + c.utt0; ip.len = d_len + c.utt0; ip.out_off = d_out_off + c.utt0;
+    ip.chunk_cu = d_chunk_cu + c.cu0; ip.hann = w.hann;
+    ip.n_utts = c.n_utts; ip.frames_per_code = hp.frames_per_code; ip.total_chunks = c.istft_blocks;
+    CKR(launch_istft(ip, stream));
+    return {};
+}
+
+std::string engine::view512_ff(a_view & v) {
+    if (!vFF512_ready) {
+        std::string e = make_view(vFF512, aFF_hi, aFF_lo, max_rows1 * 6, 512);
+        if (!e.empty()) return e;
+        vFF512_ready = true;
+    }
+    v = vFF512;
+    return {};
+}
+
+std::string engine::run(bool peak_normalize) {
+    if (!batch_uploaded) return "mio_batch_run before mio_batch_upload";
+    CK(cudaSetDevice(device));
+    launches = 0;
+    snaps.clear();
+    // AdaLN conditioning vectors of every voice of the batch (compute_adaln3, src/miocodec.cpp:310-319)
+    if (lay.n_utts > 0) CKR(launch_cond(d_voice_table, n_voices, hp.adaln_dim, w.cond_w, w.cond_b, w.cond_rows, mod, stream));
+    for (const chunk_info & c : chunks) {
+        std::string e = run_chunk(c);
+        if (!e.empty()) return e;
+    }
+    if (peak_normalize && lay.n_utts > 0) {
+        for (const chunk_info & c : chunks) {
+            CKR(launch_peak_normalize(d_wave, d_len + c.utt0, d_out_off + c.utt0, c.n_utts, hp.samples_per_token, peak, stream));
+            launches++;   // two kernels
+        }
+    }
+    batch_ran = true;
+    return {};
+}
+
+std::string engine::sync() {
+    CK(cudaSetDevice(device));
+    CK(cudaStreamSynchronize(stream));
+    int flag = 0;
+    CK(cudaMemcpy(&flag, err_flag, sizeof(int), cudaMemcpyDeviceToHost));
+    if (flag != 0) {
+        cudaMemset(err_flag, 0, sizeof(int));
+        return "RANGE: code index out of [0, " + std::to_string(hp.vocab) + ") at padded row " + std::to_string(flag - 1);
+    }
+    return {};
+}
+
+std::string engine::fetch_wave(float * out, int64_t cap) {
+    if (!batch_ran) return "mio_batch_fetch before mio_batch_run";
+    if (cap < wave_samples) return "output capacity too small";
+    std::string e = sync();
+    if (!e.empty()) return e;
+    if (wave_samples > 0) CK(cudaMemcpy(out, d_wave, (size_t) wave_samples * sizeof(float), cudaMemcpyDeviceToHost));
+    return {};
+}
+
+// spectrogram of utterance `utt` of a single-chunk batch (mio_decode_spec)
+std::string engine::fetch_spec(int utt, float * out, int64_t cap) {
+    if (!batch_ran) return "fetch before run";
+    if (chunks.size() != 1 || utt < 0 || utt >= lay.n_utts) return "fetch_spec needs a single-chunk batch";
+    std::string e = sync();
+    if (!e.empty()) return e;
+    const int fpc = hp.frames_per_code;
+    const size_t n = (size_t) lay.len[utt] * fpc * 2 * hp.n_freq;
+    if ((int64_t) n > cap) return "output capacity too small";
+    if (n) CK(cudaMemcpy(out, spec + (size_t) lay.start[utt] * fpc * 2 * hp.n_freq, n * sizeof(float), cudaMemcpyDeviceToHost));
+    return {};
+}
+
+// standalone ISTFT of a host spectrogram (mio_istft): one utterance of n_frames frames
+std::string engine::run_istft_only(const float * spec_host, int n_frames) {
+    std::string e = ensure_workspace();
+    if (!e.empty()) return e;
+    CK(cudaSetDevice(device));
+    const int fpc = hp.frames_per_code;
+    if (n_frames <= 0) return "bad argument";
+    if ((int64_t) n_frames > (int64_t) max_rows1 * fpc) return "too many frames for the workspace";
+    batch_uploaded = false; batch_ran = false;
+    // layout: a single pseudo-utterance whose length is counted in frames (frames_per_code = 1)
+    const int32_t start0 = 0, len0 = n_frames;
+    const int64_t off0 = 0;
+    const int blocks = (n_frames + ISTFT_SEG_PER_BLOCK - 1) / ISTFT_SEG_PER_BLOCK;
+    const int32_t ccu[2] = {0, blocks};
+    if (!d_start) {
+        cap_utts = 64;
+        if (!(e = dev_alloc(&d_start, cap_utts)).empty() || !(e = dev_alloc(&d_len, cap_utts)).empty() ||
+            !(e = dev_alloc(&d_voice, cap_utts)).empty() || !(e = dev_alloc(&d_out_off, cap_utts)).empty()) return e;
+    }
+    if (!d_chunk_cu) { cap_ccu = 64; if (!(e = dev_alloc(&d_chunk_cu, cap_ccu)).empty()) return e; }
+    wave_samples = (int64_t) n_frames * hp.hop;
+    if (wave_cap < wave_samples) {
+        if (d_wave) cudaFree(d_wave);
+        d_wave = nullptr; wave_cap = wave_samples + 64;
+        if (!(e = dev_alloc(&d_wave, (size_t) wave_cap)).empty()) return e;
+    }
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaMemcpy(d_start, &start0, 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_len, &len0, 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_out_off, &off0, 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_chunk_cu, ccu, 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(spec, spec_host, (size_t) n_frames * 2 * hp.n_freq * sizeof(float), cudaMemcpyHostToDevice));
+    istft_params ip;
+    ip.spec = spec; ip.wave = d_wave; ip.start = d_start; ip.len = d_len; ip.out_off = d_out_off; ip.chunk_cu = d_chunk_cu;
+    ip.hann = w.hann; ip.n_utts = 1; ip.frames_per_code = 1; ip.total_chunks = blocks;
+    launches = 0;
+    CKR(launch_istft(ip, stream));
+    lay = batch_layout();
+    batch_ran = true;
+    return {};
+}
+
+}  // namespace mio

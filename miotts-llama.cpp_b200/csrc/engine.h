@@ -1,0 +1,96 @@
+// The decoder engine: owns the device weights, the workspace and the per-batch layout, and enqueues the kernel
+// sequence of one ragged batch.  Host-side replacement of miocodec_decode()'s graph build + compute
+// (src/miocodec.cpp:519-810 of the reference) followed by istft() (src/istft.cpp:68-108).
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+#include "model.h"
+
+namespace mio {
+
+struct a_view {                  // an fp16 operand buffer viewed as [rows][K] with its TMA maps
+    __half * hi = nullptr; __half * lo = nullptr;
+    int K = 0, rows = 0;
+    CUtensorMap tm_hi, tm_lo;
+};
+
+struct chunk_info {              // a run of whole utterances that fits the workspace
+    int utt0 = 0, n_utts = 0;    // utterance range
+    int row0 = 0, rows1 = 0;     // rows (code resolution) in the concatenated device arrays
+    int cu0 = 0;                 // offset of this chunk's ISTFT block prefix in d_chunk_cu
+    int istft_blocks = 0;
+};
+
+struct engine {
+    int device = 0;
+    hparams hp;
+    weights w;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    bool use_simt = false;
+    int max_rows1 = 16384 + 512;     // workspace rows at code resolution (codes + pad rows)
+    bool ws_ready = false;
+    bool debug_snap = false;
+    std::map<std::string, std::vector<float>> snaps;
+    std::string err;
+    int64_t launches = 0;
+
+    // ---- workspace (device)
+    float *x768 = nullptr, *qkv = nullptr, *x512 = nullptr, *y512 = nullptr, *x256 = nullptr, *y256 = nullptr,
+          *x128 = nullptr, *y128 = nullptr, *spec = nullptr, *mod = nullptr, *peak = nullptr;
+    __half *aA_hi = nullptr, *aA_lo = nullptr, *aFF_hi = nullptr, *aFF_lo = nullptr, *c16 = nullptr,
+           *h512_hi = nullptr, *h512_lo = nullptr;
+    double * gn_stats = nullptr;      // [GN_SLOTS][max_utts][32][2]
+    int * err_flag = nullptr;
+    a_view vA768, vA512, vFF2048, vFF1536, vFF256, vFF128, vFF512, vC512, vC256, vC128, vH512;
+    bool vFF512_ready = false;
+    std::vector<void *> w_allocs;     // every weight allocation (freed in the destructor)
+    int max_utts = 4096;
+    int max_voices = 1024;
+
+    // ---- current batch (device copies of the layout)
+    batch_layout lay;
+    std::vector<chunk_info> chunks;
+    int cur_row0 = 0, cur_utt0 = 0, cur_rows1 = 0, cur_n_utts = 0;
+    size_t cap_rows = 0, cap_rows_ru = 0, cap_utts = 0, cap_ccu = 0, cap_vt = 0;
+    size_t h2d_bytes = 0;
+    int32_t *d_codes = nullptr, *d_row_utt = nullptr, *d_start = nullptr, *d_len = nullptr, *d_voice = nullptr,
+            *d_chunk_cu = nullptr;
+    int64_t * d_out_off = nullptr;
+    float * d_voice_table = nullptr;
+    int n_voices = 0;
+    float * d_wave = nullptr; int64_t wave_cap = 0;       // resident output of the last batch
+    int64_t wave_samples = 0;
+    int istft_chunks = 0;
+    // streaming emit buffers (stream.cu)
+    void * d_emit = nullptr; void * d_emit_jobs = nullptr; void * h_emit = nullptr;
+    int64_t emit_cap = 0, emit_jobs_cap = 0;
+    // pinned staging
+    void * h_stage = nullptr; size_t h_stage_bytes = 0;
+    bool batch_uploaded = false, batch_ran = false;
+
+    ~engine();
+    std::string load(const std::string & gguf_path, int device);
+    std::string ensure_workspace();
+    // layout + H2D. codes_concat/cu_seqlens in the caller's (unpadded) indexing.
+    std::string upload(const int32_t * codes, const int32_t * cu, int n_utts, const float * voice_table, int n_voices,
+                       const int32_t * voice_ids);
+    std::string run(bool peak_normalize);                 // enqueue all kernels of the uploaded batch
+    std::string run_istft_only(const float * spec_host, int n_frames);   // mio_istft
+    std::string sync();                                   // stream sync + error flag
+    std::string fetch_wave(float * out, int64_t cap);
+    std::string fetch_spec(int utt, float * out, int64_t cap);
+    row_map rmap() const;
+    std::string run_chunk(const chunk_info & c);
+    std::string run_resblock(const resblock_w & R, float * x, float * y, const a_view & vc, int rows, int row_div, int & gn_slot);
+    std::string run_istft(const chunk_info & c, const float * spec_dev);
+    std::string view512_ff(a_view & v);
+    cudaError_t gemm(const gemm_weight & W, const a_view & A, int M, gemm_params p);
+    void snap_f32(const char * name, const float * d, size_t n);
+    void snap_f16(const char * name, const __half * hi, const __half * lo, size_t n);
+};
+
+}  // namespace mio

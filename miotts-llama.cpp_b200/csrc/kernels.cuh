@@ -1,0 +1,98 @@
+// Launchers of the sm_100a kernels.  Everything here works on the padded row space described in DESIGN.md:
+// activations are row-major [rows][C] (channels contiguous), rows of all utterances of a batch are
+// concatenated, each utterance followed by r zero rows at resolution r in {1, 2, 6, 18}.
+#pragma once
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace mio {
+
+// ------------------------------------------------------------------------------------------ GEMM
+enum epi_kind : int {
+    EPI_STORE = 0,   // out_f32[row][col] = acc*s + bias
+    EPI_RESID = 1,   // out_f32[row][col] += (acc*s + bias) * gate[utt][col]
+    EPI_SWIGLU = 2,  // columns interleaved (gate, up): h = silu(g)*u -> split fp16 at col/2
+    EPI_SPLIT = 3,   // y = acc*s + bias (-> snake) -> split fp16
+    EPI_SNAKE = 4,   // y = snake(acc*s + bias) -> out_f32
+    EPI_HEAD = 5     // columns interleaved (log-mag, phase): (re, im) -> out_f32
+};
+
+struct gemm_params {
+    int M = 0, N = 0, K = 0, taps = 1;     // D[M][N] = sum_tap A[row + tap - (taps==3)][K] * B[N][tap*K + k]
+    int npass = 3;                         // 3: (a_hi + a_lo)(b_hi + b_lo) without lo*lo; 1: a_hi * b_hi
+    float out_scale = 1.f;
+    int epi = EPI_STORE;
+    float * out_f32 = nullptr; int ld_out = 0;
+    __half * out_hi = nullptr; __half * out_lo = nullptr; int ld_h = 0;
+    const float * bias = nullptr; int bias_mod = 1;
+    const float * gate = nullptr; int gate_ld = 0;        // gate[gate_voice[utt]*gate_ld + col]
+    const int32_t * gate_voice = nullptr;
+    const int32_t * row_utt = nullptr; int row_div = 1;   // utt = row_utt[row / row_div] (<0: pad row)
+    const float * snake_ea = nullptr; const float * snake_eb = nullptr;   // exp(alpha), exp(beta) [bias_mod]
+    // raw operand pointers (SIMT validation path; the tcgen05 path reads through the tensor maps)
+    const __half * a_hi = nullptr; const __half * a_lo = nullptr; int lda = 0; int a_rows = 0;
+    const __half * b_hi = nullptr; const __half * b_lo = nullptr;
+};
+
+// tcgen05 path. tmA_* : 2-D maps over [a_rows][K] fp16, box {64, 128}; tmB_*: over [N][taps*K], box {64, bn}.
+cudaError_t launch_gemm_tc(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
+                           const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, int bn, cudaStream_t st);
+cudaError_t launch_gemm_simt(const gemm_params & p, cudaStream_t st);
+cudaError_t gemm_tc_init();   // sets the dynamic shared memory attributes once
+
+// ------------------------------------------------------------------------------------------ elementwise
+struct row_map {                 // device pointers describing the padded row space of the current batch
+    const int32_t * row_utt;     // [rows1] utterance id or -1 (code resolution)
+    const int32_t * start;       // [n_utts] first row (code resolution)
+    const int32_t * len;         // [n_utts] codes
+    const int32_t * voice;       // [n_utts]
+    int rows1;
+    int n_utts;
+};
+
+cudaError_t launch_gather(const float * table, const int32_t * codes_padded, float * x, int rows, int D, int vocab,
+                          int * err_flag, cudaStream_t st);
+// LayerNorm over D (768 or 512). affine (w,b) for the prenet; AdaLN modulation (mod) for the decoder.
+// Outputs: split fp16 (out_hi/out_lo) and/or fp32 (out_f32). Pad rows produce zeros.
+cudaError_t launch_layernorm(const float * x, int rows, int D, float eps, const float * w, const float * b,
+                             const float * mod, int mod_ld, int shift_off, int scale_off, const row_map & rm, int row_div,
+                             __half * out_hi, __half * out_lo, float * out_f32, cudaStream_t st);
+// banded local attention with RoPE (adjacent pairs) on q,k. qkv: [rows][3*D] fp32; out: split fp16 [rows][D]
+cudaError_t launch_attention(const float * qkv, int rows, int D, int n_head, int window, const float * rope,
+                             int rope_max_pos, const row_map & rm, int row_div, __half * out_hi, __half * out_lo,
+                             cudaStream_t st);
+cudaError_t attention_init();
+// GroupNorm statistics: stats[utt][32][2] (sum, sum of squares; double), rows at resolution row_div
+cudaError_t launch_gn_stats(const float * x, int rows, int C, const row_map & rm, int row_div, double * stats,
+                            cudaStream_t st);
+// y = fp16( silu( (x-mean)*rstd*w + b ) ), zeros on pad rows
+cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double * stats,
+                                 float eps, const float * w, const float * b, __half * out, cudaStream_t st);
+cudaError_t launch_split(const float * x, int rows, int C, const row_map & rm, int row_div, __half * hi, __half * lo,
+                         cudaStream_t st);
+// mod[voice][cond_rows] = W[cond_rows][128] * silu(emb[voice]) + b
+cudaError_t launch_cond(const float * voice_table, int n_voices, int adaln_dim, const float * w, const float * b,
+                        int cond_rows, float * mod, cudaStream_t st);
+
+// ------------------------------------------------------------------------------------------ ISTFT
+struct istft_params {
+    const float * spec;          // [rows18][394]
+    float * wave;                // output samples
+    const int32_t * start;       // [n_utts] first row at code resolution (frames start at fpc*start)
+    const int32_t * len;         // [n_utts] codes
+    const int64_t * out_off;     // [n_utts] sample offset in wave
+    const int32_t * chunk_cu;    // [n_utts+1] prefix sum of per-utterance chunk counts
+    const float * hann;          // [392]
+    int n_utts;
+    int frames_per_code;         // 18
+    int total_chunks;
+};
+constexpr int ISTFT_SEG_PER_BLOCK = 28;   // output hops (98 samples) per block; +4 halo frames
+cudaError_t launch_istft(const istft_params & p, cudaStream_t st);
+// per-utterance peak normalisation 0.95/max|s| (src/test-to-speech.cpp:289-300)
+cudaError_t launch_peak_normalize(float * wave, const int32_t * len, const int64_t * out_off, int n_utts,
+                                  int samples_per_code, float * peak_scratch, cudaStream_t st);
+
+}  // namespace mio

@@ -1,0 +1,203 @@
+// Streaming policy of TestToSpeech::synthesize_stream_profiled (src/test-to-speech.cpp:348-626 of the reference),
+// re-implemented for many concurrent streams:
+//   * cadence / holdback / min-commit decisions are integer logic on the host (maybe_emit, :507-571)
+//   * every stream whose cadence fired is re-decoded over its full prefix in ONE ragged device batch
+//   * the crossfade with the previously emitted tail, the tail update and the cut [begin, end) of the window
+//     (emit_range, :367-417) run in a device kernel, so only the newly committed samples cross PCIe
+#include "stream.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace mio {
+
+struct emit_job {                 // one firing stream in the current round
+    int64_t wave_off;             // window audio of this job inside engine::d_wave
+    int64_t begin, end;           // sample range of the window to emit
+    int64_t emit_off;             // offset in the round's emit buffer
+    float * tail;                 // device, capacity MIO_TAIL_CAP
+    int * tail_len;               // device
+    int chunk, xfade;
+};
+
+// one block per job. out[j] = window[begin+j], the first chunk cross-faded with the stored tail:
+//   a = (j+1)/(xf+1), out = (1-a)*tail[j] + a*x   (products and sum rounded separately like the reference's
+//   scalar loop, :388-395); new tail = last `xfade` samples of the last chunk, or the whole last chunk if shorter.
+__global__ void stream_emit_kernel(const float * __restrict__ wave, float * __restrict__ emit, const emit_job * __restrict__ jobs) {
+    const emit_job J = jobs[blockIdx.x];
+    const int64_t n = J.end - J.begin;
+    if (n <= 0) return;
+    const float * src = wave + J.wave_off + J.begin;
+    float * dst = emit + J.emit_off;
+    const int tl = *J.tail_len;
+    const int64_t first_n = min((int64_t) J.chunk, n);
+    const int xf = (int) min((int64_t) tl, first_n);
+    for (int64_t j = threadIdx.x; j < n; j += blockDim.x) {
+        float v = src[j];
+        if (j < xf) {
+            const float a = (float) (j + 1) / (float) (xf + 1);
+            const float b = 1.0f - a;
+            v = __fadd_rn(__fmul_rn(b, J.tail[j]), __fmul_rn(a, v));
+        }
+        dst[j] = v;
+    }
+    __syncthreads();   // (global writes of this block are visible to the block after the barrier)
+    const int64_t last0 = ((n - 1) / J.chunk) * J.chunk;
+    const int64_t last_n = n - last0;
+    const int new_len = (int) (last_n >= J.xfade ? J.xfade : last_n);
+    const int64_t t0 = n - new_len;
+    __threadfence_block();
+    for (int j = threadIdx.x; j < new_len; j += blockDim.x) J.tail[j] = dst[t0 + j];
+    if (threadIdx.x == 0) *J.tail_len = new_len;
+}
+
+void stream_default_config(const engine & E, mio_stream_config * cfg) {
+    cfg->check_interval = 20;
+    cfg->holdback_codes = 32;
+    cfg->min_commit_codes = 24;
+    cfg->crossfade_samples = std::min(E.hp.sample_rate * 3 / 100, 4096);
+    cfg->chunk_samples = 4096;
+}
+
+stream_state::~stream_state() {
+    if (d_tail) cudaFree(d_tail);
+    if (d_tail_len) cudaFree(d_tail_len);
+}
+
+std::string stream_open(engine & E, const float * emb, const mio_stream_config * cfg, stream_state ** out) {
+    stream_state * s = new stream_state();
+    s->eng = &E;
+    stream_default_config(E, &s->cfg);
+    if (cfg) {
+        s->cfg = *cfg;
+        if (s->cfg.crossfade_samples < 0) s->cfg.crossfade_samples = std::min(E.hp.sample_rate * 3 / 100, 4096);
+        if (s->cfg.chunk_samples <= 0) s->cfg.chunk_samples = 4096;     // :360-362
+    }
+    if (s->cfg.check_interval <= 0 || s->cfg.holdback_codes < 0 || s->cfg.min_commit_codes < 0 ||
+        s->cfg.crossfade_samples > MIO_TAIL_CAP) { delete s; return "bad stream configuration"; }
+    s->emb.assign(emb, emb + E.hp.adaln_dim);
+    cudaSetDevice(E.device);
+    if (cudaMalloc(&s->d_tail, MIO_TAIL_CAP * sizeof(float)) != cudaSuccess || cudaMalloc(&s->d_tail_len, sizeof(int)) != cudaSuccess ||
+        cudaMemset(s->d_tail_len, 0, sizeof(int)) != cudaSuccess) { delete s; return "cudaMalloc failed (stream tail)"; }
+    *out = s;
+    return {};
+}
+
+// maybe_emit(is_final) evaluated with the prefix length `n` (src/test-to-speech.cpp:507-571)
+static void maybe_emit(stream_state & s, size_t n, bool is_final) {
+    if (n == 0) { if (is_final) s.final_queued = true; return; }
+    const size_t hold = (size_t) s.cfg.holdback_codes;
+    const size_t target = is_final ? n : (n > hold ? n - hold : 0);
+    if (target <= s.committed) { if (is_final) s.final_queued = true; return; }
+    if (!is_final && (target - s.committed) < (size_t) s.cfg.min_commit_codes) return;
+    stream_job j;
+    j.prefix = n; j.commit_begin = s.committed; j.commit_end = target; j.is_final = is_final;
+    s.jobs.push_back(j);
+    s.committed = target;          // the reference commits right after a successful decode
+    if (is_final) s.final_queued = true;
+}
+
+std::string stream_push(stream_state & s, const int32_t * codes, int n) {
+    if (s.finished) return "stream already finished";
+    for (int i = 0; i < n; i++) {
+        s.codes.push_back(codes[i]);
+        if ((s.codes.size() % (size_t) s.cfg.check_interval) == 0) maybe_emit(s, s.codes.size(), false);   // :608-613
+    }
+    return {};
+}
+
+std::string stream_finish(stream_state & s) {
+    if (s.finished) return {};
+    s.finished = true;
+    maybe_emit(s, s.codes.size(), true);   // :616-618
+    s.final_queued = true;
+    return {};
+}
+
+std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
+    cudaSetDevice(E.device);
+    const int spc = E.hp.samples_per_token;
+    for (;;) {
+        // round: the oldest pending job of every stream (jobs of one stream are ordered through its tail)
+        std::vector<stream_state *> act;
+        for (int i = 0; i < n_streams; i++)
+            if (streams[i] && streams[i]->job_head < streams[i]->jobs.size()) act.push_back(streams[i]);
+        if (act.empty()) break;
+        if ((int) act.size() > E.max_voices) act.resize(E.max_voices);
+        std::vector<int32_t> codes, cu(1, 0), vid;
+        std::vector<float> vt;
+        for (size_t k = 0; k < act.size(); k++) {
+            const stream_job & j = act[k]->jobs[act[k]->job_head];
+            codes.insert(codes.end(), act[k]->codes.begin(), act[k]->codes.begin() + j.prefix);
+            cu.push_back((int32_t) codes.size());
+            vid.push_back((int32_t) k);
+            vt.insert(vt.end(), act[k]->emb.begin(), act[k]->emb.end());
+        }
+        std::string e = E.upload(codes.data(), cu.data(), (int) act.size(), vt.data(), (int) act.size(), vid.data());
+        if (!e.empty()) return e;
+        e = E.run(false);      // streaming never peak-normalises (decode_codes_to_audio(..., false), :546)
+        if (!e.empty()) return e;
+        // cut + crossfade on the device
+        std::vector<emit_job> jobs(act.size());
+        int64_t emit_total = 0;
+        for (size_t k = 0; k < act.size(); k++) {
+            stream_state & s = *act[k];
+            const stream_job & j = s.jobs[s.job_head];
+            const int64_t win = (int64_t) j.prefix * spc;                       // window_audio.size()
+            const double spc_actual = (double) win / (double) j.prefix;          // :554-556
+            const int64_t b = (int64_t) std::llround((double) j.commit_begin * spc_actual);
+            const int64_t en = std::min<int64_t>((int64_t) std::llround((double) j.commit_end * spc_actual), win);
+            emit_job & J = jobs[k];
+            J.wave_off = (int64_t) cu[k] * spc; J.begin = b; J.end = std::max(b, en); J.emit_off = emit_total;
+            J.tail = s.d_tail; J.tail_len = s.d_tail_len; J.chunk = s.cfg.chunk_samples; J.xfade = s.cfg.crossfade_samples;
+            emit_total += J.end - J.begin;
+            s.decode_calls++; s.decoded_codes += (int64_t) j.prefix;
+        }
+        if (E.emit_cap < emit_total || E.emit_jobs_cap < (int64_t) jobs.size()) {
+            if (E.d_emit) cudaFree(E.d_emit);
+            if (E.d_emit_jobs) cudaFree(E.d_emit_jobs);
+            if (E.h_emit) cudaFreeHost(E.h_emit);
+            E.emit_cap = emit_total + emit_total / 4 + 4096;
+            E.emit_jobs_cap = (int64_t) jobs.size() + 64;
+            if (cudaMalloc(&E.d_emit, (size_t) E.emit_cap * sizeof(float)) != cudaSuccess ||
+                cudaMalloc(&E.d_emit_jobs, (size_t) E.emit_jobs_cap * sizeof(emit_job)) != cudaSuccess ||
+                cudaMallocHost(&E.h_emit, (size_t) E.emit_cap * sizeof(float)) != cudaSuccess) return "cudaMalloc failed (emit buffers)";
+        }
+        if (cudaMemcpyAsync(E.d_emit_jobs, jobs.data(), jobs.size() * sizeof(emit_job), cudaMemcpyHostToDevice, E.stream) != cudaSuccess)
+            return "cudaMemcpyAsync failed (emit jobs)";
+        stream_emit_kernel<<<(unsigned) jobs.size(), 256, 0, E.stream>>>(E.d_wave, (float *) E.d_emit, (const emit_job *) E.d_emit_jobs);
+        E.launches++;
+        if (cudaGetLastError() != cudaSuccess) return "stream_emit_kernel launch failed";
+        if (emit_total > 0 &&
+            cudaMemcpyAsync(E.h_emit, E.d_emit, (size_t) emit_total * sizeof(float), cudaMemcpyDeviceToHost, E.stream) != cudaSuccess)
+            return "cudaMemcpyAsync failed (emit D2H)";
+        e = E.sync();
+        if (!e.empty()) return e;
+        for (size_t k = 0; k < act.size(); k++) {
+            stream_state & s = *act[k];
+            const emit_job & J = jobs[k];
+            const float * src = (const float *) E.h_emit + J.emit_off;
+            s.queue.insert(s.queue.end(), src, src + (J.end - J.begin));
+            s.emitted_samples += J.end - J.begin;
+            s.job_head++;
+        }
+    }
+    for (int i = 0; i < n_streams; i++) {
+        stream_state * s = streams[i];
+        if (s && s->final_queued && s->job_head >= s->jobs.size()) s->done = true;
+    }
+    return {};
+}
+
+int64_t stream_read(stream_state & s, float * out, int64_t cap, int * is_last) {
+    const int64_t avail = (int64_t) s.queue.size() - s.queue_head;
+    const int64_t n = std::max<int64_t>(0, std::min(avail, cap));
+    if (n > 0) memcpy(out, s.queue.data() + s.queue_head, (size_t) n * sizeof(float));
+    s.queue_head += n;
+    if (s.queue_head == (int64_t) s.queue.size()) { s.queue.clear(); s.queue_head = 0; }
+    if (is_last) *is_last = (s.done && s.queue.empty()) ? 1 : 0;
+    return n;
+}
+
+}  // namespace mio

@@ -1,0 +1,43 @@
+// Host state of one audio stream (see stream.cu).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "../../include/miocodec_b200.h"
+#include "engine.h"
+
+namespace mio {
+
+constexpr int MIO_TAIL_CAP = 4096;   // crossfade_samples is capped at 4096 by the reference (:364)
+
+struct stream_job {
+    size_t prefix = 0;            // codes decoded (the whole prefix at the time the cadence fired)
+    size_t commit_begin = 0, commit_end = 0;
+    bool is_final = false;
+};
+
+struct stream_state {
+    engine * eng = nullptr;
+    mio_stream_config cfg;
+    std::vector<float> emb;
+    std::vector<int32_t> codes;
+    size_t committed = 0;
+    std::vector<stream_job> jobs;
+    size_t job_head = 0;
+    bool finished = false, final_queued = false, done = false;
+    float * d_tail = nullptr;
+    int * d_tail_len = nullptr;
+    std::vector<float> queue;     // emitted samples not yet read
+    int64_t queue_head = 0;
+    int64_t decode_calls = 0, decoded_codes = 0, emitted_samples = 0;
+    ~stream_state();
+};
+
+void stream_default_config(const engine & E, mio_stream_config * cfg);
+std::string stream_open(engine & E, const float * emb, const mio_stream_config * cfg, stream_state ** out);
+std::string stream_push(stream_state & s, const int32_t * codes, int n);
+std::string stream_finish(stream_state & s);
+std::string streams_step(engine & E, stream_state ** streams, int n_streams);
+int64_t stream_read(stream_state & s, float * out, int64_t cap, int * is_last);
+
+}  // namespace mio
