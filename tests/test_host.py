@@ -1,0 +1,113 @@
+"""CPU tests of the host side: the C-ABI library loads without a GPU and exports every declared symbol, the GGUF
+reader / voice loader behave like the reference's, errors are reported (never a silent CPU fallback), and the FFT
+arithmetic of the ISTFT kernel (shared host/device header) is exact."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+PKG = os.path.join(ROOT, "miotts-llama.cpp_b200")
+
+
+def _lib():
+    from miocodec_b200 import binding
+    if not os.path.exists(binding.LIB_PATH):
+        import __graft_entry__
+        __graft_entry__.build()
+    return binding.lib()
+
+
+def test_library_exports_every_declared_symbol():
+    from miocodec_b200 import binding
+    L = _lib()
+    header = open(os.path.join(ROOT, "include", "miocodec_b200.h")).read()
+    declared = sorted(set(re.findall(r"\b(mio_[a-z0-9_]+)\s*\(", header)))
+    assert declared == sorted(binding.EXPORTS)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert b"sm_100a" in L.mio_version()
+
+
+def test_no_cpu_fallback_and_error_codes(assets, tmp_path):
+    import torch
+    from miocodec_b200 import binding
+    L = _lib()
+    h = C.c_void_p()
+    rc = L.mio_ctx_create(b"/nonexistent/miocodec.gguf", 0, C.byref(h))
+    assert rc == binding.MIO_ERR_IO and not h.value
+    bad = tmp_path / "bad.gguf"
+    bad.write_bytes(b"NOPE" + b"\0" * 64)
+    assert L.mio_ctx_create(str(bad).encode(), 0, C.byref(h)) == binding.MIO_ERR_FORMAT
+    if not torch.cuda.is_available():
+        rc = L.mio_ctx_create(assets[0].encode(), 0, C.byref(h))
+        assert rc == binding.MIO_ERR_CUDA and not h.value
+        assert b"no CPU fallback" in L.mio_last_error() or b"CUDA" in L.mio_last_error()
+        assert binding.miocodec_load(assets[0]) is None          # reference contract: nullptr on failure
+    assert L.mio_ctx_sample_rate(None) == 0                      # null-safe accessors
+
+
+def test_voice_loader_matches_reference_layout(assets, tmp_path):
+    from miocodec_b200 import binding, synth
+    _lib()
+    for v in (0, 5):
+        emb = binding.load_voice_embedding(assets[1][v])
+        assert emb.dtype == np.float32 and emb.shape == (128,)
+        assert np.array_equal(emb, synth.synth_voice(v))
+    # first tensor whatever its name; non-F32 rejected; missing file -> empty (src/miocodec.cpp:816-853)
+    w = synth.GGUFWriter("mio-embedding")
+    w.add_u32("mio.embedding.dim", 4)
+    w.add_tensor("anything", np.arange(4, dtype=np.float32))
+    w.add_tensor("second", np.ones(4, dtype=np.float32))
+    p = str(tmp_path / "v.gguf")
+    w.write(p)
+    assert np.array_equal(binding.load_voice_embedding(p), np.arange(4, dtype=np.float32))
+    w = synth.GGUFWriter("mio-embedding")
+    w.add_tensor("h", np.arange(4, dtype=np.float16))
+    w.write(p)
+    assert binding.load_voice_embedding(p).size == 0
+    assert binding.load_voice_embedding(str(tmp_path / "missing.gguf")).size == 0
+    from oracle import ref
+    if ref.available():
+        R = ref.Reference(assets[0])
+        assert np.array_equal(R.load_voice(assets[1][3]), binding.load_voice_embedding(assets[1][3]))
+        R.close()
+
+
+def test_print_tensors_lists_all_227(assets, capfd):
+    from miocodec_b200 import binding
+    _lib()
+    binding.miocodec_print_tensors(assets[0])
+    out = capfd.readouterr().out
+    assert "Tensors in" in out and ": 227" in out
+    assert "token_embd" in out and "istft_head.out.weight" in out and "miocodec.wave_upsampler.factors" in out
+
+
+def test_fft_arithmetic_of_the_istft_kernel(tmp_path):
+    """csrc/istft_math.h is compiled for the host and checked against the reference's irfft formula."""
+    exe = str(tmp_path / "istft_math_test")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", os.path.join(PKG, "csrc", "istft_math_test.cpp"), "-o", exe])
+    for seed in ("1", "2"):
+        out = subprocess.run([exe, seed], capture_output=True, text=True)
+        assert out.returncode == 0, out.stdout
+        err = float(out.stdout.split()[1])
+        assert err < 5e-7
+
+
+def test_sharding_balances_and_covers():
+    from miocodec_b200 import sharding
+    rng = np.random.default_rng(5)
+    lens = rng.integers(50, 751, size=4096)
+    for world in (1, 2, 4, 8):
+        parts = [sharding.shard_utterances(lens, world, r) for r in range(world)]
+        allidx = np.sort(np.concatenate(parts))
+        assert np.array_equal(allidx, np.arange(len(lens)))          # every utterance exactly once
+        loads = np.array([lens[p].sum() for p in parts], dtype=np.float64)
+        assert loads.max() / loads.mean() < 1.01                      # longest-first packing: <1% imbalance
+    assert sharding.shard_utterances(np.array([], dtype=np.int64), 4, 2).size == 0
+    assert sharding.shard_utterances(np.array([7]), 4, 3).size + sharding.shard_utterances(np.array([7]), 4, 0).size == 1

@@ -1,0 +1,100 @@
+"""CPU tests of the oracle itself: the torch restatement (oracle/port.py) against golden vectors produced by the
+unmodified reference, the compiled reference (oracle/_ref) against the same vectors when it is present, and the
+known-answer structure of the path (frame / sample counts)."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, load_golden, snr_db
+
+
+def test_weights_digest_matches_golden(weights):
+    # the goldens are only meaningful for bit-identical synthetic weights
+    _, W = weights
+    from miocodec_b200 import synth
+    _, tensors = synth.synth_tensors(0)
+    h = hashlib.sha256()
+    for name, arr in tensors:
+        h.update(name.encode())
+        h.update(np.ascontiguousarray(arr).tobytes())
+    meta = dict(l.strip().split("=", 1) for l in open(os.path.join(GOLDEN, "meta.txt")))
+    assert h.hexdigest() == meta["weights_sha256"]
+    assert len(tensors) == 227                      # 227 tensors
+    assert sum(int(np.prod(a.shape)) for _, a in tensors if a.dtype != np.int32) == 92_344_074
+
+
+@pytest.mark.parametrize("case", ["ref20", "rand33", "one"])
+def test_port_matches_reference_golden(weights, case):
+    """The port is an independent fp32 evaluation; the reference's own FP16 operand rounding in conv1d
+    (ggml.c:4416) makes its output discontinuous in fp32 round-off, which caps ANY independent evaluation at
+    ~60 dB (DESIGN.md 'parity floor'); counts and indexing are exact."""
+    from miocodec_b200 import synth
+    from oracle import port
+    hp, W = weights
+    g = load_golden(case)
+    codes, vid = g["codes"], int(g["voice"])
+    spec = port.decode(W, hp, codes, synth.synth_voice(vid))
+    assert spec.shape == g["spec"].shape == (18 * len(codes), 394)
+    assert snr_db(spec, g["spec"]) > 55.0
+    wave = port.istft(spec)
+    assert wave.shape == g["wave"].shape == (1764 * len(codes),)
+    assert snr_db(wave, g["wave"]) > 55.0
+    assert np.abs(wave - g["wave"]).max() < 5e-3 * max(1.0, np.abs(g["wave"]).max())
+
+
+def test_port_istft_matches_reference_golden():
+    from oracle import port
+    for case in ("ref20", "istft50"):
+        g = load_golden(case)
+        wave = port.istft(g["spec"])
+        assert wave.shape == g["wave"].shape
+        assert snr_db(wave, g["wave"]) > 110.0
+        assert np.abs(wave - g["wave"]).max() < 2e-5 * max(1.0, np.abs(g["wave"]).max())
+
+
+def test_compiled_reference_reproduces_golden(assets):
+    from oracle import ref
+    if not ref.available():
+        pytest.skip("oracle/_ref not built on this machine")
+    from miocodec_b200 import synth
+    R = ref.Reference(assets[0])
+    g = load_golden("ref20")
+    spec = R.decode_spec(g["codes"], synth.synth_voice(int(g["voice"])))
+    meta = dict(l.strip().split("=", 1) for l in open(os.path.join(GOLDEN, "meta.txt")))
+    if R.variant == meta["variant"]:
+        assert np.array_equal(spec, g["spec"])          # bitwise deterministic
+    else:
+        assert snr_db(spec, g["spec"]) > 55.0           # other SIMD width => other summation order
+    wave = R.istft(g["spec"])
+    assert snr_db(wave, g["wave"]) > 120.0
+    assert R.samples_per_token == 1764 and R.n_fft == 392 and R.hop == 98 and R.sample_rate == 44100
+    R.close()
+
+
+def test_stream_policy_cadence():
+    """Cadence known answers: decodes fire at n = 60, 100, 140, ... and once more at the end."""
+    from oracle import port
+    calls = []
+
+    def fake_decode(c):
+        calls.append(len(c))
+        return np.arange(len(c) * 1764, dtype=np.float32)
+
+    codes = np.zeros(230, dtype=np.int32)
+    out, st = port.stream_policy(fake_decode, codes)
+    assert calls == [60, 100, 140, 180, 220, 230]
+    assert st["decoded_codes"] == sum(calls) and st["emitted_samples"] == 230 * 1764 == len(out)
+    # with a waveform that does not depend on the prefix, only the cross-faded heads differ from offline
+    ref = np.arange(230 * 1764, dtype=np.float32)
+    diff = np.nonzero(out != ref)[0]
+    assert len(diff) == 0 or diff.max() < 230 * 1764
+    # a multiple of 20 decodes the last prefix twice but emits nothing twice
+    calls.clear()
+    out, st = port.stream_policy(fake_decode, np.zeros(100, dtype=np.int32))
+    assert calls == [60, 100, 100] and len(out) == 100 * 1764
+    # short utterance: single final decode
+    calls.clear()
+    out, st = port.stream_policy(fake_decode, np.zeros(7, dtype=np.int32))
+    assert calls == [7] and len(out) == 7 * 1764
