@@ -126,6 +126,18 @@ int64_t mio_stream_read(mio_stream * s, float * out, int64_t cap, int * is_last)
 /* counters mirroring StreamProfile (src/test-to-speech.h:28-38): decode_calls, decoded_codes, emitted_samples */
 int  mio_stream_stats(const mio_stream * s, int64_t * decode_calls, int64_t * decoded_codes, int64_t * emitted_samples);
 
+/* ---- pinned host buffers (cudaMallocHost) so callers can hand the library transfer-friendly memory */
+void * mio_host_alloc(size_t bytes);
+void   mio_host_free(void * p);
+
+/* ---- per-kernel-category device timing: CUDA events are recorded around every launch while enabled;
+ * totals accumulate over mio_batch_run calls until the next mio_profile_enable.  Read after mio_batch_sync. */
+int  mio_profile_enable(mio_ctx * ctx, int on);
+int  mio_profile_categories(void);
+const char * mio_profile_name(int cat);
+int  mio_profile_read(mio_ctx * ctx, int cat, double * ms, double * flops, double * bytes, int64_t * launches);
+int64_t mio_batch_h2d_bytes(const mio_ctx * ctx);         /* bytes copied host->device by the last upload */
+
 /* ---- introspection for parity tests: copy a named intermediate of the LAST decode to the host.
  * Returns number of floats written or <0.  Names: see csrc/decode.cu (e.g. "prenet_out", "spec"). */
 int64_t mio_debug_read(mio_ctx * ctx, const char * name, float * out, int64_t cap);

@@ -260,6 +260,38 @@ int mio_stream_stats(const mio_stream * s, int64_t * dc, int64_t * codes, int64_
     return MIO_OK;
 }
 
+// ---- pinned host memory for callers that want asynchronous / full-rate PCIe transfers
+void * mio_host_alloc(size_t bytes) {
+    void * p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { g_err = "cudaMallocHost failed"; return nullptr; }
+    return p;
+}
+void mio_host_free(void * p) { if (p) cudaFreeHost(p); }
+
+// ---- per-category device timings accumulated since the last reset (CUDA events around every launch)
+int mio_profile_enable(mio_ctx * c, int on) {
+    if (!c) return fail(MIO_ERR_ARG, "bad argument");
+    c->E.profiling = on != 0;
+    for (auto & t : c->E.prof_tot) t = prof_total();
+    return MIO_OK;
+}
+int mio_profile_categories(void) { return CAT_COUNT; }
+const char * mio_profile_name(int cat) {
+    static const char * names[CAT_COUNT] = {"gemm_split3", "gemm_f16", "attention", "layernorm", "gn_stats", "gn_apply",
+                                            "split", "gather", "cond", "istft", "peak"};
+    return (cat >= 0 && cat < CAT_COUNT) ? names[cat] : "";
+}
+int mio_profile_read(mio_ctx * c, int cat, double * ms, double * flops, double * bytes, int64_t * launches) {
+    if (!c || cat < 0 || cat >= CAT_COUNT) return fail(MIO_ERR_ARG, "bad argument");
+    const prof_total & t = c->E.prof_tot[cat];
+    if (ms) *ms = t.ms;
+    if (flops) *flops = t.flops;
+    if (bytes) *bytes = t.bytes;
+    if (launches) *launches = t.launches;
+    return MIO_OK;
+}
+int64_t mio_batch_h2d_bytes(const mio_ctx * c) { return c ? (int64_t) c->E.h2d_bytes : 0; }
+
 int64_t mio_debug_read(mio_ctx * c, const char * name, float * out, int64_t cap) {
     if (!c || !name) return fail(MIO_ERR_ARG, "bad argument");
     auto it = c->E.snaps.find(name);

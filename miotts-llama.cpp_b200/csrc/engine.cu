@@ -532,7 +532,13 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
             if (rows + T + 1 > max_rows1 || (u - c.utt0) >= max_utts) break;
             lay.start.push_back(rows); lay.len.push_back(T); lay.voice.push_back(voice_ids[u]);
             lay.out_off.push_back((int64_t) cu[u] * hp.samples_per_token);
-            for (int i = 0; i < T; i++) { lay.codes_padded.push_back(codes[cu[u] + i]); lay.row_utt.push_back(u - c.utt0); }
+            for (int i = 0; i < T; i++) {
+                const int32_t code = codes[cu[u] + i];
+                if (code < 0 || code >= hp.vocab)   // the reference aborts in GGML_ASSERT (ggml-cpu/ops.cpp:4811)
+                    return "RANGE: code " + std::to_string(code) + " at position " + std::to_string(i) + " of utterance " +
+                           std::to_string(u) + " is outside [0, " + std::to_string(hp.vocab) + ")";
+                lay.codes_padded.push_back(code); lay.row_utt.push_back(u - c.utt0);
+            }
             lay.codes_padded.push_back(-1); lay.row_utt.push_back(-1);
             rows += T + 1;
             blocks += (T * fpc + ISTFT_SEG_PER_BLOCK - 1) / ISTFT_SEG_PER_BLOCK;
@@ -636,16 +642,51 @@ cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_pa
     p.b_hi = W.hi; p.b_lo = W.lo;
     if (A.K != W.K) return cudaErrorInvalidValue;
     launches++;
-    if (use_simt) return launch_gemm_simt(p, stream);
-    return launch_gemm_tc(p, A.tm_hi, A.tm_lo, W.tm_hi, W.tm_lo, W.box_n, stream);
+    prof_begin(W.npass == 3 ? CAT_GEMM_SPLIT : CAT_GEMM_F16, 2.0 * M * (double) W.N * W.K * W.taps, 0.0);
+    cudaError_t ce = use_simt ? launch_gemm_simt(p, stream)
+                              : launch_gemm_tc(p, A.tm_hi, A.tm_lo, W.tm_hi, W.tm_lo, W.box_n, stream);
+    prof_end();
+    return ce;
+}
+
+// ---------------------------------------------------------------------------------------------
+// per-category device timing (CUDA events on the launching stream), used by bench.py for the roofline lines
+// ---------------------------------------------------------------------------------------------
+void engine::prof_begin(int cat, double flops, double bytes) {
+    if (!profiling) return;
+    if (prof_used + 2 > prof_events.size()) {
+        const size_t old = prof_events.size();
+        prof_events.resize(old + 256);
+        for (size_t i = old; i < prof_events.size(); i++) cudaEventCreate(&prof_events[i]);
+    }
+    prof_rec r; r.cat = cat; r.flops = flops; r.bytes = bytes; r.ev = prof_used;
+    prof_recs.push_back(r);
+    cudaEventRecord(prof_events[prof_used], stream);
+    prof_used += 2;
+}
+void engine::prof_end() {
+    if (!profiling) return;
+    cudaEventRecord(prof_events[prof_recs.back().ev + 1], stream);
+}
+void engine::prof_collect() {
+    // call after the stream has been synchronised
+    for (const prof_rec & r : prof_recs) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, prof_events[r.ev], prof_events[r.ev + 1]) != cudaSuccess) continue;
+        prof_tot[r.cat].ms += ms; prof_tot[r.cat].flops += r.flops; prof_tot[r.cat].bytes += r.bytes; prof_tot[r.cat].launches++;
+    }
+    prof_recs.clear();
+    prof_used = 0;
 }
 
 // ---------------------------------------------------------------------------------------------
 // the decoder forward of one chunk + ISTFT (stage numbers follow src/miocodec.cpp:598-740)
 // ---------------------------------------------------------------------------------------------
-#define CKR(expr)                                                                                      \
+#define CKR(cat, bytes, expr)                                                                          \
     do {                                                                                               \
+        prof_begin(cat, 0.0, bytes);                                                                   \
         cudaError_t _e = (expr);                                                                       \
+        prof_end();                                                                                    \
         launches++;                                                                                    \
         if (_e != cudaSuccess) return std::string(#expr) + ": " + cudaGetErrorString(_e);              \
     } while (0)
@@ -664,13 +705,13 @@ std::string engine::run_resblock(const resblock_w & R, float * x, float * y, con
     if (gn_slot > GN_SLOTS) return "internal: GroupNorm slot overflow";
     gemm_params p;
     // GN -> SiLU -> conv1 + bias
-    CKR(launch_gn_stats(x, rows, C, rm, row_div, st1, stream));
-    CKR(launch_gn_apply_silu(x, rows, C, rm, row_div, st1, hp.gn_eps, R.n1w, R.n1b, vc.hi, stream));
+    CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(x, rows, C, rm, row_div, st1, stream));
+    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(x, rows, C, rm, row_div, st1, hp.gn_eps, R.n1w, R.n1b, vc.hi, stream));
     p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = y; p.ld_out = C; p.bias = R.c1b;
     CKG(gemm(R.c1, vc, rows, p));
     // GN -> SiLU -> conv2 + bias + residual
-    CKR(launch_gn_stats(y, rows, C, rm, row_div, st2, stream));
-    CKR(launch_gn_apply_silu(y, rows, C, rm, row_div, st2, hp.gn_eps, R.n2w, R.n2b, vc.hi, stream));
+    CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(y, rows, C, rm, row_div, st2, stream));
+    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(y, rows, C, rm, row_div, st2, hp.gn_eps, R.n2w, R.n2b, vc.hi, stream));
     p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x; p.ld_out = C; p.bias = R.c2b;
     CKG(gemm(R.c2, vc, rows, p));
     return {};
@@ -687,21 +728,21 @@ std::string engine::run_chunk(const chunk_info & c) {
     int gn_slot = 0;
 
     // 1. token gather
-    CKR(launch_gather(w.token_embd, d_codes + c.row0, x768, R1, D, hp.vocab, err_flag, stream));
+    CKR(CAT_GATHER, (double) (R1) * (4.0 + 8.0 * (D)), launch_gather(w.token_embd, d_codes + c.row0, x768, R1, D, hp.vocab, err_flag, stream));
     snap_f32("embed", x768, (size_t) R1 * D);
     // 2. prenet
     for (int i = 0; i < hp.prenet_layers; i++) {
         const prenet_layer_w & l = w.prenet[i];
-        CKR(launch_layernorm(x768, R1, D, hp.norm_eps, l.an_w, l.an_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
+        CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.an_w, l.an_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
         p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = qkv; p.ld_out = 3 * D;
         CKG(gemm(l.qkv, vA768, R1, p));
         if (i == 0) snap_f32("pre0_qkv", qkv, (size_t) R1 * 3 * D);
-        CKR(launch_attention(qkv, R1, D, hp.prenet_heads, hp.prenet_window, w.rope_pre, w.rope_max_pos, rm, 1, vA768.hi, vA768.lo, stream));
+        CKR(CAT_ATTN, (double) (R1) * 16.0 * (D), launch_attention(qkv, R1, D, hp.prenet_heads, hp.prenet_window, w.rope_pre, w.rope_max_pos, rm, 1, vA768.hi, vA768.lo, stream));
         if (i == 0) snap_f16("pre0_attn", vA768.hi, vA768.lo, (size_t) R1 * D);
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
         CKG(gemm(l.wo, vA768, R1, p));
         if (i == 0) snap_f32("pre0_x_attn", x768, (size_t) R1 * D);
-        CKR(launch_layernorm(x768, R1, D, hp.norm_eps, l.fn_w, l.fn_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
+        CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.fn_w, l.fn_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
         p = gemm_params(); p.epi = EPI_SWIGLU; p.out_hi = vFF2048.hi; p.out_lo = vFF2048.lo; p.ld_h = hp.prenet_ff;
         CKG(gemm(l.gu, vA768, R1, p));
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
@@ -709,7 +750,7 @@ std::string engine::run_chunk(const chunk_info & c) {
         if (i == 0) snap_f32("pre0_out", x768, (size_t) R1 * D);
     }
     snap_f32("prenet_x", x768, (size_t) R1 * D);
-    CKR(launch_layernorm(x768, R1, D, hp.norm_eps, w.pre_norm_w, w.pre_norm_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
+    CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, w.pre_norm_w, w.pre_norm_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
     // 2b. 768 -> 512 (+bias) written straight as the split operand of the ConvTranspose GEMM
     p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = vA512.hi; p.out_lo = vA512.lo; p.ld_h = C; p.bias = w.pre_out_b;
     // the prenet LN output lives in aA viewed as [R1][768]; the 512-wide result must not overwrite it while other
@@ -733,14 +774,14 @@ std::string engine::run_chunk(const chunk_info & c) {
     for (int i = 0; i < hp.dec_layers; i++) {
         const dec_layer_w & l = w.dec[i];
         const int oa = (i * 2 + 0) * 3 * C, of = (i * 2 + 1) * 3 * C;     // shift | scale | gate
-        CKR(launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, oa, oa + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream));
+        CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, oa, oa + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream));
         p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = qkv; p.ld_out = 3 * C;
         CKG(gemm(l.qkv, vA512, R2, p));
-        CKR(launch_attention(qkv, R2, C, hp.dec_heads, hp.dec_window, w.rope_pre, w.rope_max_pos, rm, 2, vA512.hi, vA512.lo, stream));
+        CKR(CAT_ATTN, (double) (R2) * 16.0 * (C), launch_attention(qkv, R2, C, hp.dec_heads, hp.dec_window, w.rope_pre, w.rope_max_pos, rm, 2, vA512.hi, vA512.lo, stream));
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x512; p.ld_out = C;
         p.gate = mod + oa + 2 * C; p.gate_ld = w.cond_rows; p.row_utt = rm.row_utt; p.row_div = 2; p.gate_voice = rm.voice;
         CKG(gemm(l.wo, vA512, R2, p));
-        CKR(launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, of, of + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream));
+        CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, of, of + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream));
         p = gemm_params(); p.epi = EPI_SWIGLU; p.out_hi = vFF1536.hi; p.out_lo = vFF1536.lo; p.ld_h = hp.dec_ff;
         CKG(gemm(l.gu, vA512, R2, p));
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x512; p.ld_out = C;
@@ -752,7 +793,7 @@ std::string engine::run_chunk(const chunk_info & c) {
     // 6. final AdaLN (shift, scale only) -> fp32 in place
     {
         const int on = hp.dec_layers * 2 * 3 * C;
-        CKR(launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, on, on + C, rm, 2, nullptr, nullptr, x512, stream));
+        CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, on, on + C, rm, 2, nullptr, nullptr, x512, stream));
     }
     snap_f32("final_norm", x512, (size_t) R2 * C);
     // 7. post resnet blocks
@@ -760,7 +801,7 @@ std::string engine::run_chunk(const chunk_info & c) {
         if (!(e = run_resblock(w.post[b], x512, y512, vC512, R2, 2, gn_slot)).empty()) return e;
     snap_f32("post", x512, (size_t) R2 * C);
     // 8. upsampler stage 0: ConvT(512->256, k9 s3) + bias + trim + Snake, then resblock
-    CKR(launch_split(x512, R2, C, rm, 2, vA512.hi, vA512.lo, stream));
+    CKR(CAT_SPLIT, (double) (R2) * 8.0 * (C), launch_split(x512, R2, C, rm, 2, vA512.hi, vA512.lo, stream));
     p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = x256; p.ld_out = 3 * 256; p.bias = w.upT_b[0]; p.bias_mod = 256;
     p.snake_ea = w.snake_ea[0]; p.snake_eb = w.snake_eb[0];
     CKG(gemm(w.upT[0], vA512, R2, p));
@@ -768,14 +809,14 @@ std::string engine::run_chunk(const chunk_info & c) {
     if (!(e = run_resblock(w.up_res[0], x256, y256, vC256, R6, 6, gn_slot)).empty()) return e;
     snap_f32("up0", x256, (size_t) R6 * 256);
     //    stage 1: ConvT(256->128, k9 s3)
-    CKR(launch_split(x256, R6, 256, rm, 6, vFF256.hi, vFF256.lo, stream));
+    CKR(CAT_SPLIT, (double) (R6) * 8.0 * (256), launch_split(x256, R6, 256, rm, 6, vFF256.hi, vFF256.lo, stream));
     p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = x128; p.ld_out = 3 * 128; p.bias = w.upT_b[1]; p.bias_mod = 128;
     p.snake_ea = w.snake_ea[1]; p.snake_eb = w.snake_eb[1];
     CKG(gemm(w.upT[1], vFF256, R6, p));
     if (!(e = run_resblock(w.up_res[1], x128, y128, vC128, R18, 18, gn_slot)).empty()) return e;
     snap_f32("up1", x128, (size_t) R18 * 128);
     // 8b. out_proj 128 -> 512 + bias + Snake -> split operand of the head
-    CKR(launch_split(x128, R18, 128, rm, 18, vFF128.hi, vFF128.lo, stream));
+    CKR(CAT_SPLIT, (double) (R18) * 8.0 * (128), launch_split(x128, R18, 128, rm, 18, vFF128.hi, vFF128.lo, stream));
     p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = vH512.hi; p.out_lo = vH512.lo; p.ld_h = 512; p.bias = w.out_proj_b;
     p.snake_ea = w.out_snake_ea; p.snake_eb = w.out_snake_eb;
     CKG(gemm(w.out_proj, vFF128, R18, p));
@@ -794,7 +835,9 @@ std::string engine::run_istft(const chunk_info & c, const float * spec_dev) {
     ip.start = d_start + c.utt0; ip.len = d_len + c.utt0; ip.out_off = d_out_off + c.utt0;
     ip.chunk_cu = d_chunk_cu + c.cu0; ip.hann = w.hann;
     ip.n_utts = c.n_utts; ip.frames_per_code = hp.frames_per_code; ip.total_chunks = c.istft_blocks;
-    CKR(launch_istft(ip, stream));
+    double istft_bytes = 0.0;   // 394*4 read + 98*4 written per frame
+    for (int u = 0; u < c.n_utts; u++) istft_bytes += (double) lay.len[c.utt0 + u] * hp.frames_per_code * 1968.0;
+    CKR(CAT_ISTFT, istft_bytes, launch_istft(ip, stream));
     return {};
 }
 
@@ -814,14 +857,14 @@ std::string engine::run(bool peak_normalize) {
     launches = 0;
     snaps.clear();
     // AdaLN conditioning vectors of every voice of the batch (compute_adaln3, src/miocodec.cpp:310-319)
-    if (lay.n_utts > 0) CKR(launch_cond(d_voice_table, n_voices, hp.adaln_dim, w.cond_w, w.cond_b, w.cond_rows, mod, stream));
+    if (lay.n_utts > 0) CKR(CAT_COND, 0.0, launch_cond(d_voice_table, n_voices, hp.adaln_dim, w.cond_w, w.cond_b, w.cond_rows, mod, stream));
     for (const chunk_info & c : chunks) {
         std::string e = run_chunk(c);
         if (!e.empty()) return e;
     }
     if (peak_normalize && lay.n_utts > 0) {
         for (const chunk_info & c : chunks) {
-            CKR(launch_peak_normalize(d_wave, d_len + c.utt0, d_out_off + c.utt0, c.n_utts, hp.samples_per_token, peak, stream));
+            CKR(CAT_PEAK, (double) wave_samples * 12.0, launch_peak_normalize(d_wave, d_len + c.utt0, d_out_off + c.utt0, c.n_utts, hp.samples_per_token, peak, stream));
             launches++;   // two kernels
         }
     }
@@ -832,6 +875,7 @@ std::string engine::run(bool peak_normalize) {
 std::string engine::sync() {
     CK(cudaSetDevice(device));
     CK(cudaStreamSynchronize(stream));
+    if (profiling) prof_collect();
     int flag = 0;
     CK(cudaMemcpy(&flag, err_flag, sizeof(int), cudaMemcpyDeviceToHost));
     if (flag != 0) {
@@ -898,8 +942,9 @@ std::string engine::run_istft_only(const float * spec_host, int n_frames) {
     istft_params ip;
     ip.spec = spec; ip.wave = d_wave; ip.start = d_start; ip.len = d_len; ip.out_off = d_out_off; ip.chunk_cu = d_chunk_cu;
     ip.hann = w.hann; ip.n_utts = 1; ip.frames_per_code = 1; ip.total_chunks = blocks;
+    const double istft_bytes = (double) n_frames * 1968.0;
     launches = 0;
-    CKR(launch_istft(ip, stream));
+    CKR(CAT_ISTFT, istft_bytes, launch_istft(ip, stream));
     lay = batch_layout();
     batch_ran = true;
     return {};

@@ -17,6 +17,11 @@ struct a_view {                  // an fp16 operand buffer viewed as [rows][K] w
     CUtensorMap tm_hi, tm_lo;
 };
 
+enum prof_cat : int { CAT_GEMM_SPLIT = 0, CAT_GEMM_F16, CAT_ATTN, CAT_LN, CAT_GN_STATS, CAT_GN_APPLY, CAT_SPLIT, CAT_GATHER,
+                      CAT_COND, CAT_ISTFT, CAT_PEAK, CAT_COUNT };
+struct prof_rec { int cat; double flops, bytes; size_t ev; };
+struct prof_total { double ms = 0, flops = 0, bytes = 0; int64_t launches = 0; };
+
 struct chunk_info {              // a run of whole utterances that fits the workspace
     int utt0 = 0, n_utts = 0;    // utterance range
     int row0 = 0, rows1 = 0;     // rows (code resolution) in the concatenated device arrays
@@ -89,6 +94,14 @@ struct engine {
     std::string run_istft(const chunk_info & c, const float * spec_dev);
     std::string view512_ff(a_view & v);
     cudaError_t gemm(const gemm_weight & W, const a_view & A, int M, gemm_params p);
+    // profiling
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_events; size_t prof_used = 0;
+    std::vector<prof_rec> prof_recs;
+    prof_total prof_tot[CAT_COUNT];
+    void prof_begin(int cat, double flops, double bytes);
+    void prof_end();
+    void prof_collect();
     void snap_f32(const char * name, const float * d, size_t n);
     void snap_f16(const char * name, const __half * hi, const __half * lo, size_t n);
 };

@@ -25,7 +25,8 @@ EXPORTS = [
     "mio_decode_wave_batch", "mio_batch_upload", "mio_batch_run", "mio_batch_fetch", "mio_batch_sync",
     "mio_batch_kernel_launches", "mio_batch_wave_device", "mio_stream_default_config", "mio_stream_open",
     "mio_stream_close", "mio_stream_push_codes", "mio_stream_finish", "mio_streams_step", "mio_stream_read",
-    "mio_stream_stats", "mio_debug_read", "mio_last_error", "mio_version",
+    "mio_stream_stats", "mio_debug_read", "mio_last_error", "mio_version", "mio_host_alloc", "mio_host_free",
+    "mio_profile_enable", "mio_profile_categories", "mio_profile_name", "mio_profile_read", "mio_batch_h2d_bytes",
 ]
 
 
@@ -86,10 +87,33 @@ def lib() -> C.CDLL:
     L.mio_stream_read.argtypes = [vp, f32p, i64, C.POINTER(C.c_int)]
     L.mio_stream_read.restype = i64
     L.mio_stream_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
+    L.mio_host_alloc.argtypes = [C.c_size_t]
+    L.mio_host_alloc.restype = vp
+    L.mio_host_free.argtypes = [vp]
+    L.mio_host_free.restype = None
+    L.mio_profile_enable.argtypes = [vp, C.c_int]
+    L.mio_profile_name.argtypes = [C.c_int]
+    L.mio_profile_name.restype = C.c_char_p
+    L.mio_profile_read.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(i64)]
+    L.mio_batch_h2d_bytes.argtypes = [vp]
+    L.mio_batch_h2d_bytes.restype = i64
     L.mio_debug_read.argtypes = [vp, C.c_char_p, f32p, i64]
     L.mio_debug_read.restype = i64
     _lib = L
     return L
+
+
+def pinned_empty(n: int, dtype) -> np.ndarray:
+    """numpy array over cudaMallocHost memory (freed when the array is collected)."""
+    dt = np.dtype(dtype)
+    ptr = lib().mio_host_alloc(max(1, n * dt.itemsize))
+    if not ptr:
+        raise MioError(MIO_ERR_CUDA, "cudaMallocHost failed")
+    buf = (C.c_char * (n * dt.itemsize)).from_address(ptr)
+    arr = np.frombuffer(buf, dtype=dt, count=n)
+    import weakref
+    weakref.finalize(buf, lib().mio_host_free, C.c_void_p(ptr))
+    return arr
 
 
 def _check(rc: int):
@@ -204,6 +228,20 @@ class MioCodec:
         _check(lib().mio_decode_wave_batch(self._h, c.ctypes.data, cu.ctypes.data, len(cu) - 1, vt.ctypes.data, vt.shape[0],
                                            vi.ctypes.data, int(peak_normalize), out.ctypes.data, out.size))
         return out
+
+    def profile_enable(self, on: bool = True):
+        _check(lib().mio_profile_enable(self._h, int(on)))
+
+    def profile_read(self) -> dict:
+        out = {}
+        for cat in range(lib().mio_profile_categories()):
+            ms, fl, by, n = C.c_double(0), C.c_double(0), C.c_double(0), C.c_int64(0)
+            _check(lib().mio_profile_read(self._h, cat, C.byref(ms), C.byref(fl), C.byref(by), C.byref(n)))
+            out[lib().mio_profile_name(cat).decode()] = dict(ms=ms.value, flops=fl.value, bytes=by.value, launches=n.value)
+        return out
+
+    def h2d_bytes(self) -> int:
+        return int(lib().mio_batch_h2d_bytes(self._h))
 
     def debug_read(self, name: str) -> np.ndarray:
         n = lib().mio_debug_read(self._h, name.encode(), None, 0)

@@ -1,0 +1,221 @@
+"""GPU parity tests: every call goes through the C ABI (miocodec_b200.binding -> libmiocodec_b200.so) and is
+compared with the oracle: golden vectors produced by the unmodified reference, the compiled reference itself when
+oracle/_ref loads on this host, and the torch restatement (oracle/port.py) for per-stage checks.
+
+Tolerances (DESIGN.md "parity floor"): the reference rounds conv1d operands to FP16 (ggml.c:4416), which makes its
+output discontinuous in fp32 round-off; an exact (fp64) evaluation of the same graph only reaches ~59-60 dB SNR /
+~2e-3 max-abs against it.  Stages before the first conv1d and the ISTFT are continuous and are held to
+>= 90 dB; the end-to-end waveform is held to >= 55 dB and to within 3 dB of what the fp32 port reaches.
+Frame counts, sample counts and indexing are exact."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import load_golden, snr_db
+
+pytestmark = pytest.mark.gpu
+
+WAVE_SNR_MIN = 55.0
+WAVE_MAXABS_REL = 5e-3
+
+
+def _voice(v):
+    from miocodec_b200 import synth
+    return synth.synth_voice(v)
+
+
+@pytest.mark.parametrize("case", ["ref20", "rand33", "one"])
+def test_wave_and_spec_match_reference_golden(codec, weights, case):
+    from oracle import port
+    g = load_golden(case)
+    codes, emb = g["codes"], _voice(int(g["voice"]))
+    spec = codec.decode(codes, emb)                                   # miocodec_decode
+    assert spec.shape == g["spec"].shape == (18 * len(codes), 394)    # exact frame indexing
+    wave = codec.istft(spec)                                          # istft
+    assert wave.shape == g["wave"].shape == (1764 * len(codes),)
+    fused = codec.decode_wave(codes, emb)                             # decode_codes_to_audio
+    assert fused.shape == wave.shape
+    assert snr_db(fused, wave) > 60.0                                 # same kernels, only GN atomics order differs
+    hp, W = weights
+    floor = snr_db(port.istft(port.decode(W, hp, codes, emb)), g["wave"])
+    s = snr_db(wave, g["wave"])
+    print(f"{case}: wave SNR {s:.1f} dB (fp32 port reaches {floor:.1f} dB), spec SNR {snr_db(spec, g['spec']):.1f} dB")
+    assert s > WAVE_SNR_MIN and s > floor - 3.0
+    assert np.abs(wave - g["wave"]).max() < WAVE_MAXABS_REL * max(1.0, np.abs(g["wave"]).max())
+    assert snr_db(spec, g["spec"]) > WAVE_SNR_MIN
+
+
+def test_istft_matches_reference_golden(codec):
+    for case in ("istft50", "ref20", "one"):
+        g = load_golden(case)
+        wave = codec.istft(g["spec"])
+        assert wave.shape == g["wave"].shape
+        # the reference's DFT tables are built from f32 angles (src/istft.cpp:19-25, error ~6e-5 rad at k*n ~ 7e4),
+        # an exact FFT therefore differs from it at the 1e-5 level
+        assert snr_db(wave, g["wave"]) > 88.0
+        assert np.abs(wave - g["wave"]).max() < 3e-5 * max(1.0, np.abs(g["wave"]).max())
+
+
+def test_istft_is_linear_at_full_size(codec):
+    """Size-independent property at BASELINE config C2 size (12600 frames = 700 codes)."""
+    rng = np.random.default_rng(0)
+    X = rng.standard_normal((12600, 394)).astype(np.float32)
+    Y = rng.standard_normal((12600, 394)).astype(np.float32)
+    wx, wy = codec.istft(X), codec.istft(Y)
+    assert wx.shape == (12600 * 98,)
+    wz = codec.istft((0.5 * X - 2.0 * Y).astype(np.float32))
+    assert np.abs(wz - (0.5 * wx - 2.0 * wy)).max() < 2e-5
+    # frame locality: changing frame t only changes samples [98 t - 147, 98 t + 245)
+    X2 = X.copy(); X2[6000] += 1.0
+    d = np.nonzero(codec.istft(X2) != wx)[0]
+    assert d.min() >= 98 * 6000 - 147 and d.max() < 98 * 6000 + 245
+
+
+@pytest.mark.parametrize("mode", ["tc", "simt"])
+def test_stages_before_first_conv_are_fp32_accurate(assets, weights, mode):
+    from miocodec_b200 import binding, synth
+    from oracle import port
+    hp, W = weights
+    codes, emb = synth.REFERENCE_TEST_CODES, _voice(0)
+    _, inter = port.decode(W, hp, codes, emb, want_inter=True)
+    c = binding.MioCodec(assets[0], 0, gemm=mode)
+    c.set_option("debug_snapshots", "1")
+    c.decode_wave(codes, emb)
+    T = len(codes)
+    lim = {"tc": 90.0, "simt": 105.0}[mode]
+    for name, r in [("embed", 1), ("pre0_qkv", 1), ("pre0_attn", 1), ("pre0_out", 1), ("prenet_out", 1), ("upsample", 2)]:
+        got = c.debug_read(name).reshape(-1, inter[name].shape[1])[: T * r]
+        s = snr_db(got, inter[name])
+        print(f"{mode} {name}: {s:.1f} dB")
+        assert s > lim, (name, s)
+    # after the convs the reference's own fp16 rounding dominates
+    for name, r in [("prior", 2), ("decoder_x", 2), ("post", 2), ("up0", 6), ("up1", 18), ("spec", 18)]:
+        ref = inter[name] if name != "spec" else port.decode(W, hp, codes, emb)
+        got = c.debug_read(name).reshape(-1, ref.shape[1])[: T * r]
+        assert np.isfinite(got).all()
+        assert snr_db(got, ref) > 54.0, name
+    c.close()
+
+
+def test_batch_ragged_equals_single(codec):
+    from miocodec_b200 import synth
+    lens = [1, 7, 33, 64, 100, 2, 129]
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    codes = synth.synth_codes(int(cu[-1]), 21)
+    vt = np.stack([_voice(v) for v in range(4)])
+    vids = np.array([0, 1, 2, 3, 0, 1, 2], dtype=np.int32)
+    out = codec.decode_wave_batch(codes, cu, vt, vids)
+    assert out.shape == (1764 * int(cu[-1]),)
+    for b, n in enumerate(lens):
+        single = codec.decode_wave(codes[cu[b]:cu[b + 1]], vt[vids[b]])
+        got = out[1764 * cu[b]: 1764 * cu[b + 1]]
+        assert got.shape == single.shape
+        assert snr_db(got, single) > 60.0, (b, n, snr_db(got, single))
+    # permutation invariance: utterances are independent
+    perm = [3, 0, 6, 2, 5, 1, 4]
+    cu2 = np.concatenate([[0], np.cumsum([lens[p] for p in perm])]).astype(np.int32)
+    codes2 = np.concatenate([codes[cu[p]:cu[p + 1]] for p in perm])
+    out2 = codec.decode_wave_batch(codes2, cu2, vt, vids[perm])
+    for j, p in enumerate(perm):
+        assert snr_db(out2[1764 * cu2[j]: 1764 * cu2[j + 1]], out[1764 * cu[p]: 1764 * cu[p + 1]]) > 60.0
+
+
+def test_multi_chunk_batches(assets, codec):
+    """A batch larger than the workspace is split into chunks of whole utterances."""
+    from miocodec_b200 import binding, synth
+    small = binding.MioCodec(assets[0], 0, max_chunk_codes=128)
+    lens = [60, 50, 100, 10, 90, 40]
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    codes = synth.synth_codes(int(cu[-1]), 33)
+    vt = np.stack([_voice(v) for v in range(2)])
+    vids = np.array([0, 1, 0, 1, 0, 1], dtype=np.int32)
+    a = small.decode_wave_batch(codes, cu, vt, vids)
+    b = codec.decode_wave_batch(codes, cu, vt, vids)
+    assert snr_db(a, b) > 60.0
+    with pytest.raises(binding.MioError) as ei:
+        small.decode_wave(synth.synth_codes(400, 1), vt[0])          # one utterance larger than the workspace
+    assert ei.value.code == binding.MIO_ERR_ARG
+    small.close()
+
+
+def test_edge_cases_and_errors(codec):
+    from miocodec_b200 import binding, synth
+    emb = _voice(0)
+    assert codec.decode_wave(np.zeros(0, dtype=np.int32), emb).shape == (0,)      # decode_codes_to_audio: empty, true
+    bad = synth.synth_codes(10, 3)
+    bad[4] = codec.vocab                                                          # reference: GGML_ASSERT abort
+    with pytest.raises(binding.MioError) as ei:
+        codec.decode_wave(bad, emb)
+    assert ei.value.code == binding.MIO_ERR_RANGE
+    bad[4] = -7
+    with pytest.raises(binding.MioError):
+        codec.decode_wave(bad, emb)
+    # the context stays usable after an error
+    w = codec.decode_wave(synth.synth_codes(5, 4), emb, peak_normalize=True)
+    assert abs(np.abs(w).max() - 0.95) < 1e-5                                     # 0.95 / max|s| (test-to-speech.cpp:289-300)
+    # boundary codes 0 and vocab-1 decode
+    w = codec.decode_wave(np.array([0, codec.vocab - 1, 0], dtype=np.int32), emb)
+    assert np.isfinite(w).all() and w.shape == (3 * 1764,)
+    # accessors
+    assert (codec.sample_rate, codec.n_fft, codec.hop_length, codec.samples_per_token, codec.frames_per_code) == (44100, 392, 98, 1764, 18)
+
+
+def test_simt_and_tensor_core_paths_agree(assets, codec):
+    from miocodec_b200 import binding, synth
+    codes, emb = synth.synth_codes(50, 8), _voice(2)
+    simt = binding.MioCodec(assets[0], 0, gemm="simt")
+    a, b = simt.decode_wave(codes, emb), codec.decode_wave(codes, emb)
+    assert snr_db(b, a) > WAVE_SNR_MIN
+    simt.close()
+
+
+def test_c2_full_size_against_live_reference(assets, codec):
+    """BASELINE config C2: one 700-code utterance; compared with the compiled reference when it loads here."""
+    from miocodec_b200 import synth
+    from oracle import ref
+    codes, emb = synth.synth_codes(700, 1234), _voice(0)
+    wave = codec.decode_wave(codes, emb)
+    assert wave.shape == (700 * 1764,) and np.isfinite(wave).all()
+    if not ref.available():
+        pytest.skip("oracle/_ref does not load on this host")
+    R = ref.Reference(assets[0])
+    w_ref = R.decode_wave(codes, emb)
+    R.close()
+    assert w_ref.shape == wave.shape
+    s = snr_db(wave, w_ref)
+    print(f"C2 T=700: SNR {s:.1f} dB, max-abs {np.abs(wave - w_ref).max():.2e}, peak {np.abs(w_ref).max():.2f}")
+    assert s > WAVE_SNR_MIN
+    assert np.abs(wave - w_ref).max() < WAVE_MAXABS_REL * max(1.0, np.abs(w_ref).max()) * 2
+
+
+def test_streaming_matches_reference_policy(codec):
+    """Streams fed one code per tick (the reference emits one code per LLM token) against the restated policy of
+    src/test-to-speech.cpp:364-417, :499-571 driven by the same decoder."""
+    from miocodec_b200 import synth
+    from oracle import port
+    n_streams, N = 3, [230, 100, 47]
+    embs = [_voice(v) for v in range(n_streams)]
+    codes = [synth.synth_codes(n, 70 + i) for i, n in enumerate(N)]
+    streams = [codec.open_stream(e) for e in embs]
+    got = [[] for _ in streams]
+    for tick in range(max(N)):
+        for i, s in enumerate(streams):
+            if tick < N[i]:
+                s.push(codes[i][tick])
+            if tick == N[i] - 1:
+                s.finish()
+        codec.step_streams(streams)
+        for i, s in enumerate(streams):
+            a, last = s.read()
+            got[i].append(a)
+    for i, s in enumerate(streams):
+        a, last = s.read()
+        assert last
+        out = np.concatenate(got[i] + [a])
+        ref_out, st = port.stream_policy(lambda c: codec.decode_wave(c, embs[i]), codes[i])
+        mine = s.stats()
+        assert mine == st, (mine, st)                                  # decode_calls / decoded_codes / emitted_samples exact
+        assert out.shape == ref_out.shape == (N[i] * 1764,)            # sample_diff == 0 (stream-compare.cpp:258-262)
+        assert snr_db(out, ref_out) > 58.0, snr_db(out, ref_out)
+        s.close()
