@@ -162,6 +162,10 @@ struct loader {
         std::string e = make_map(&W.tm_hi, W.hi, N, K * taps, W.box_n);
         if (e.empty() && W.lo) e = make_map(&W.tm_lo, W.lo, N, K * taps, W.box_n);
         if (e.empty() && !W.lo) W.tm_lo = W.tm_hi;
+        W.bn2 = (N % 256 == 0) ? 256 : 128;
+        if (e.empty()) e = make_map(&W.tm2_hi, W.hi, N, K * taps, W.bn2 / 2);
+        if (e.empty() && W.lo) e = make_map(&W.tm2_lo, W.lo, N, K * taps, W.bn2 / 2);
+        if (e.empty() && !W.lo) W.tm2_lo = W.tm2_hi;
         if (!e.empty()) { err = e; return false; }
         return true;
     }
@@ -643,8 +647,10 @@ cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_pa
     if (A.K != W.K) return cudaErrorInvalidValue;
     launches++;
     prof_begin(W.npass == 3 ? CAT_GEMM_SPLIT : CAT_GEMM_F16, 2.0 * M * (double) W.N * W.K * W.taps, 0.0);
-    cudaError_t ce = use_simt ? launch_gemm_simt(p, stream)
-                              : launch_gemm_tc(p, A.tm_hi, A.tm_lo, W.tm_hi, W.tm_lo, W.box_n, stream);
+    cudaError_t ce;
+    if (use_simt) ce = launch_gemm_simt(p, stream);
+    else if (gemm_gen == 2) ce = launch_gemm_tc2(p, A.tm_hi, A.tm_lo, W.tm2_hi, W.tm2_lo, W.bn2, stream);
+    else ce = launch_gemm_tc(p, A.tm_hi, A.tm_lo, W.tm_hi, W.tm_lo, W.box_n, stream);
     prof_end();
     return ce;
 }

@@ -36,6 +36,7 @@ struct engine {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     bool use_simt = false;
+    int gemm_gen = 2;                // 1: one CTA per tile; 2: persistent CTA pairs (cta_group::2, default)
     int max_rows1 = 16384 + 512;     // workspace rows at code resolution (codes + pad rows)
     bool ws_ready = false;
     bool debug_snap = false;

@@ -384,6 +384,263 @@ cudaError_t launch_gemm_tc(const gemm_params & p, const CUtensorMap & tmA_hi, co
 
 cudaError_t gemm_tc_init() { return cudaSuccess; }
 
+// =============================================================================================
+// Generation 2: persistent, CTA-pair (cta_group::2) tap-GEMM.
+//   * one cluster of 2 CTAs per SM pair, 74 clusters, static round-robin over 256 x BN output tiles
+//   * each CTA loads its 128 rows of A and HALF of the B tile (BN/2 rows): 64 KB per k-block instead of 96 KB for
+//     a 128x256 single-CTA tile -> fits 3 stages and cuts L2->SM operand traffic per MMA by a third
+//   * the leader CTA issues tcgen05.mma.cta_group::2 (M = 256); accumulators are double buffered in TMEM
+//     (2 x BN columns) so the epilogue of tile i overlaps the main loop of tile i+1
+// Barriers: full[s] lives in the leader (both CTAs' TMA loads complete_tx on it), empty[s] / tmem_full[b] are
+// multicast by tcgen05.commit to both CTAs, tmem_empty[b] lives in the leader and counts the 8 epilogue warps.
+// =============================================================================================
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(void * dst, const CUtensorMap * tm, uint32_t leader_bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(tm), "r"(leader_bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint64_t * bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t) 3)
+                 : "memory");
+}
+
+template <int BN, int NPASS>
+struct gemm2_cfg {
+    static constexpr int A_BYTES = 128 * BK * 2;                     // this CTA's 128 rows
+    static constexpr int B_BYTES = (BN / 2) * BK * 2;                // this CTA's half of the B tile
+    static constexpr int NOPS = (NPASS == 3) ? 2 : 1;
+    static constexpr int STAGE_BYTES = NOPS * (A_BYTES + B_BYTES);
+    static constexpr int STAGES = (196608 / STAGE_BYTES) > 8 ? 8 : (196608 / STAGE_BYTES);
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+    static constexpr uint32_t IDESC = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (256 >> 4) << 24);
+    static constexpr uint32_t TMEM_COLS = 2 * BN;                    // double-buffered accumulator
+};
+
+template <int BN, int NPASS, int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
+                const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
+                const gemm_params p) {
+    using cfg = gemm2_cfg<BN, NPASS>;
+    extern __shared__ uint8_t gemm_smem_raw[];
+    const uint32_t raw = smem_u32(gemm_smem_raw);
+    uint8_t * smem = gemm_smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    uint64_t * bars = (uint64_t *) (smem + cfg::STAGES * cfg::STAGE_BYTES);
+    uint64_t * full = bars;                               // [STAGES]   (used in the leader)
+    uint64_t * empty = bars + cfg::STAGES;                // [STAGES]   (both CTAs)
+    uint64_t * tmem_full = bars + 2 * cfg::STAGES;        // [2]        (both CTAs)
+    uint64_t * tmem_empty = bars + 2 * cfg::STAGES + 2;   // [2]        (used in the leader)
+    uint32_t * tmem_slot = (uint32_t *) (bars + 2 * cfg::STAGES + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+    const int tiles_n = (p.N + BN - 1) / BN, tiles_m = (p.M + 255) / 256;
+    const int num_tiles = tiles_n * tiles_m;
+    const int kb_per_tap = p.K / BK;
+    const int num_kb = p.taps * kb_per_tap;
+    const int shift0 = (p.taps == 3) ? -1 : 0;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA_hi);
+        tma_prefetch_desc(&tmB_hi);
+        if (NPASS == 3) { tma_prefetch_desc(&tmA_lo); tma_prefetch_desc(&tmB_lo); }
+        for (int s = 0; s < cfg::STAGES; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int b = 0; b < 2; b++) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(cfg::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs) =====
+        if (lane == 0) {
+            int it = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                const int tm = tile / tiles_n, tn = tile - tm * tiles_n;
+                const int m0 = tm * 256 + (int) rank * 128, n0 = tn * BN + (int) rank * (BN / 2);
+                for (int kb = 0; kb < num_kb; kb++, it++) {
+                    const int s = it % cfg::STAGES;
+                    const uint32_t ph = (uint32_t) (it / cfg::STAGES) & 1u;
+                    mbar_wait(&empty[s], ph ^ 1u);
+                    const uint32_t lbar = mapa_u32(smem_u32(&full[s]), 0);
+                    if (leader) mbar_expect_tx(&full[s], 2u * (uint32_t) cfg::STAGE_BYTES);
+                    uint8_t * st = smem + s * cfg::STAGE_BYTES;
+                    const int tap = kb / kb_per_tap, kk = kb - tap * kb_per_tap;
+                    const int arow = m0 + tap + shift0;
+                    tma_load_2d_pair(st, &tmA_hi, lbar, kk * BK, arow);
+                    if (NPASS == 3) tma_load_2d_pair(st + cfg::A_BYTES, &tmA_lo, lbar, kk * BK, arow);
+                    uint8_t * sb = st + cfg::NOPS * cfg::A_BYTES;
+                    tma_load_2d_pair(sb, &tmB_hi, lbar, kb * BK, n0);
+                    if (NPASS == 3) tma_load_2d_pair(sb + cfg::B_BYTES, &tmB_lo, lbar, kb * BK, n0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader CTA only) =====
+        if (leader && lane == 0) {
+            int it = 0, tile_iter = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, tile_iter++) {
+                const int b = tile_iter & 1;
+                const uint32_t aph = (uint32_t) (tile_iter >> 1) & 1u;
+                mbar_wait(&tmem_empty[b], aph ^ 1u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t d_tmem = tmem_base + (uint32_t) (b * BN);
+                for (int kb = 0; kb < num_kb; kb++, it++) {
+                    const int s = it % cfg::STAGES;
+                    const uint32_t ph = (uint32_t) (it / cfg::STAGES) & 1u;
+                    mbar_wait(&full[s], ph);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = smem_u32(smem + s * cfg::STAGE_BYTES);
+                    const uint32_t sb = sa + cfg::NOPS * cfg::A_BYTES;
+                    const uint64_t da_hi = umma_desc(sa), db_hi = umma_desc(sb);
+                    const uint64_t da_lo = umma_desc(sa + cfg::A_BYTES), db_lo = umma_desc(sb + cfg::B_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; k++) {
+                        const uint64_t adv = (uint64_t) (k * 2);
+                        umma_f16_pair(d_tmem, da_hi + adv, db_hi + adv, cfg::IDESC, (kb > 0 || k > 0) ? 1u : 0u);
+                        if (NPASS == 3) {
+                            umma_f16_pair(d_tmem, da_hi + adv, db_lo + adv, cfg::IDESC, 1u);
+                            umma_f16_pair(d_tmem, da_lo + adv, db_hi + adv, cfg::IDESC, 1u);
+                        }
+                    }
+                    umma_commit_pair(&empty[s]);
+                }
+                umma_commit_pair(&tmem_full[b]);
+            }
+        }
+    } else {
+        // ===== epilogue warps (both CTAs): TMEM lane group = warp % 4 =====
+        const int lg = warp & 3;
+        int tile_iter = 0;
+        for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, tile_iter++) {
+            const int tm = tile / tiles_n, tn = tile - tm * tiles_n;
+            const int b = tile_iter & 1;
+            const uint32_t aph = (uint32_t) (tile_iter >> 1) & 1u;
+            mbar_wait(&tmem_full[b], aph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int row = tm * 256 + (int) rank * 128 + lg * 32 + lane;
+            const int n0 = tn * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; c++) {
+                if (n0 + c * 32 >= p.N) break;
+                float v[32];
+                tmem_ld32(tmem_base + ((uint32_t) (lg * 32) << 16) + (uint32_t) (b * BN + c * 32), v);
+                if (row < p.M) gemm_epilogue<EPI, 32>(p, row, n0 + c * 32, v);
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive_remote(mapa_u32(smem_u32(&tmem_empty[b]), 0));
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(cfg::TMEM_COLS) : "memory");
+    }
+}
+
+static int g_num_sms = 0;
+
+template <int BN, int NPASS, int EPI>
+static cudaError_t launch_tc2_inst(const gemm_params & p, const CUtensorMap & a_hi, const CUtensorMap & a_lo,
+                                   const CUtensorMap & b_hi, const CUtensorMap & b_lo, cudaStream_t st) {
+    using cfg = gemm2_cfg<BN, NPASS>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc2_kernel<BN, NPASS, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    if (g_num_sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int tiles = ((p.N + BN - 1) / BN) * ((p.M + 255) / 256);
+    int clusters = g_num_sms / 2;
+    if (tiles < clusters) clusters = tiles;
+    gemm_tc2_kernel<BN, NPASS, EPI><<<2 * clusters, GEMM_THREADS, cfg::SMEM_BYTES, st>>>(a_hi, a_lo, b_hi, b_lo, p);
+    return cudaGetLastError();
+}
+
+template <int BN, int NPASS>
+static cudaError_t launch_tc2_epi(const gemm_params & p, const CUtensorMap & a_hi, const CUtensorMap & a_lo,
+                                  const CUtensorMap & b_hi, const CUtensorMap & b_lo, cudaStream_t st) {
+    switch (p.epi) {
+        case EPI_STORE: return launch_tc2_inst<BN, NPASS, EPI_STORE>(p, a_hi, a_lo, b_hi, b_lo, st);
+        case EPI_RESID: return launch_tc2_inst<BN, NPASS, EPI_RESID>(p, a_hi, a_lo, b_hi, b_lo, st);
+        default: break;
+    }
+    if constexpr (NPASS == 3) {
+        switch (p.epi) {
+            case EPI_SWIGLU: return launch_tc2_inst<BN, 3, EPI_SWIGLU>(p, a_hi, a_lo, b_hi, b_lo, st);
+            case EPI_SPLIT: return launch_tc2_inst<BN, 3, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, st);
+            case EPI_SNAKE: return launch_tc2_inst<BN, 3, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, st);
+            case EPI_HEAD: return launch_tc2_inst<BN, 3, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, st);
+            default: break;
+        }
+    }
+    return cudaErrorInvalidValue;
+}
+
+// tmB_*: box {64, bn/2}
+cudaError_t launch_gemm_tc2(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
+                            const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, int bn, cudaStream_t st) {
+    if (p.M <= 0) return cudaSuccess;
+    if (p.K % BK != 0 || (p.taps != 1 && p.taps != 3)) return cudaErrorInvalidValue;
+    if (bn == 256) {
+        if (p.npass == 3) return launch_tc2_epi<256, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, st);
+        return launch_tc2_epi<256, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, st);
+    }
+    if (bn == 128) {
+        if (p.npass == 3) return launch_tc2_epi<128, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, st);
+        return launch_tc2_epi<128, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
+
 // ---------------------------------------------------------------------------------------------
 // SIMT validation path: same operands, same epilogues, FP32 CUDA-core FMAs ((a_hi+a_lo)*(b_hi+b_lo) in full).
 // Selected with mio_ctx_set_option("gemm", "simt"); used by the parity tests to separate tensor-core plumbing

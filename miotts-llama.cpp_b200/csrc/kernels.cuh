@@ -39,6 +39,9 @@ struct gemm_params {
 // tcgen05 path. tmA_* : 2-D maps over [a_rows][K] fp16, box {64, 128}; tmB_*: over [N][taps*K], box {64, bn}.
 cudaError_t launch_gemm_tc(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
                            const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, int bn, cudaStream_t st);
+// generation 2: persistent CTA-pair kernel (cta_group::2, 256 x bn tiles). tmB_*: box {64, bn/2}
+cudaError_t launch_gemm_tc2(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
+                            const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, int bn, cudaStream_t st);
 cudaError_t launch_gemm_simt(const gemm_params & p, cudaStream_t st);
 cudaError_t gemm_tc_init();   // sets the dynamic shared memory attributes once
 

@@ -34,8 +34,10 @@ struct gemm_weight {
     float out_scale = 1.f;            // epilogue multiplier (inverse of the power-of-two weight pre-scale)
     __half * hi = nullptr;
     __half * lo = nullptr;
-    CUtensorMap tm_hi, tm_lo;         // box {64, BN}
+    CUtensorMap tm_hi, tm_lo;         // box {64, box_n}       (generation-1 kernel, one CTA per 128 x box_n tile)
     int box_n = 0;
+    CUtensorMap tm2_hi, tm2_lo;       // box {64, bn2 / 2}     (generation-2 kernel, CTA pair per 256 x bn2 tile)
+    int bn2 = 0;
 };
 
 struct resblock_w {
