@@ -38,6 +38,10 @@ typedef struct mio_stream mio_stream;
  * src/istft.cpp:7-32).  `device` is a CUDA ordinal. */
 int  mio_ctx_create(const char * gguf_path, int device, mio_ctx ** out_ctx);
 void mio_ctx_destroy(mio_ctx * ctx);
+/* A context that can only run mio_istft: replaces constructing an istft_cache (src/istft.h:6-30,
+ * src/istft.cpp:7-32) when no codec is loaded — the reference's istft() is a free function that needs no
+ * miocodec_context.  Geometry is the reference's fixed n_fft = win_length = 392, hop = 98. */
+int  mio_istft_ctx_create(int device, mio_ctx ** out_ctx);
 
 /* accessors: miocodec_sample_rate / n_fft / hop_length / samples_per_token (src/miocodec.h:34-37) */
 int  mio_ctx_sample_rate(const mio_ctx * ctx);

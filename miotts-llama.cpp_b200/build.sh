@@ -19,3 +19,9 @@ g++ -O2 -std=c++17 -fPIC -c "$SRC/gguf_reader.cpp" -o "$OBJ/gguf_reader.o"
 for p in "${pids[@]}"; do wait "$p"; done
 "$NVCC" -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT/libmiocodec_b200.so" "$OBJ"/gemm.o "$OBJ"/elementwise.o "$OBJ"/istft.o "$OBJ"/engine.o "$OBJ"/stream.o "$OBJ"/capi.o "$OBJ"/gguf_reader.o -cudart static
 echo "built $OUT/libmiocodec_b200.so"
+# C++ drop-in layer (reference-named entry points on top of the C ABI) + its test program
+g++ -O2 -std=c++17 -fPIC -shared -I"$HERE/shim" "$HERE/shim/miocodec_shim.cpp" -o "$OUT/libmiocodec_shim.so" \
+    -L"$OUT" -lmiocodec_b200 -Wl,-rpath,'$ORIGIN'
+g++ -O2 -std=c++17 -I"$HERE/shim" "$HERE/../tests/shim_demo.cpp" -o "$OUT/shim_demo" -L"$OUT" -lmiocodec_shim -lmiocodec_b200 \
+    -Wl,-rpath,'$ORIGIN'
+echo "built $OUT/libmiocodec_shim.so and $OUT/shim_demo"

@@ -64,6 +64,20 @@ int mio_ctx_create(const char * gguf_path, int device, mio_ctx ** out_ctx) {
     return MIO_OK;
 }
 
+int mio_istft_ctx_create(int device, mio_ctx ** out_ctx) {
+    if (!out_ctx) return fail(MIO_ERR_ARG, "bad argument");
+    *out_ctx = nullptr;
+    mio_ctx * c = new (std::nothrow) mio_ctx();
+    if (!c) return fail(MIO_ERR_ARG, "out of host memory");
+    std::string e = c->E.init_istft_only(device);
+    if (!e.empty()) {
+        delete c;
+        return fail(classify(e), e);
+    }
+    *out_ctx = c;
+    return MIO_OK;
+}
+
 void mio_ctx_destroy(mio_ctx * ctx) { delete ctx; }
 
 int mio_ctx_sample_rate(const mio_ctx * c) { return c ? c->E.hp.sample_rate : 0; }

@@ -451,6 +451,28 @@ std::string engine::load(const std::string & path, int dev) {
     return {};
 }
 
+// A context without decoder weights: istft() of the reference is a free function of (spec, istft_cache)
+// (src/istft.h:38-42), so the drop-in needs an ISTFT that works before / without miocodec_load.
+std::string engine::init_istft_only(int dev) {
+    device = dev;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) return "no CUDA device available (this library has no CPU fallback)";
+    if (dev < 0 || dev >= n_dev) return "invalid CUDA device ordinal";
+    CK(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major != 10) return std::string("device '") + prop.name + "' is not sm_100 (B200); this build contains sm_100a code only";
+    istft_only = true;
+    std::vector<float> hn(hp.n_fft);   // periodic Hann window (istft_cache, src/istft.cpp:29-31)
+    for (int i = 0; i < hp.n_fft; i++) hn[i] = 0.5f * (1.0f - cosf(2.0f * (float) M_PI * i / hp.n_fft));
+    std::string e = upload_f32(hn, &w.hann);
+    if (!e.empty()) return e;
+    w_allocs.push_back(w.hann);
+    CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    own_stream = true;
+    return {};
+}
+
 // ---------------------------------------------------------------------------------------------
 // workspace
 // ---------------------------------------------------------------------------------------------
@@ -468,6 +490,12 @@ std::string engine::ensure_workspace() {
     const size_t R1 = (size_t) max_rows1, R2 = 2 * R1, R6 = 6 * R1, R18 = 18 * R1;
     std::string e;
 #define A(ptr, n) if (!(e = dev_alloc(&ptr, (size_t) (n))).empty()) return e;
+    if (istft_only) {   // mio_istft_ctx_create: only the spectrogram staging buffer is needed
+        A(spec, R18 * 394); A(err_flag, 1);
+        CK(cudaMemset(err_flag, 0, sizeof(int)));
+        ws_ready = true;
+        return {};
+    }
     A(x768, R1 * 768); A(qkv, std::max(R1 * 2304, R2 * 1536));
     A(x512, R2 * 512); A(y512, R2 * 512); A(x256, R6 * 256); A(y256, R6 * 256); A(x128, R18 * 128); A(y128, R18 * 128);
     A(spec, R18 * 394);
@@ -511,6 +539,7 @@ row_map engine::rmap() const {
 std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts, const float * voice_table, int nv,
                            const int32_t * voice_ids) {
     batch_uploaded = false; batch_ran = false;
+    if (istft_only) return "bad argument: this context was created by mio_istft_ctx_create and has no decoder weights";
     if (n_utts < 0 || (n_utts > 0 && (!codes || !cu || !voice_table || !voice_ids)) || nv <= 0) return "bad argument";
     if (nv > max_voices) return "too many voices (max " + std::to_string(max_voices) + ")";
     std::string e = ensure_workspace();

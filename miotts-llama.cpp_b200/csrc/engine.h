@@ -39,6 +39,7 @@ struct engine {
     int gemm_gen = 2;                // 1: one CTA per tile; 2: persistent CTA pairs (cta_group::2, default)
     int max_rows1 = 16384 + 512;     // workspace rows at code resolution (codes + pad rows)
     bool ws_ready = false;
+    bool istft_only = false;         // created by mio_istft_ctx_create: no decoder weights, ISTFT workspace only
     bool debug_snap = false;
     std::map<std::string, std::vector<float>> snaps;
     std::string err;
@@ -80,6 +81,7 @@ struct engine {
 
     ~engine();
     std::string load(const std::string & gguf_path, int device);
+    std::string init_istft_only(int device);
     std::string ensure_workspace();
     // layout + H2D. codes_concat/cu_seqlens in the caller's (unpadded) indexing.
     std::string upload(const int32_t * codes, const int32_t * cu, int n_utts, const float * voice_table, int n_voices,

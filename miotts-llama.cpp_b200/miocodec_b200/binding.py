@@ -19,7 +19,7 @@ MIO_OK, MIO_ERR_ARG, MIO_ERR_IO, MIO_ERR_FORMAT, MIO_ERR_CUDA, MIO_ERR_RANGE, MI
 
 # every symbol include/miocodec_b200.h declares (tests check the library exports exactly these)
 EXPORTS = [
-    "mio_ctx_create", "mio_ctx_destroy", "mio_ctx_sample_rate", "mio_ctx_n_fft", "mio_ctx_hop_length",
+    "mio_ctx_create", "mio_istft_ctx_create", "mio_ctx_destroy", "mio_ctx_sample_rate", "mio_ctx_n_fft", "mio_ctx_hop_length",
     "mio_ctx_samples_per_token", "mio_ctx_frames_per_code", "mio_ctx_vocab", "mio_ctx_device", "mio_ctx_set_option",
     "mio_ctx_set_stream", "mio_voice_load", "mio_print_tensors", "mio_decode_spec", "mio_istft", "mio_decode_wave",
     "mio_decode_wave_batch", "mio_batch_upload", "mio_batch_run", "mio_batch_fetch", "mio_batch_sync",
@@ -56,6 +56,7 @@ def lib() -> C.CDLL:
     L.mio_last_error.restype = C.c_char_p
     L.mio_version.restype = C.c_char_p
     L.mio_ctx_create.argtypes = [C.c_char_p, C.c_int, C.POINTER(vp)]
+    L.mio_istft_ctx_create.argtypes = [C.c_int, C.POINTER(vp)]
     L.mio_ctx_destroy.argtypes = [vp]
     L.mio_ctx_destroy.restype = None
     for n in ("sample_rate", "n_fft", "hop_length", "samples_per_token", "frames_per_code", "vocab", "device"):
