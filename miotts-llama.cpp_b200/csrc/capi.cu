@@ -60,6 +60,7 @@ int mio_ctx_create(const char * gguf_path, int device, mio_ctx ** out_ctx) {
     if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "simt")) c->E.use_simt = true;
     if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "tc1")) c->E.gemm_gen = 1;
     if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "tc2")) c->E.gemm_gen = 2;
+    if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "tc3")) c->E.gemm_gen = 3;
     *out_ctx = c;
     return MIO_OK;
 }
@@ -91,7 +92,7 @@ int mio_ctx_device(const mio_ctx * c) { return c ? c->E.device : -1; }
 int mio_ctx_set_option(mio_ctx * c, const char * key, const char * value) {
     if (!c || !key || !value) return fail(MIO_ERR_ARG, "bad argument");
     if (!strcmp(key, "gemm")) {
-        if (!strcmp(value, "tc")) { c->E.use_simt = false; }
+        if (!strcmp(value, "tc") || !strcmp(value, "tc3")) { c->E.use_simt = false; c->E.gemm_gen = 3; }
         else if (!strcmp(value, "tc1")) { c->E.use_simt = false; c->E.gemm_gen = 1; }
         else if (!strcmp(value, "tc2")) { c->E.use_simt = false; c->E.gemm_gen = 2; }
         else if (!strcmp(value, "simt")) c->E.use_simt = true;

@@ -14,6 +14,7 @@ namespace mio {
     } while (0)
 
 constexpr int GN_SLOTS = 16;
+constexpr int SPEC_LD = 400;   // spectrogram row pitch in floats: 394 padded to a 16-byte multiple (TMA store pitch rule)
 
 // ---------------------------------------------------------------------------------------------
 // TMA descriptors (driver entry point fetched at run time: the library has no link-time libcuda dependency, so it
@@ -47,6 +48,35 @@ static std::string make_map(CUtensorMap * tm, const __half * base, int rows, int
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return "cuTensorMapEncodeTiled failed (" + std::to_string((int) r) + ")";
     return {};
+}
+
+// output tile map of the generation-3 GEMM epilogue: [rows][cols] elements of `esize` bytes with row pitch ld_bytes,
+// box {32, 32}; fp32 -> SWIZZLE_128B (128-byte box rows), fp16 -> SWIZZLE_64B.  rows == M: the TMA unit clips.
+static std::string make_out_map(CUtensorMap * tm, const void * base, int esize, int rows, int cols, size_t ld_bytes) {
+    std::string e = get_encode();
+    if (!e.empty()) return e;
+    if (ld_bytes % 16 != 0 || ((uintptr_t) base & 15) != 0) return "internal: GEMM output not 16-byte aligned for TMA";
+    cuuint64_t dims[2] = {(cuuint64_t) cols, (cuuint64_t) rows};
+    cuuint64_t strides[1] = {(cuuint64_t) ld_bytes};
+    cuuint32_t box[2] = {32u, 32u};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = g_encode(tm, esize == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (void *) base,
+                          dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          esize == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                          CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return "cuTensorMapEncodeTiled (output) failed (" + std::to_string((int) r) + ")";
+    return {};
+}
+
+const CUtensorMap * engine::out_map(const void * base, int esize, int rows, int cols, size_t ld_bytes) {
+    out_map_key k{base, esize, rows, cols, ld_bytes};
+    auto it = out_maps.find(k);
+    if (it != out_maps.end()) return &it->second;
+    CUtensorMap tm;
+    std::string e = make_out_map(&tm, base, esize, rows, cols, ld_bytes);
+    if (!e.empty()) { err = e; return nullptr; }
+    if (out_maps.size() > 4096) out_maps.clear();        // bounded: shapes repeat in steady state
+    return &(out_maps[k] = tm);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -491,14 +521,14 @@ std::string engine::ensure_workspace() {
     std::string e;
 #define A(ptr, n) if (!(e = dev_alloc(&ptr, (size_t) (n))).empty()) return e;
     if (istft_only) {   // mio_istft_ctx_create: only the spectrogram staging buffer is needed
-        A(spec, R18 * 394); A(err_flag, 1);
+        A(spec, R18 * SPEC_LD); A(err_flag, 1);
         CK(cudaMemset(err_flag, 0, sizeof(int)));
         ws_ready = true;
         return {};
     }
     A(x768, R1 * 768); A(qkv, std::max(R1 * 2304, R2 * 1536));
     A(x512, R2 * 512); A(y512, R2 * 512); A(x256, R6 * 256); A(y256, R6 * 256); A(x128, R18 * 128); A(y128, R18 * 128);
-    A(spec, R18 * 394);
+    A(spec, R18 * SPEC_LD);
     A(aA_hi, R1 * 1024); A(aA_lo, R1 * 1024); A(aFF_hi, R1 * 3072); A(aFF_lo, R1 * 3072);
     A(c16, R1 * 2304); A(h512_hi, R18 * 512); A(h512_lo, R18 * 512);
     A(gn_stats, (size_t) GN_SLOTS * max_utts * 64);
@@ -654,6 +684,13 @@ void engine::snap_f32(const char * name, const float * d, size_t n) {
     v.resize(n);
     cudaMemcpy(v.data(), d, n * sizeof(float), cudaMemcpyDeviceToHost);
 }
+void engine::snap_f32_2d(const char * name, const float * d, size_t rows, size_t cols, size_t ld) {
+    if (!debug_snap) return;
+    cudaStreamSynchronize(stream);
+    std::vector<float> & v = snaps[name];
+    v.resize(rows * cols);
+    cudaMemcpy2D(v.data(), cols * sizeof(float), d, ld * sizeof(float), cols * sizeof(float), rows, cudaMemcpyDeviceToHost);
+}
 void engine::snap_f16(const char * name, const __half * hi, const __half * lo, size_t n) {
     if (!debug_snap) return;
     cudaStreamSynchronize(stream);
@@ -678,7 +715,19 @@ cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_pa
     prof_begin(W.npass == 3 ? CAT_GEMM_SPLIT : CAT_GEMM_F16, 2.0 * M * (double) W.N * W.K * W.taps, 0.0);
     cudaError_t ce;
     if (use_simt) ce = launch_gemm_simt(p, stream);
-    else if (gemm_gen == 2) ce = launch_gemm_tc2(p, A.tm_hi, A.tm_lo, W.tm2_hi, W.tm2_lo, W.bn2, stream);
+    else if (gemm_gen == 3) {
+        const bool f16 = (p.epi == EPI_SWIGLU || p.epi == EPI_SPLIT || p.epi == EPI_QKV);
+        const int ncols = (p.epi == EPI_SWIGLU) ? W.N / 2 : W.N;
+        const CUtensorMap *o0, *o1;
+        if (f16) {
+            o0 = out_map(p.out_hi, 2, M, ncols, (size_t) p.ld_h * 2);
+            o1 = out_map(p.out_lo, 2, M, ncols, (size_t) p.ld_h * 2);
+        } else {
+            o0 = o1 = out_map(p.out_f32, 4, M, ncols, (size_t) p.ld_out * 4);
+        }
+        if (!o0 || !o1) { prof_end(); return cudaErrorInvalidValue; }
+        ce = launch_gemm_tc3(p, A.tm_hi, A.tm_lo, W.tm2_hi, W.tm2_lo, *o0, *o1, W.bn2, stream);
+    } else if (gemm_gen == 2) ce = launch_gemm_tc2(p, A.tm_hi, A.tm_lo, W.tm2_hi, W.tm2_lo, W.bn2, stream);
     else ce = launch_gemm_tc(p, A.tm_hi, A.tm_lo, W.tm_hi, W.tm_lo, W.box_n, stream);
     prof_end();
     return ce;
@@ -856,9 +905,9 @@ std::string engine::run_chunk(const chunk_info & c) {
     p.snake_ea = w.out_snake_ea; p.snake_eb = w.out_snake_eb;
     CKG(gemm(w.out_proj, vFF128, R18, p));
     // 9. head: 512 -> 394, exp/clamp/cos/sin -> interleaved (re, im)
-    p = gemm_params(); p.epi = EPI_HEAD; p.out_f32 = spec; p.ld_out = 2 * hp.n_freq; p.bias = w.head_b;
+    p = gemm_params(); p.epi = EPI_HEAD; p.out_f32 = spec; p.ld_out = SPEC_LD; p.bias = w.head_b;
     CKG(gemm(w.head, vH512, R18, p));
-    snap_f32("spec", spec, (size_t) R18 * 2 * hp.n_freq);
+    snap_f32_2d("spec", spec, (size_t) R18, 2 * hp.n_freq, SPEC_LD);
     // ISTFT
     if (!(e = run_istft(c, spec)).empty()) return e;
     return {};
@@ -866,7 +915,7 @@ std::string engine::run_chunk(const chunk_info & c) {
 
 std::string engine::run_istft(const chunk_info & c, const float * spec_dev) {
     istft_params ip;
-    ip.spec = spec_dev; ip.wave = d_wave;
+    ip.spec = spec_dev; ip.spec_ld = SPEC_LD; ip.wave = d_wave;
     ip.start = d_start + c.utt0; ip.len = d_len + c.utt0; ip.out_off = d_out_off + c.utt0;
     ip.chunk_cu = d_chunk_cu + c.cu0; ip.hann = w.hann;
     ip.n_utts = c.n_utts; ip.frames_per_code = hp.frames_per_code; ip.total_chunks = c.istft_blocks;
@@ -938,7 +987,9 @@ std::string engine::fetch_spec(int utt, float * out, int64_t cap) {
     const int fpc = hp.frames_per_code;
     const size_t n = (size_t) lay.len[utt] * fpc * 2 * hp.n_freq;
     if ((int64_t) n > cap) return "output capacity too small";
-    if (n) CK(cudaMemcpy(out, spec + (size_t) lay.start[utt] * fpc * 2 * hp.n_freq, n * sizeof(float), cudaMemcpyDeviceToHost));
+    if (n) CK(cudaMemcpy2D(out, (size_t) 2 * hp.n_freq * sizeof(float), spec + (size_t) lay.start[utt] * fpc * SPEC_LD,
+                           (size_t) SPEC_LD * sizeof(float), (size_t) 2 * hp.n_freq * sizeof(float), (size_t) lay.len[utt] * fpc,
+                           cudaMemcpyDeviceToHost));
     return {};
 }
 
@@ -973,9 +1024,10 @@ std::string engine::run_istft_only(const float * spec_host, int n_frames) {
     CK(cudaMemcpy(d_len, &len0, 4, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_out_off, &off0, 8, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_chunk_cu, ccu, 8, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(spec, spec_host, (size_t) n_frames * 2 * hp.n_freq * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy2D(spec, (size_t) SPEC_LD * sizeof(float), spec_host, (size_t) 2 * hp.n_freq * sizeof(float),
+                    (size_t) 2 * hp.n_freq * sizeof(float), (size_t) n_frames, cudaMemcpyHostToDevice));
     istft_params ip;
-    ip.spec = spec; ip.wave = d_wave; ip.start = d_start; ip.len = d_len; ip.out_off = d_out_off; ip.chunk_cu = d_chunk_cu;
+    ip.spec = spec; ip.spec_ld = SPEC_LD; ip.wave = d_wave; ip.start = d_start; ip.len = d_len; ip.out_off = d_out_off; ip.chunk_cu = d_chunk_cu;
     ip.hann = w.hann; ip.n_utts = 1; ip.frames_per_code = 1; ip.total_chunks = blocks;
     const double istft_bytes = (double) n_frames * 1968.0;
     launches = 0;

@@ -29,6 +29,17 @@ struct chunk_info {              // a run of whole utterances that fits the work
     int istft_blocks = 0;
 };
 
+struct out_map_key {
+    const void * base; int esize, rows, cols; size_t ld;
+    bool operator<(const out_map_key & o) const {
+        if (base != o.base) return base < o.base;
+        if (esize != o.esize) return esize < o.esize;
+        if (rows != o.rows) return rows < o.rows;
+        if (cols != o.cols) return cols < o.cols;
+        return ld < o.ld;
+    }
+};
+
 struct engine {
     int device = 0;
     hparams hp;
@@ -36,7 +47,7 @@ struct engine {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     bool use_simt = false;
-    int gemm_gen = 2;                // 1: one CTA per tile; 2: persistent CTA pairs (cta_group::2, default)
+    int gemm_gen = 3;                // 1: one CTA per tile; 2: persistent CTA pairs (cta_group::2); 3: + TMA-store epilogue (default)
     int max_rows1 = 16384 + 512;     // workspace rows at code resolution (codes + pad rows)
     bool ws_ready = false;
     bool istft_only = false;         // created by mio_istft_ctx_create: no decoder weights, ISTFT workspace only
@@ -97,6 +108,8 @@ struct engine {
     std::string run_istft(const chunk_info & c, const float * spec_dev);
     std::string view512_ff(a_view & v);
     cudaError_t gemm(const gemm_weight & W, const a_view & A, int M, gemm_params p);
+    std::map<out_map_key, CUtensorMap> out_maps;          // TMA maps of GEMM outputs, keyed by (buffer, shape)
+    const CUtensorMap * out_map(const void * base, int esize, int rows, int cols, size_t ld_bytes);
     // profiling
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events; size_t prof_used = 0;
@@ -106,6 +119,7 @@ struct engine {
     void prof_end();
     void prof_collect();
     void snap_f32(const char * name, const float * d, size_t n);
+    void snap_f32_2d(const char * name, const float * d, size_t rows, size_t cols, size_t ld);
     void snap_f16(const char * name, const __half * hi, const __half * lo, size_t n);
 };
 

@@ -1,0 +1,423 @@
+// Generation-3 tap-GEMM: the persistent CTA-pair tcgen05 main loop of gemm.cu (generation 2) with a rebuilt epilogue.
+//
+// Why: the layers of this decoder have short K (128..2048), so a 256 x 256 tile spends only ~6 us in MMAs and the
+// epilogue sets the tile time (profiles/r1b_summary.md: tensor pipe 31-74 % busy, tracking K).  Generation 2 used 4
+// epilogue warps with per-thread row-strided 16-byte global stores and an exposed read-modify-write for residuals.
+// Here:
+//   * 8 epilogue warps per CTA (two per TMEM lane quadrant, each owning half of the tile's columns)
+//   * each warp moves 32 rows x 32 accumulator columns at a time: tcgen05.ld -> registers -> fused math -> swizzled
+//     shared-memory staging tile (4 KB per warp, bank-conflict free) -> one TMA store (full 128-byte lines, clipped
+//     by the tensor map at the M / N edges, asynchronous)
+//   * residual layers (x += gate * y) use the TMA reduce-add (cp.reduce.async.bulk.tensor .add.f32): no load of x
+//   * new EPI_QKV: RoPE + 1/sqrt(d) + fp16 hi/lo split fused behind the QKV projection
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace mio {
+
+constexpr int G3_BK = 64;
+constexpr int G3_THREADS = 320;     // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-9: epilogue
+constexpr int G3_EPI_WARPS = 8;
+constexpr int G3_STAGE_TILE = 4096; // staging bytes per epilogue warp
+
+template <int BN, int NPASS>
+struct gemm3_cfg {
+    static constexpr int A_BYTES = 128 * G3_BK * 2;                  // this CTA's 128 rows
+    static constexpr int B_BYTES = (BN / 2) * G3_BK * 2;             // this CTA's half of the B tile
+    static constexpr int NOPS = (NPASS == 3) ? 2 : 1;
+    static constexpr int STAGE_BYTES = NOPS * (A_BYTES + B_BYTES);
+    static constexpr int STAGES = (196608 / STAGE_BYTES) > 8 ? 8 : (196608 / STAGE_BYTES);
+    static constexpr int EPI_BYTES = G3_EPI_WARPS * G3_STAGE_TILE;   // 32 KB
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
+    static constexpr uint32_t IDESC = (1u << 4) | ((uint32_t) (BN >> 3) << 17) | ((uint32_t) (256 >> 4) << 24);
+    static constexpr uint32_t TMEM_COLS = 2 * BN;                    // double-buffered accumulator
+};
+
+__device__ __forceinline__ uint32_t pack_split_hi_lo(float a, float b, uint32_t & lo) {
+    __half ah, al, bh, bl;
+    split_half2(a, ah, al);
+    split_half2(b, bh, bl);
+    lo = pack_h2(al, bl);
+    return pack_h2(ah, bh);
+}
+
+// fp32 staging tile: [32 rows][128 B], SWIZZLE_128B (16-byte chunk index ^= row & 7)
+__device__ __forceinline__ void stage_f32_row(uint8_t * stage, int lane, const float (&v)[32]) {
+    float4 * rowp = (float4 *) (stage + lane * 128);
+#pragma unroll
+    for (int j = 0; j < 8; j++) rowp[j ^ (lane & 7)] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+}
+// fp16 staging tiles: hi at +0, lo at +2048, each [32 rows][64 B], SWIZZLE_64B (chunk index ^= (row >> 1) & 3).
+// Writes outputs [first, first + 2*NP) of the 32-wide row, NP pairs given as packed half2.
+template <int NP>
+__device__ __forceinline__ void stage_f16_row(uint8_t * stage, int lane, int first_chunk, const uint32_t (&hi)[NP],
+                                              const uint32_t (&lo)[NP]) {
+    uint4 * rh = (uint4 *) (stage + lane * 64);
+    uint4 * rl = (uint4 *) (stage + 2048 + lane * 64);
+    const int sw = (lane >> 1) & 3;
+#pragma unroll
+    for (int j = 0; j < NP / 4; j++) {
+        const int c = (first_chunk + j) ^ sw;
+        rh[c] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
+        rl[c] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+    }
+}
+
+// One row (this thread's), 32 accumulator columns starting at col0: fused math + write into the staging tile.
+// `part` is the half of an fp16 output row this chunk fills (EPI_SWIGLU only: 32 accumulators -> 16 outputs).
+template <int EPI>
+__device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int col0, float (&v)[32], uint8_t * stage,
+                                           int lane, int part) {
+    const bool full = (col0 + 32 <= p.N);
+    const int cb = col0 % p.bias_mod;
+    if (p.bias != nullptr) {
+        if (full) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+                const float4 b = __ldg((const float4 *) (p.bias + cb + i));
+                v[i] = v[i] * p.out_scale + b.x; v[i + 1] = v[i + 1] * p.out_scale + b.y;
+                v[i + 2] = v[i + 2] * p.out_scale + b.z; v[i + 3] = v[i + 3] * p.out_scale + b.w;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; i++) v[i] = v[i] * p.out_scale + ((col0 + i < p.N) ? __ldg(p.bias + cb + i) : 0.f);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 32; i++) v[i] *= p.out_scale;
+    }
+    if constexpr (EPI == EPI_STORE) {
+        stage_f32_row(stage, lane, v);
+    } else if constexpr (EPI == EPI_RESID) {
+        // x += gate[utt] * y: the add itself is done by the TMA reduce; pad rows of gated layers contribute 0
+        if (p.gate != nullptr) {
+            const int u = (row < p.M) ? p.row_utt[row / p.row_div] : -1;
+            if (u < 0) {
+#pragma unroll
+                for (int i = 0; i < 32; i++) v[i] = 0.f;
+            } else {
+                const float * g = p.gate + (size_t) p.gate_voice[u] * p.gate_ld + col0;
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                    const float4 gg = __ldg((const float4 *) (g + i));
+                    v[i] *= gg.x; v[i + 1] *= gg.y; v[i + 2] *= gg.z; v[i + 3] *= gg.w;
+                }
+            }
+        }
+        stage_f32_row(stage, lane, v);
+    } else if constexpr (EPI == EPI_SWIGLU) {
+        // (gate, up) interleaved: h = silu(g) * u  (swiglu_ffn, src/miocodec.cpp:220-225)
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const float g0 = v[4 * i], u0 = v[4 * i + 1], g1 = v[4 * i + 2], u1 = v[4 * i + 3];
+            const float h0 = (g0 / (1.0f + expf(-g0))) * u0;
+            const float h1 = (g1 / (1.0f + expf(-g1))) * u1;
+            hi[i] = pack_split_hi_lo(h0, h1, lo[i]);
+        }
+        stage_f16_row<8>(stage, lane, 2 * part, hi, lo);
+    } else if constexpr (EPI == EPI_SPLIT || EPI == EPI_SNAKE) {
+        if (p.snake_ea != nullptr) {
+            // snake(x) = x + sin^2(e^alpha x) / e^beta  (snake_activation, src/miocodec.cpp:410-420, :717-725)
+#pragma unroll
+            for (int i = 0; i < 32; i++) {
+                if (full || col0 + i < p.N) {
+                    const float ea = __ldg(p.snake_ea + cb + i), eb = __ldg(p.snake_eb + cb + i);
+                    const float s = sinf(v[i] * ea);
+                    v[i] = v[i] + (s * s) / eb;
+                }
+            }
+        }
+        if constexpr (EPI == EPI_SNAKE) {
+            stage_f32_row(stage, lane, v);
+        } else {
+            uint32_t hi[16], lo[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) hi[i] = pack_split_hi_lo(v[2 * i], v[2 * i + 1], lo[i]);
+            stage_f16_row<16>(stage, lane, 0, hi, lo);
+        }
+    } else if constexpr (EPI == EPI_HEAD) {
+        // (log-magnitude, phase) interleaved -> (re, im)  (src/miocodec.cpp:732-737)
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+            const float mag = fminf(fmaxf(expf(v[i]), 0.0f), 100.0f);
+            float sn, cs;
+            sincosf(v[i + 1], &sn, &cs);
+            v[i] = mag * cs;
+            v[i + 1] = mag * sn;
+        }
+        stage_f32_row(stage, lane, v);
+    } else if constexpr (EPI == EPI_QKV) {
+        // RoPE mode 0 (adjacent pairs) on the q and k columns with the utterance-relative position
+        // (mha_rope, src/miocodec.cpp:260-263; ggml rope cache ops.cpp:5612-5626); q pre-scaled by 1/sqrt(head_dim)
+        if (col0 < p.rope_cols) {
+            const int u = (row < p.M) ? p.row_utt[row / p.row_div] : -1;
+            if (u >= 0) {
+                const int pos = min(row - p.utt_start[u] * p.row_div, p.rope_max_pos - 1);
+                const float4 * cs = (const float4 *) (p.rope + ((size_t) pos * 32 + ((col0 & 63) >> 1)) * 2);
+                const float qs = (col0 < p.q_cols) ? p.q_scale : 1.0f;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const float4 t = __ldg(cs + i);       // (cos, sin) of two consecutive pairs
+                    const float x0 = v[4 * i], x1 = v[4 * i + 1], x2 = v[4 * i + 2], x3 = v[4 * i + 3];
+                    v[4 * i] = (x0 * t.x - x1 * t.y) * qs;
+                    v[4 * i + 1] = (x0 * t.y + x1 * t.x) * qs;
+                    v[4 * i + 2] = (x2 * t.z - x3 * t.w) * qs;
+                    v[4 * i + 3] = (x2 * t.w + x3 * t.z) * qs;
+                }
+            }
+        }
+        uint32_t hi[16], lo[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) hi[i] = pack_split_hi_lo(v[2 * i], v[2 * i + 1], lo[i]);
+        stage_f16_row<16>(stage, lane, 0, hi, lo);
+    }
+}
+
+template <int EPI> struct epi3_out {
+    static constexpr bool F16 = (EPI == EPI_SWIGLU || EPI == EPI_SPLIT || EPI == EPI_QKV);
+    static constexpr bool REDUCE = (EPI == EPI_RESID);
+    static constexpr int ACC_PER_OUT = (EPI == EPI_SWIGLU) ? 2 : 1;   // accumulator columns per output column
+};
+
+template <int BN, int NPASS, int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G3_THREADS, 1)
+gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
+                const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
+                const __grid_constant__ CUtensorMap tmO0, const __grid_constant__ CUtensorMap tmO1,
+                const gemm_params p) {
+    using cfg = gemm3_cfg<BN, NPASS>;
+    using eo = epi3_out<EPI>;
+    extern __shared__ uint8_t gemm3_smem_raw[];
+    const uint32_t raw = smem_u32(gemm3_smem_raw);
+    uint8_t * smem = gemm3_smem_raw + ((1024u - (raw & 1023u)) & 1023u);
+    uint8_t * epi_smem = smem + cfg::STAGES * cfg::STAGE_BYTES;            // 8 x 4 KB, 1024-aligned
+    uint64_t * bars = (uint64_t *) (epi_smem + cfg::EPI_BYTES);
+    uint64_t * full = bars;                               // [STAGES]   (used in the leader)
+    uint64_t * empty = bars + cfg::STAGES;                // [STAGES]   (both CTAs)
+    uint64_t * tmem_full = bars + 2 * cfg::STAGES;        // [2]        (both CTAs)
+    uint64_t * tmem_empty = bars + 2 * cfg::STAGES + 2;   // [2]        (used in the leader)
+    uint32_t * tmem_slot = (uint32_t *) (bars + 2 * cfg::STAGES + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+    const int tiles_n = (p.N + BN - 1) / BN, tiles_m = (p.M + 255) / 256;
+    const int num_tiles = tiles_n * tiles_m;
+    const int kb_per_tap = p.K / G3_BK;
+    const int num_kb = p.taps * kb_per_tap;
+    const int shift0 = (p.taps == 3) ? -1 : 0;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA_hi);
+        tma_prefetch_desc(&tmB_hi);
+        if (NPASS == 3) { tma_prefetch_desc(&tmA_lo); tma_prefetch_desc(&tmB_lo); }
+        tma_prefetch_desc(&tmO0);
+        if (eo::F16) tma_prefetch_desc(&tmO1);
+        for (int s = 0; s < cfg::STAGES; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int b = 0; b < 2; b++) { mbar_init(&tmem_full[b], 1); mbar_init(&tmem_empty[b], 2 * G3_EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(cfg::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs) =====
+        if (lane == 0) {
+            int it = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                const int tm = tile / tiles_n, tn = tile - tm * tiles_n;
+                const int m0 = tm * 256 + (int) rank * 128, n0 = tn * BN + (int) rank * (BN / 2);
+                for (int kb = 0; kb < num_kb; kb++, it++) {
+                    const int s = it % cfg::STAGES;
+                    const uint32_t ph = (uint32_t) (it / cfg::STAGES) & 1u;
+                    mbar_wait(&empty[s], ph ^ 1u);
+                    const uint32_t lbar = mapa_u32(smem_u32(&full[s]), 0);
+                    if (leader) mbar_expect_tx(&full[s], 2u * (uint32_t) cfg::STAGE_BYTES);
+                    uint8_t * st = smem + s * cfg::STAGE_BYTES;
+                    const int tap = kb / kb_per_tap, kk = kb - tap * kb_per_tap;
+                    const int arow = m0 + tap + shift0;
+                    tma_load_2d_pair(st, &tmA_hi, lbar, kk * G3_BK, arow);
+                    if (NPASS == 3) tma_load_2d_pair(st + cfg::A_BYTES, &tmA_lo, lbar, kk * G3_BK, arow);
+                    uint8_t * sb = st + cfg::NOPS * cfg::A_BYTES;
+                    tma_load_2d_pair(sb, &tmB_hi, lbar, kb * G3_BK, n0);
+                    if (NPASS == 3) tma_load_2d_pair(sb + cfg::B_BYTES, &tmB_lo, lbar, kb * G3_BK, n0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader CTA only) =====
+        if (leader && lane == 0) {
+            int it = 0, tile_iter = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, tile_iter++) {
+                const int b = tile_iter & 1;
+                const uint32_t aph = (uint32_t) (tile_iter >> 1) & 1u;
+                mbar_wait(&tmem_empty[b], aph ^ 1u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t d_tmem = tmem_base + (uint32_t) (b * BN);
+                for (int kb = 0; kb < num_kb; kb++, it++) {
+                    const int s = it % cfg::STAGES;
+                    const uint32_t ph = (uint32_t) (it / cfg::STAGES) & 1u;
+                    mbar_wait(&full[s], ph);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = smem_u32(smem + s * cfg::STAGE_BYTES);
+                    const uint32_t sb = sa + cfg::NOPS * cfg::A_BYTES;
+                    const uint64_t da_hi = umma_desc(sa), db_hi = umma_desc(sb);
+                    const uint64_t da_lo = umma_desc(sa + cfg::A_BYTES), db_lo = umma_desc(sb + cfg::B_BYTES);
+#pragma unroll
+                    for (int k = 0; k < G3_BK / 16; k++) {
+                        const uint64_t adv = (uint64_t) (k * 2);
+                        umma_f16_pair(d_tmem, da_hi + adv, db_hi + adv, cfg::IDESC, (kb > 0 || k > 0) ? 1u : 0u);
+                        if (NPASS == 3) {
+                            umma_f16_pair(d_tmem, da_hi + adv, db_lo + adv, cfg::IDESC, 1u);
+                            umma_f16_pair(d_tmem, da_lo + adv, db_hi + adv, cfg::IDESC, 1u);
+                        }
+                    }
+                    umma_commit_pair(&empty[s]);
+                }
+                umma_commit_pair(&tmem_full[b]);
+            }
+        }
+    } else {
+        // ===== epilogue warps (both CTAs): TMEM lane quadrant = warp % 4, column half = (warp - 2) / 4 =====
+        const int lg = warp & 3;
+        const int half = (warp - 2) >> 2;
+        constexpr int CH = BN / 2 / 32;                          // 32-column chunks per warp per tile
+        uint8_t * stage = epi_smem + (warp - 2) * G3_STAGE_TILE;
+        const uint32_t tmem_empty_leader0 = mapa_u32(smem_u32(&tmem_empty[0]), 0);
+        const uint32_t tmem_empty_leader1 = mapa_u32(smem_u32(&tmem_empty[1]), 0);
+        int tile_iter = 0;
+        for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, tile_iter++) {
+            const int tm = tile / tiles_n, tn = tile - tm * tiles_n;
+            const int b = tile_iter & 1;
+            const uint32_t aph = (uint32_t) (tile_iter >> 1) & 1u;
+            const int row0 = tm * 256 + (int) rank * 128 + lg * 32;      // first row of this warp's 32-row slab
+            const int row = row0 + lane;
+            const int colw = tn * BN + half * (BN / 2);                  // first accumulator column of this warp
+            int nch = (p.N - colw + 31) / 32;                            // valid chunks (warp-uniform)
+            nch = nch < 0 ? 0 : (nch > CH ? CH : nch);
+            if (row0 >= p.M) nch = 0;
+            mbar_wait(&tmem_full[b], aph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t t_addr = tmem_base + ((uint32_t) (lg * 32) << 16) + (uint32_t) (b * BN + half * (BN / 2));
+#pragma unroll 1
+            for (int c = 0; c < nch; c++) {
+                float v[32];
+                tmem_ld32(t_addr + (uint32_t) (c * 32), v);
+                if (c == nch - 1) {                                      // accumulator drained: hand it back early
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_remote(b ? tmem_empty_leader1 : tmem_empty_leader0);
+                }
+                const int part = (eo::ACC_PER_OUT == 2) ? (c & 1) : 0;
+                if (part == 0) {                                         // staging tile free again?
+                    if (lane == 0) tma_store_wait_read0();
+                    __syncwarp();
+                }
+                epi3_chunk<EPI>(p, row, colw + c * 32, v, stage, lane, part);
+                const bool flush = (eo::ACC_PER_OUT == 1) || part == 1 || c == nch - 1;
+                if (flush) {
+                    fence_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        const int oc = (eo::ACC_PER_OUT == 2) ? (colw + (c & ~1) * 32) / 2 : colw + c * 32;
+                        if (eo::REDUCE) tma_reduce_add_2d(&tmO0, stage, oc, row0);
+                        else tma_store_2d(&tmO0, stage, oc, row0);
+                        if (eo::F16) tma_store_2d(&tmO1, stage + 2048, oc, row0);
+                        tma_store_commit();
+                    }
+                }
+            }
+            if (nch == 0) {
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive_remote(b ? tmem_empty_leader1 : tmem_empty_leader0);
+            }
+        }
+        if (lane == 0) tma_store_wait_all0();
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(cfg::TMEM_COLS) : "memory");
+    }
+}
+
+static int g3_num_sms = 0;
+
+template <int BN, int NPASS, int EPI>
+static cudaError_t launch_tc3_inst(const gemm_params & p, const CUtensorMap & a_hi, const CUtensorMap & a_lo,
+                                   const CUtensorMap & b_hi, const CUtensorMap & b_lo, const CUtensorMap & o0,
+                                   const CUtensorMap & o1, cudaStream_t st) {
+    using cfg = gemm3_cfg<BN, NPASS>;
+    static_assert(cfg::SMEM_BYTES <= 232448, "shared memory budget");
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc3_kernel<BN, NPASS, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    if (g3_num_sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g3_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int tiles = ((p.N + BN - 1) / BN) * ((p.M + 255) / 256);
+    int clusters = g3_num_sms / 2;
+    if (tiles < clusters) clusters = tiles;
+    gemm_tc3_kernel<BN, NPASS, EPI><<<2 * clusters, G3_THREADS, cfg::SMEM_BYTES, st>>>(a_hi, a_lo, b_hi, b_lo, o0, o1, p);
+    return cudaGetLastError();
+}
+
+template <int BN, int NPASS>
+static cudaError_t launch_tc3_epi(const gemm_params & p, const CUtensorMap & a_hi, const CUtensorMap & a_lo,
+                                  const CUtensorMap & b_hi, const CUtensorMap & b_lo, const CUtensorMap & o0,
+                                  const CUtensorMap & o1, cudaStream_t st) {
+    switch (p.epi) {
+        case EPI_STORE: return launch_tc3_inst<BN, NPASS, EPI_STORE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+        case EPI_RESID: return launch_tc3_inst<BN, NPASS, EPI_RESID>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+        default: break;
+    }
+    if constexpr (NPASS == 3) {
+        switch (p.epi) {
+            case EPI_SWIGLU:
+                if (p.N % 64 != 0) return cudaErrorInvalidValue;
+                return launch_tc3_inst<BN, 3, EPI_SWIGLU>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+            case EPI_SPLIT: return launch_tc3_inst<BN, 3, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+            case EPI_SNAKE: return launch_tc3_inst<BN, 3, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+            case EPI_HEAD: return launch_tc3_inst<BN, 3, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+            case EPI_QKV: return launch_tc3_inst<BN, 3, EPI_QKV>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+            default: break;
+        }
+    }
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_gemm_tc3(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
+                            const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, const CUtensorMap & tmO0,
+                            const CUtensorMap & tmO1, int bn, cudaStream_t st) {
+    if (p.M <= 0) return cudaSuccess;
+    if (p.K % G3_BK != 0 || (p.taps != 1 && p.taps != 3)) return cudaErrorInvalidValue;
+    if (bn == 256) {
+        if (p.npass == 3) return launch_tc3_epi<256, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
+        return launch_tc3_epi<256, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
+    }
+    if (bn == 128) {
+        if (p.npass == 3) return launch_tc3_epi<128, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
+        return launch_tc3_epi<128, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace mio

@@ -41,17 +41,18 @@ __global__ void __launch_bounds__(128) istft_kernel(istft_params p, const float 
     const int g1 = min(F, g0 + IST_G);
     const int f_lo = max(0, g0 - 2), f_hi = min(F, g1 + 2);   // frames needed [f_lo, f_hi)
     const int nfr = f_hi - f_lo;
-    const float * spec = p.spec + ((size_t) p.start[u] * p.frames_per_code + f_lo) * (2 * IST_NFREQ);
+    const float * spec = p.spec + ((size_t) p.start[u] * p.frames_per_code + f_lo) * p.spec_ld;
 
     for (int i = threadIdx.x; i < 2 * 196; i += blockDim.x) { tw392[i] = tw392g[i]; tw196[i] = tw196g[i]; }
     for (int i = threadIdx.x; i < IST_NFFT; i += blockDim.x) hann[i] = p.hann[i];
-    // phase 0: rows are contiguous in HBM (1576 B each, 8-byte aligned) -> float2 stream
+    // phase 0: frame rows are spec_ld floats apart (8-byte aligned) -> float2 stream
     {
         const float2 * src = (const float2 *) spec;
         const int total = nfr * IST_NFREQ;
+        const int ld2 = p.spec_ld >> 1;
         for (int i = threadIdx.x; i < total; i += blockDim.x) {
             const int fr = i / IST_NFREQ, k = i - fr * IST_NFREQ;
-            const float2 v = __ldg(src + i);
+            const float2 v = __ldg(src + (size_t) fr * ld2 + k);
             *(float2 *) (slots + fr * IST_SLOT_FLOATS + 2 * k) = v;
         }
     }

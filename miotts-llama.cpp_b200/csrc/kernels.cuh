@@ -16,7 +16,8 @@ enum epi_kind : int {
     EPI_SWIGLU = 2,  // columns interleaved (gate, up): h = silu(g)*u -> split fp16 at col/2
     EPI_SPLIT = 3,   // y = acc*s + bias (-> snake) -> split fp16
     EPI_SNAKE = 4,   // y = snake(acc*s + bias) -> out_f32
-    EPI_HEAD = 5     // columns interleaved (log-mag, phase): (re, im) -> out_f32
+    EPI_HEAD = 5,    // columns interleaved (log-mag, phase): (re, im) -> out_f32
+    EPI_QKV = 6      // stacked q|k|v: RoPE (adjacent pairs) on q and k, q pre-scaled by 1/sqrt(64) -> split fp16
 };
 
 struct gemm_params {
@@ -31,6 +32,10 @@ struct gemm_params {
     const int32_t * gate_voice = nullptr;
     const int32_t * row_utt = nullptr; int row_div = 1;   // utt = row_utt[row / row_div] (<0: pad row)
     const float * snake_ea = nullptr; const float * snake_eb = nullptr;   // exp(alpha), exp(beta) [bias_mod]
+    // EPI_QKV: rope[pos][32][2] (cos, sin), pos = row - utt_start[utt] * row_div; columns < rope_cols are rotated,
+    // columns < q_cols additionally multiplied by q_scale
+    const float * rope = nullptr; int rope_max_pos = 0; const int32_t * utt_start = nullptr;
+    int rope_cols = 0, q_cols = 0; float q_scale = 1.f;
     // raw operand pointers (SIMT validation path; the tcgen05 path reads through the tensor maps)
     const __half * a_hi = nullptr; const __half * a_lo = nullptr; int lda = 0; int a_rows = 0;
     const __half * b_hi = nullptr; const __half * b_lo = nullptr;
@@ -42,6 +47,12 @@ cudaError_t launch_gemm_tc(const gemm_params & p, const CUtensorMap & tmA_hi, co
 // generation 2: persistent CTA-pair kernel (cta_group::2, 256 x bn tiles). tmB_*: box {64, bn/2}
 cudaError_t launch_gemm_tc2(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
                             const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, int bn, cudaStream_t st);
+// generation 3 (default): generation 2's main loop + 8 epilogue warps that stage results in swizzled shared memory and
+// write them with TMA stores (reduce-add for EPI_RESID).  tmO0: fp32 output or fp16 hi, tmO1: fp16 lo; box {32, 32},
+// SWIZZLE_128B (fp32) / SWIZZLE_64B (fp16), row extent == M so the TMA unit clips the last tile.
+cudaError_t launch_gemm_tc3(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
+                            const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, const CUtensorMap & tmO0,
+                            const CUtensorMap & tmO1, int bn, cudaStream_t st);
 cudaError_t launch_gemm_simt(const gemm_params & p, cudaStream_t st);
 cudaError_t gemm_tc_init();   // sets the dynamic shared memory attributes once
 
@@ -81,7 +92,8 @@ cudaError_t launch_cond(const float * voice_table, int n_voices, int adaln_dim, 
 
 // ------------------------------------------------------------------------------------------ ISTFT
 struct istft_params {
-    const float * spec;          // [rows18][394]
+    const float * spec;          // [rows18][spec_ld], 394 floats used per row
+    int spec_ld;                 // row pitch in floats (even)
     float * wave;                // output samples
     const int32_t * start;       // [n_utts] first row at code resolution (frames start at fpc*start)
     const int32_t * len;         // [n_utts] codes
