@@ -146,17 +146,23 @@ cudaError_t launch_layernorm(const float * x, int rows, int D, float eps, const 
 }
 
 // ---------------------------------------------------------------------------------------------
-// Banded local attention, head_dim 64, |i-j| <= window/2, per-utterance boundaries, RoPE mode 0 (adjacent pairs)
-// on q and k with per-utterance positions (mha_rope, src/miocodec.cpp:245-286; the reference materialises dense
-// scores with a -inf mask, :233-242 — masked terms are exactly 0 after softmax so the band is identical).
-// Block: 4 warps, ATT_QB query rows x 1 head; K (RoPE applied) and V of rows [q0-32, q0+QB+32) staged in smem.
+// Banded local attention, CUDA-core validation kernel (fp32 dot products): head_dim 64, |i-j| <= window/2,
+// per-utterance boundaries; q, k arrive rotated/scaled as fp16 hi/lo pairs from the QKV epilogue (EPI_QKV).
+// (mha_rope, src/miocodec.cpp:245-286; the reference materialises dense scores with a -inf mask, :233-242 — masked
+// terms are exactly 0 after softmax so the band is identical.)
+// Block: 4 warps, ATT_QB query rows x 1 head; K and V of rows [q0-32, q0+QB+32) staged in smem.
 constexpr int ATT_QB = 32;
 constexpr int ATT_HALF = 32;
 constexpr int ATT_KROWS = ATT_QB + 2 * ATT_HALF;   // 96
 constexpr int ATT_KLD = 65;                        // padded: lane j reads K[j][d] conflict-free
 
+__device__ __forceinline__ float2 ld_hl2(const __half * hi, const __half * lo, size_t idx) {
+    const float2 a = __half22float2(*(const __half2 *) (hi + idx)), b = __half22float2(*(const __half2 *) (lo + idx));
+    return make_float2(a.x + b.x, a.y + b.y);
+}
+
 __global__ void __launch_bounds__(128) attention_kernel(
-        const float * __restrict__ qkv, int rows, int D, int half_w, const float * __restrict__ rope, int rope_max_pos,
+        const __half * __restrict__ qkv_hi, const __half * __restrict__ qkv_lo, int rows, int D, int half_w,
         const int32_t * __restrict__ row_utt, const int32_t * __restrict__ start, const int32_t * __restrict__ len,
         int row_div, __half * __restrict__ out_hi, __half * __restrict__ out_lo) {
     extern __shared__ float att_smem[];
@@ -176,13 +182,8 @@ __global__ void __launch_bounds__(128) attention_kernel(
         if (j >= 0 && j < rows) {
             const int u = row_utt[j / row_div];
             if (u >= 0) {
-                int pos = j - start[u] * row_div;
-                pos = min(pos, rope_max_pos - 1);
-                const float2 cs = *(const float2 *) (rope + ((size_t) pos * 32 + lane) * 2);
-                const float2 kin = *(const float2 *) (qkv + (size_t) j * ld + D + h * 64 + 2 * lane);
-                kk.x = kin.x * cs.x - kin.y * cs.y;
-                kk.y = kin.x * cs.y + kin.y * cs.x;
-                vv = *(const float2 *) (qkv + (size_t) j * ld + 2 * D + h * 64 + 2 * lane);
+                kk = ld_hl2(qkv_hi, qkv_lo, (size_t) j * ld + D + h * 64 + 2 * lane);
+                vv = ld_hl2(qkv_hi, qkv_lo, (size_t) j * ld + 2 * D + h * 64 + 2 * lane);
             }
         }
         Ks[r * ATT_KLD + 2 * lane] = kk.x;
@@ -204,12 +205,10 @@ __global__ void __launch_bounds__(128) attention_kernel(
         }
         const int ustart = start[u] * row_div, uend = ustart + len[u] * row_div;
         {
-            int pos = min(i - ustart, rope_max_pos - 1);
-            const float2 cs = *(const float2 *) (rope + ((size_t) pos * 32 + lane) * 2);
-            const float2 qin = *(const float2 *) (qkv + (size_t) i * ld + h * 64 + 2 * lane);
+            const float2 qin = ld_hl2(qkv_hi, qkv_lo, (size_t) i * ld + h * 64 + 2 * lane);
             __syncwarp();
-            qs[2 * lane] = qin.x * cs.x - qin.y * cs.y;
-            qs[2 * lane + 1] = qin.x * cs.y + qin.y * cs.x;
+            qs[2 * lane] = qin.x;
+            qs[2 * lane + 1] = qin.y;
             __syncwarp();
         }
         // scores for keys i-32+jj, jj = lane, lane+32, lane+64
@@ -223,8 +222,7 @@ __global__ void __launch_bounds__(128) attention_kernel(
             if (valid) {
                 const float * kr = Ks + (j - k_lo) * ATT_KLD;
 #pragma unroll 16
-                for (int d = 0; d < 64; d++) acc += qs[d] * kr[d];
-                acc *= 0.125f;                      // 1/sqrt(64)
+                for (int d = 0; d < 64; d++) acc += qs[d] * kr[d];   // q carries the 1/sqrt(64) factor (EPI_QKV)
             }
             sc[t] = valid ? acc : -INFINITY;
         }
@@ -259,217 +257,22 @@ __global__ void __launch_bounds__(128) attention_kernel(
 }
 
 
-// ---------------------------------------------------------------------------------------------
-// Tensor-core version of the same banded attention (default).  FA2-style: one warp owns 16 query rows and the
-// 80 keys [r0-32, r0+48) that cover their bands; S = Q.K^T and O = P.V run as warp-level m16n8k16 MMAs on
-// fragments with split-precision operands (x = x_hi + x_lo in fp16, three MMAs per product, fp32 accumulate), so
-// the result keeps fp32-class accuracy; softmax is done on the accumulator fragments.
-// Block = 4 warps = 64 queries x 1 head; Q, K (RoPE applied) and V^T are staged once per block as fp16 pairs.
-constexpr int AM_QB = 64;
-constexpr int AM_KR = AM_QB + 64;          // 128 key rows staged
-constexpr int AM_LDQ = 72;                 // padded row strides (halves): fragment loads are bank-conflict free
-constexpr int AM_LDV = AM_KR + 8;          // 136
-constexpr size_t AM_SMEM = (size_t) (2 * AM_QB * AM_LDQ + 2 * AM_KR * AM_LDQ + 2 * 64 * AM_LDV) * sizeof(__half);
-
-__device__ __forceinline__ void mma_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-__device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
-    return (uint32_t) __half_as_ushort(a) | ((uint32_t) __half_as_ushort(b) << 16);
-}
-__device__ __forceinline__ void split_pack(float x0, float x1, uint32_t & hi, uint32_t & lo) {
-    __half h0, l0, h1, l1;
-    split_half(x0, h0, l0);
-    split_half(x1, h1, l1);
-    hi = pack_h2(h0, h1);
-    lo = pack_h2(l0, l1);
-}
-
-__global__ void __launch_bounds__(128, 2) attention_mma_kernel(
-        const float * __restrict__ qkv, int rows, int D, int half_w, const float * __restrict__ rope, int rope_max_pos,
-        const int32_t * __restrict__ row_utt, const int32_t * __restrict__ start, const int32_t * __restrict__ len,
-        int row_div, __half * __restrict__ out_hi, __half * __restrict__ out_lo) {
-    extern __shared__ __align__(16) unsigned char am_smem_raw[];
-    __half * Qh = (__half *) am_smem_raw;           // [64][72]
-    __half * Ql = Qh + AM_QB * AM_LDQ;
-    __half * Kh = Ql + AM_QB * AM_LDQ;              // [128][72]
-    __half * Kl = Kh + AM_KR * AM_LDQ;
-    __half * Vh = Kl + AM_KR * AM_LDQ;              // V^T [64][136]
-    __half * Vl = Vh + 64 * AM_LDV;
-    const int q0 = blockIdx.x * AM_QB;
-    const int h = blockIdx.y;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int ld = 3 * D;
-    const int k_lo = q0 - 32;
-
-    // ---- staging: lane owns the RoPE pair (2*lane, 2*lane+1) of a row
-    for (int r = warp; r < AM_KR; r += 4) {
-        const int j = k_lo + r;
-        float2 kk = make_float2(0.f, 0.f), vv = make_float2(0.f, 0.f), qq = make_float2(0.f, 0.f);
-        const bool is_q = (r >= 32 && r < 32 + AM_QB);
-        if (j >= 0 && j < rows) {
-            const int u = row_utt[j / row_div];
-            if (u >= 0) {
-                const int pos = min(j - start[u] * row_div, rope_max_pos - 1);
-                const float2 cs = *(const float2 *) (rope + ((size_t) pos * 32 + lane) * 2);
-                const float * base = qkv + (size_t) j * ld + h * 64 + 2 * lane;
-                const float2 kin = *(const float2 *) (base + D);
-                kk.x = kin.x * cs.x - kin.y * cs.y;
-                kk.y = kin.x * cs.y + kin.y * cs.x;
-                vv = *(const float2 *) (base + 2 * D);
-                if (is_q) {
-                    const float2 qin = *(const float2 *) base;
-                    qq.x = qin.x * cs.x - qin.y * cs.y;
-                    qq.y = qin.x * cs.y + qin.y * cs.x;
-                }
-            }
-        }
-        uint32_t hi, lo;
-        split_pack(kk.x, kk.y, hi, lo);
-        *(uint32_t *) (Kh + r * AM_LDQ + 2 * lane) = hi;
-        *(uint32_t *) (Kl + r * AM_LDQ + 2 * lane) = lo;
-        if (is_q) {
-            split_pack(qq.x, qq.y, hi, lo);
-            *(uint32_t *) (Qh + (r - 32) * AM_LDQ + 2 * lane) = hi;
-            *(uint32_t *) (Ql + (r - 32) * AM_LDQ + 2 * lane) = lo;
-        }
-        __half h0, l0, h1, l1;
-        split_half(vv.x, h0, l0);
-        split_half(vv.y, h1, l1);
-        Vh[(2 * lane) * AM_LDV + r] = h0; Vh[(2 * lane + 1) * AM_LDV + r] = h1;
-        Vl[(2 * lane) * AM_LDV + r] = l0; Vl[(2 * lane + 1) * AM_LDV + r] = l1;
-    }
-    __syncthreads();
-
-    const int g = lane >> 2, t = lane & 3;
-    const int qr = warp * 16;                       // warp's first query row inside the block
-    const int kw = warp * 16;                       // warp's first key row inside the staged window (query - 32)
-    // ---- S = Q K^T over 10 key tiles of 8
-    float s[10][4];
-#pragma unroll
-    for (int nt = 0; nt < 10; nt++) { s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f; }
-#pragma unroll
-    for (int ks = 0; ks < 4; ks++) {
-        uint32_t ah[4], al[4];
-        const int c = ks * 16 + 2 * t;
-        ah[0] = *(const uint32_t *) (Qh + (qr + g) * AM_LDQ + c);      al[0] = *(const uint32_t *) (Ql + (qr + g) * AM_LDQ + c);
-        ah[1] = *(const uint32_t *) (Qh + (qr + g + 8) * AM_LDQ + c);  al[1] = *(const uint32_t *) (Ql + (qr + g + 8) * AM_LDQ + c);
-        ah[2] = *(const uint32_t *) (Qh + (qr + g) * AM_LDQ + c + 8);  al[2] = *(const uint32_t *) (Ql + (qr + g) * AM_LDQ + c + 8);
-        ah[3] = *(const uint32_t *) (Qh + (qr + g + 8) * AM_LDQ + c + 8); al[3] = *(const uint32_t *) (Ql + (qr + g + 8) * AM_LDQ + c + 8);
-#pragma unroll
-        for (int nt = 0; nt < 10; nt++) {
-            const int kr = kw + nt * 8 + g;
-            const uint32_t bh0 = *(const uint32_t *) (Kh + kr * AM_LDQ + c), bh1 = *(const uint32_t *) (Kh + kr * AM_LDQ + c + 8);
-            const uint32_t bl0 = *(const uint32_t *) (Kl + kr * AM_LDQ + c), bl1 = *(const uint32_t *) (Kl + kr * AM_LDQ + c + 8);
-            mma_16816(s[nt], al, bh0, bh1);
-            mma_16816(s[nt], ah, bl0, bl1);
-            mma_16816(s[nt], ah, bh0, bh1);
-        }
-    }
-    // ---- masked softmax on the fragments: thread holds rows i0 = g, i1 = g+8; key columns nt*8 + 2t, +1
-    const int i0 = q0 + qr + g, i1 = i0 + 8;
-    int us0 = 0, ue0 = 0, us1 = 0, ue1 = 0;
-    bool v0 = false, v1 = false;
-    if (i0 < rows) { const int u = row_utt[i0 / row_div]; if (u >= 0) { v0 = true; us0 = start[u] * row_div; ue0 = us0 + len[u] * row_div; } }
-    if (i1 < rows) { const int u = row_utt[i1 / row_div]; if (u >= 0) { v1 = true; us1 = start[u] * row_div; ue1 = us1 + len[u] * row_div; } }
-    float m0 = -INFINITY, m1 = -INFINITY;
-#pragma unroll
-    for (int nt = 0; nt < 10; nt++) {
-#pragma unroll
-        for (int e = 0; e < 2; e++) {
-            const int j = k_lo + kw + nt * 8 + 2 * t + e;
-            const bool ok0 = v0 && j >= us0 && j < ue0 && j >= i0 - half_w && j <= i0 + half_w;
-            const bool ok1 = v1 && j >= us1 && j < ue1 && j >= i1 - half_w && j <= i1 + half_w;
-            s[nt][e] = ok0 ? s[nt][e] * 0.125f : -INFINITY;
-            s[nt][2 + e] = ok1 ? s[nt][2 + e] * 0.125f : -INFINITY;
-            m0 = fmaxf(m0, s[nt][e]);
-            m1 = fmaxf(m1, s[nt][2 + e]);
-        }
-    }
-    m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)); m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
-    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)); m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
-    float l0 = 0.f, l1 = 0.f;
-#pragma unroll
-    for (int nt = 0; nt < 10; nt++) {
-#pragma unroll
-        for (int e = 0; e < 2; e++) {
-            const float p0 = (s[nt][e] == -INFINITY) ? 0.f : expf(s[nt][e] - m0);
-            const float p1 = (s[nt][2 + e] == -INFINITY) ? 0.f : expf(s[nt][2 + e] - m1);
-            s[nt][e] = p0; s[nt][2 + e] = p1;
-            l0 += p0; l1 += p1;
-        }
-    }
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-    const float inv0 = v0 ? 1.0f / l0 : 0.f, inv1 = v1 ? 1.0f / l1 : 0.f;
-    // ---- O = P V over 5 key steps of 16, 8 d-tiles of 8
-    float o[8][4];
-#pragma unroll
-    for (int nd = 0; nd < 8; nd++) { o[nd][0] = o[nd][1] = o[nd][2] = o[nd][3] = 0.f; }
-#pragma unroll
-    for (int ks = 0; ks < 5; ks++) {
-        uint32_t ph[4], pl[4];
-        split_pack(s[2 * ks][0] * inv0, s[2 * ks][1] * inv0, ph[0], pl[0]);
-        split_pack(s[2 * ks][2] * inv1, s[2 * ks][3] * inv1, ph[1], pl[1]);
-        split_pack(s[2 * ks + 1][0] * inv0, s[2 * ks + 1][1] * inv0, ph[2], pl[2]);
-        split_pack(s[2 * ks + 1][2] * inv1, s[2 * ks + 1][3] * inv1, ph[3], pl[3]);
-        const int kc = kw + ks * 16 + 2 * t;
-#pragma unroll
-        for (int nd = 0; nd < 8; nd++) {
-            const int dr = nd * 8 + g;
-            const uint32_t bh0 = *(const uint32_t *) (Vh + dr * AM_LDV + kc), bh1 = *(const uint32_t *) (Vh + dr * AM_LDV + kc + 8);
-            const uint32_t bl0 = *(const uint32_t *) (Vl + dr * AM_LDV + kc), bl1 = *(const uint32_t *) (Vl + dr * AM_LDV + kc + 8);
-            mma_16816(o[nd], pl, bh0, bh1);
-            mma_16816(o[nd], ph, bl0, bl1);
-            mma_16816(o[nd], ph, bh0, bh1);
-        }
-    }
-    // ---- store split fp16 (pad rows get zeros: inv = 0)
-#pragma unroll
-    for (int nd = 0; nd < 8; nd++) {
-        const int c = h * 64 + nd * 8 + 2 * t;
-        uint32_t hi, lo;
-        if (i0 < rows) {
-            split_pack(o[nd][0], o[nd][1], hi, lo);
-            *(uint32_t *) (out_hi + (size_t) i0 * D + c) = hi;
-            *(uint32_t *) (out_lo + (size_t) i0 * D + c) = lo;
-        }
-        if (i1 < rows) {
-            split_pack(o[nd][2], o[nd][3], hi, lo);
-            *(uint32_t *) (out_hi + (size_t) i1 * D + c) = hi;
-            *(uint32_t *) (out_lo + (size_t) i1 * D + c) = lo;
-        }
-    }
-}
-
 static constexpr size_t ATT_SMEM = (size_t) (ATT_KROWS * ATT_KLD + ATT_KROWS * 64 + 4 * 64) * sizeof(float);
 
-static bool g_attn_simt = false;   // MIO_ATTN=simt selects the CUDA-core validation kernel
-
 cudaError_t attention_init() {
-    const char * e = getenv("MIO_ATTN");
-    g_attn_simt = e && !strcmp(e, "simt");
     cudaError_t ce = cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ATT_SMEM);
     if (ce != cudaSuccess) return ce;
-    return cudaFuncSetAttribute(attention_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) AM_SMEM);
+    return attention_tc_init();
 }
 
-cudaError_t launch_attention(const float * qkv, int rows, int D, int n_head, int window, const float * rope,
-                             int rope_max_pos, const row_map & rm, int row_div, __half * out_hi, __half * out_lo,
-                             cudaStream_t st) {
+// CUDA-core validation kernel (MIO_ATTN=simt); the product path is launch_attention_tc (attention.cu)
+cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, int rows, int D, int n_head, int window,
+                                  const row_map & rm, int row_div, __half * out_hi, __half * out_lo, cudaStream_t st) {
     if (rows <= 0) return cudaSuccess;
     if (D != n_head * 64 || window / 2 != ATT_HALF) return cudaErrorInvalidValue;
-    if (!g_attn_simt) {
-        dim3 gm((rows + AM_QB - 1) / AM_QB, n_head);
-        attention_mma_kernel<<<gm, 128, AM_SMEM, st>>>(qkv, rows, D, window / 2, rope, rope_max_pos, rm.row_utt, rm.start,
-                                                       rm.len, row_div, out_hi, out_lo);
-        return cudaGetLastError();
-    }
     dim3 grid((rows + ATT_QB - 1) / ATT_QB, n_head);
-    attention_kernel<<<grid, 128, ATT_SMEM, st>>>(qkv, rows, D, window / 2, rope, rope_max_pos, rm.row_utt, rm.start,
-                                                  rm.len, row_div, out_hi, out_lo);
+    attention_kernel<<<grid, 128, ATT_SMEM, st>>>(qkv_hi, qkv_lo, rows, D, window / 2, rm.row_utt, rm.start, rm.len, row_div,
+                                                  out_hi, out_lo);
     return cudaGetLastError();
 }
 

@@ -52,28 +52,30 @@ static std::string make_map(CUtensorMap * tm, const __half * base, int rows, int
 
 // output tile map of the generation-3 GEMM epilogue: [rows][cols] elements of `esize` bytes with row pitch ld_bytes,
 // box {32, 32}; fp32 -> SWIZZLE_128B (128-byte box rows), fp16 -> SWIZZLE_64B.  rows == M: the TMA unit clips.
-static std::string make_out_map(CUtensorMap * tm, const void * base, int esize, int rows, int cols, size_t ld_bytes) {
+static std::string make_out_map(CUtensorMap * tm, const void * base, int esize, int rows, int cols, size_t ld_bytes,
+                                int box_c, int box_r) {
     std::string e = get_encode();
     if (!e.empty()) return e;
     if (ld_bytes % 16 != 0 || ((uintptr_t) base & 15) != 0) return "internal: GEMM output not 16-byte aligned for TMA";
     cuuint64_t dims[2] = {(cuuint64_t) cols, (cuuint64_t) rows};
     cuuint64_t strides[1] = {(cuuint64_t) ld_bytes};
-    cuuint32_t box[2] = {32u, 32u};
+    cuuint32_t box[2] = {(cuuint32_t) box_c, (cuuint32_t) box_r};
     cuuint32_t estr[2] = {1u, 1u};
+    if (box_c * esize != 128 && box_c * esize != 64) return "internal: unsupported TMA box width";
     CUresult r = g_encode(tm, esize == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (void *) base,
                           dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                          esize == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                          box_c * esize == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
                           CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return "cuTensorMapEncodeTiled (output) failed (" + std::to_string((int) r) + ")";
     return {};
 }
 
-const CUtensorMap * engine::out_map(const void * base, int esize, int rows, int cols, size_t ld_bytes) {
-    out_map_key k{base, esize, rows, cols, ld_bytes};
+const CUtensorMap * engine::out_map(const void * base, int esize, int rows, int cols, size_t ld_bytes, int box_c, int box_r) {
+    out_map_key k{base, esize, rows, cols, ld_bytes, box_c, box_r};
     auto it = out_maps.find(k);
     if (it != out_maps.end()) return &it->second;
     CUtensorMap tm;
-    std::string e = make_out_map(&tm, base, esize, rows, cols, ld_bytes);
+    std::string e = make_out_map(&tm, base, esize, rows, cols, ld_bytes, box_c, box_r);
     if (!e.empty()) { err = e; return nullptr; }
     if (out_maps.size() > 4096) out_maps.clear();        // bounded: shapes repeat in steady state
     return &(out_maps[k] = tm);
@@ -111,7 +113,7 @@ engine::~engine() {
     cudaSetDevice(device);
     if (stream && own_stream) cudaStreamSynchronize(stream);
     auto F = [](void * p) { if (p) cudaFree(p); };
-    F(x768); F(qkv); F(x512); F(y512); F(x256); F(y256); F(x128); F(y128); F(spec); F(mod); F(peak);
+    F(x768); F(qkv_hi); F(qkv_lo); F(x512); F(y512); F(x256); F(y256); F(x128); F(y128); F(spec); F(mod); F(peak);
     F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_stats); F(err_flag);
     F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_out_off); F(d_voice_table); F(d_wave);
     for (void * p : w_allocs) F(p);
@@ -477,6 +479,7 @@ std::string engine::load(const std::string & path, int dev) {
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     own_stream = true;
     CK(attention_init());
+    { const char * ev = getenv("MIO_ATTN"); attn_simt = ev && !strcmp(ev, "simt"); }
     CK(cudaDeviceSynchronize());
     return {};
 }
@@ -526,7 +529,7 @@ std::string engine::ensure_workspace() {
         ws_ready = true;
         return {};
     }
-    A(x768, R1 * 768); A(qkv, std::max(R1 * 2304, R2 * 1536));
+    A(x768, R1 * 768); A(qkv_hi, std::max(R1 * 2304, R2 * 1536)); A(qkv_lo, std::max(R1 * 2304, R2 * 1536));
     A(x512, R2 * 512); A(y512, R2 * 512); A(x256, R6 * 256); A(y256, R6 * 256); A(x128, R18 * 128); A(y128, R18 * 128);
     A(spec, R18 * SPEC_LD);
     A(aA_hi, R1 * 1024); A(aA_lo, R1 * 1024); A(aFF_hi, R1 * 3072); A(aFF_lo, R1 * 3072);
@@ -801,6 +804,31 @@ std::string engine::run_resblock(const resblock_w & R, float * x, float * y, con
     return {};
 }
 
+// QKV projection epilogue: RoPE on q|k with utterance-relative positions, q / sqrt(head_dim), fp16 hi/lo split
+gemm_params engine::qkv_params(const row_map & rm, int D, int row_div) {
+    gemm_params p;
+    p.epi = EPI_QKV; p.out_hi = qkv_hi; p.out_lo = qkv_lo; p.ld_h = 3 * D;
+    p.row_utt = rm.row_utt; p.row_div = row_div; p.utt_start = rm.start;
+    p.rope = w.rope_pre; p.rope_max_pos = w.rope_max_pos; p.rope_cols = 2 * D; p.q_cols = D; p.q_scale = 0.125f;   // 1/sqrt(64)
+    return p;
+}
+
+// banded attention over the q|k|v written by the QKV epilogue; bytes: 12*D read (hi+lo of q,k,v) + 4*D written per row
+std::string engine::run_attention(int rows, int D, int n_head, int window, int row_div, const a_view & out) {
+    const row_map rm = rmap();
+    if (attn_simt) {
+        CKR(CAT_ATTN, (double) rows * 16.0 * D, launch_attention_simt(qkv_hi, qkv_lo, rows, D, n_head, window, rm, row_div, out.hi, out.lo, stream));
+        return {};
+    }
+    const CUtensorMap * ih = out_map(qkv_hi, 2, rows, 3 * D, (size_t) 3 * D * 2, 64, 64);
+    const CUtensorMap * il = out_map(qkv_lo, 2, rows, 3 * D, (size_t) 3 * D * 2, 64, 64);
+    const CUtensorMap * oh = out_map(out.hi, 2, rows, D, (size_t) D * 2, 64, 16);
+    const CUtensorMap * ol = out_map(out.lo, 2, rows, D, (size_t) D * 2, 64, 16);
+    if (!ih || !il || !oh || !ol) return err;
+    CKR(CAT_ATTN, (double) rows * 16.0 * D, launch_attention_tc(*ih, *il, *oh, *ol, rows, D, n_head, window, rm, row_div, stream));
+    return {};
+}
+
 std::string engine::run_chunk(const chunk_info & c) {
     cur_row0 = c.row0; cur_utt0 = c.utt0; cur_rows1 = c.rows1; cur_n_utts = c.n_utts;
     const row_map rm = rmap();
@@ -818,10 +846,10 @@ std::string engine::run_chunk(const chunk_info & c) {
     for (int i = 0; i < hp.prenet_layers; i++) {
         const prenet_layer_w & l = w.prenet[i];
         CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.an_w, l.an_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
-        p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = qkv; p.ld_out = 3 * D;
+        p = qkv_params(rm, D, 1);
         CKG(gemm(l.qkv, vA768, R1, p));
-        if (i == 0) snap_f32("pre0_qkv", qkv, (size_t) R1 * 3 * D);
-        CKR(CAT_ATTN, (double) (R1) * 16.0 * (D), launch_attention(qkv, R1, D, hp.prenet_heads, hp.prenet_window, w.rope_pre, w.rope_max_pos, rm, 1, vA768.hi, vA768.lo, stream));
+        if (i == 0) snap_f16("pre0_qkv_rope", qkv_hi, qkv_lo, (size_t) R1 * 3 * D);
+        if (!(e = run_attention(R1, D, hp.prenet_heads, hp.prenet_window, 1, vA768)).empty()) return e;
         if (i == 0) snap_f16("pre0_attn", vA768.hi, vA768.lo, (size_t) R1 * D);
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
         CKG(gemm(l.wo, vA768, R1, p));
@@ -859,9 +887,9 @@ std::string engine::run_chunk(const chunk_info & c) {
         const dec_layer_w & l = w.dec[i];
         const int oa = (i * 2 + 0) * 3 * C, of = (i * 2 + 1) * 3 * C;     // shift | scale | gate
         CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, oa, oa + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream));
-        p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = qkv; p.ld_out = 3 * C;
+        p = qkv_params(rm, C, 2);
         CKG(gemm(l.qkv, vA512, R2, p));
-        CKR(CAT_ATTN, (double) (R2) * 16.0 * (C), launch_attention(qkv, R2, C, hp.dec_heads, hp.dec_window, w.rope_pre, w.rope_max_pos, rm, 2, vA512.hi, vA512.lo, stream));
+        if (!(e = run_attention(R2, C, hp.dec_heads, hp.dec_window, 2, vA512)).empty()) return e;
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x512; p.ld_out = C;
         p.gate = mod + oa + 2 * C; p.gate_ld = w.cond_rows; p.row_utt = rm.row_utt; p.row_div = 2; p.gate_voice = rm.voice;
         CKG(gemm(l.wo, vA512, R2, p));
@@ -1020,12 +1048,15 @@ std::string engine::run_istft_only(const float * spec_host, int n_frames) {
         if (!(e = dev_alloc(&d_wave, (size_t) wave_cap)).empty()) return e;
     }
     CK(cudaStreamSynchronize(stream));
-    CK(cudaMemcpy(d_start, &start0, 4, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(d_len, &len0, 4, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(d_out_off, &off0, 8, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(d_chunk_cu, ccu, 8, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy2D(spec, (size_t) SPEC_LD * sizeof(float), spec_host, (size_t) 2 * hp.n_freq * sizeof(float),
-                    (size_t) 2 * hp.n_freq * sizeof(float), (size_t) n_frames, cudaMemcpyHostToDevice));
+    // all copies are ordered on the context stream (a blocking cudaMemcpy from pageable memory may return before
+    // its DMA lands, and the context stream does not synchronise with the legacy default stream)
+    CK(cudaMemcpyAsync(d_start, &start0, 4, cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(d_len, &len0, 4, cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(d_out_off, &off0, 8, cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpyAsync(d_chunk_cu, ccu, 8, cudaMemcpyHostToDevice, stream));
+    CK(cudaMemcpy2DAsync(spec, (size_t) SPEC_LD * sizeof(float), spec_host, (size_t) 2 * hp.n_freq * sizeof(float),
+                         (size_t) 2 * hp.n_freq * sizeof(float), (size_t) n_frames, cudaMemcpyHostToDevice, stream));
+    CK(cudaStreamSynchronize(stream));   // the small host sources above are locals
     istft_params ip;
     ip.spec = spec; ip.spec_ld = SPEC_LD; ip.wave = d_wave; ip.start = d_start; ip.len = d_len; ip.out_off = d_out_off; ip.chunk_cu = d_chunk_cu;
     ip.hann = w.hann; ip.n_utts = 1; ip.frames_per_code = 1; ip.total_chunks = blocks;

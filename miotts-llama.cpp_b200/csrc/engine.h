@@ -30,13 +30,15 @@ struct chunk_info {              // a run of whole utterances that fits the work
 };
 
 struct out_map_key {
-    const void * base; int esize, rows, cols; size_t ld;
+    const void * base; int esize, rows, cols; size_t ld; int box_c, box_r;
     bool operator<(const out_map_key & o) const {
         if (base != o.base) return base < o.base;
         if (esize != o.esize) return esize < o.esize;
         if (rows != o.rows) return rows < o.rows;
         if (cols != o.cols) return cols < o.cols;
-        return ld < o.ld;
+        if (ld != o.ld) return ld < o.ld;
+        if (box_c != o.box_c) return box_c < o.box_c;
+        return box_r < o.box_r;
     }
 };
 
@@ -57,10 +59,11 @@ struct engine {
     int64_t launches = 0;
 
     // ---- workspace (device)
-    float *x768 = nullptr, *qkv = nullptr, *x512 = nullptr, *y512 = nullptr, *x256 = nullptr, *y256 = nullptr,
+    float *x768 = nullptr, *x512 = nullptr, *y512 = nullptr, *x256 = nullptr, *y256 = nullptr,
           *x128 = nullptr, *y128 = nullptr, *spec = nullptr, *mod = nullptr, *peak = nullptr;
     __half *aA_hi = nullptr, *aA_lo = nullptr, *aFF_hi = nullptr, *aFF_lo = nullptr, *c16 = nullptr,
-           *h512_hi = nullptr, *h512_lo = nullptr;
+           *h512_hi = nullptr, *h512_lo = nullptr, *qkv_hi = nullptr, *qkv_lo = nullptr;
+    bool attn_simt = false;           // MIO_ATTN=simt: CUDA-core validation kernel
     double * gn_stats = nullptr;      // [GN_SLOTS][max_utts][32][2]
     int * err_flag = nullptr;
     a_view vA768, vA512, vFF2048, vFF1536, vFF256, vFF128, vFF512, vC512, vC256, vC128, vH512;
@@ -109,7 +112,10 @@ struct engine {
     std::string view512_ff(a_view & v);
     cudaError_t gemm(const gemm_weight & W, const a_view & A, int M, gemm_params p);
     std::map<out_map_key, CUtensorMap> out_maps;          // TMA maps of GEMM outputs, keyed by (buffer, shape)
-    const CUtensorMap * out_map(const void * base, int esize, int rows, int cols, size_t ld_bytes);
+    // box {box_c, box_r}; swizzle = box_c * esize (128-byte or 64-byte box rows)
+    const CUtensorMap * out_map(const void * base, int esize, int rows, int cols, size_t ld_bytes, int box_c = 32, int box_r = 32);
+    gemm_params qkv_params(const row_map & rm, int D, int row_div);
+    std::string run_attention(int rows, int D, int n_head, int window, int row_div, const a_view & out);
     // profiling
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events; size_t prof_used = 0;

@@ -114,6 +114,32 @@ __device__ __forceinline__ void gemm_epilogue(const gemm_params & p, int row, in
                 for (int i = 0; i < NC && col0 + i < p.N; i++) { oh[i] = hi[i]; ol[i] = lo[i]; }
             }
         }
+    } else if constexpr (EPI == EPI_QKV) {
+        // RoPE (adjacent pairs, utterance-relative position) on q|k, q pre-scaled, split fp16 (see gemm3.cu)
+        if (col0 < p.rope_cols) {
+            const int u = p.row_utt[row / p.row_div];
+            if (u >= 0) {
+                const int pos = min(row - p.utt_start[u] * p.row_div, p.rope_max_pos - 1);
+                const float qs = (col0 < p.q_cols) ? p.q_scale : 1.0f;
+#pragma unroll
+                for (int i = 0; i < NC; i += 2) {
+                    const float2 cs = __ldg((const float2 *) (p.rope + ((size_t) pos * 32 + (((col0 + i) & 63) >> 1)) * 2));
+                    const float x0 = v[i], x1 = v[i + 1];
+                    v[i] = (x0 * cs.x - x1 * cs.y) * qs;
+                    v[i + 1] = (x0 * cs.y + x1 * cs.x) * qs;
+                }
+            }
+        }
+        __half hi[NC], lo[NC];
+#pragma unroll
+        for (int i = 0; i < NC; i++) split_half2(v[i], hi[i], lo[i]);
+        __half * oh = p.out_hi + (size_t) row * p.ld_h + col0;
+        __half * ol = p.out_lo + (size_t) row * p.ld_h + col0;
+#pragma unroll
+        for (int i = 0; i < NC; i += 4) {
+            *(uint2 *) (oh + i) = *(uint2 *) (hi + i);
+            *(uint2 *) (ol + i) = *(uint2 *) (lo + i);
+        }
     } else if constexpr (EPI == EPI_HEAD) {
         // (log-magnitude, phase) interleaved -> (re, im)  (src/miocodec.cpp:732-737)
         float * o = p.out_f32 + (size_t) row * p.ld_out + col0;
@@ -273,6 +299,7 @@ static cudaError_t launch_tc_epi(const gemm_params & p, const CUtensorMap & a_hi
             case EPI_SPLIT: return launch_tc_inst<BN, 3, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, st);
             case EPI_SNAKE: return launch_tc_inst<BN, 3, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, st);
             case EPI_HEAD: return launch_tc_inst<BN, 3, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, st);
+            case EPI_QKV: return launch_tc_inst<BN, 3, EPI_QKV>(p, a_hi, a_lo, b_hi, b_lo, st);
             default: break;
         }
     }
@@ -491,6 +518,7 @@ static cudaError_t launch_tc2_epi(const gemm_params & p, const CUtensorMap & a_h
             case EPI_SPLIT: return launch_tc2_inst<BN, 3, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, st);
             case EPI_SNAKE: return launch_tc2_inst<BN, 3, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, st);
             case EPI_HEAD: return launch_tc2_inst<BN, 3, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, st);
+            case EPI_QKV: return launch_tc2_inst<BN, 3, EPI_QKV>(p, a_hi, a_lo, b_hi, b_lo, st);
             default: break;
         }
     }
@@ -583,6 +611,7 @@ cudaError_t launch_gemm_simt(const gemm_params & p, cudaStream_t st) {
         case EPI_SPLIT: gemm_simt_kernel<EPI_SPLIT><<<grid, 256, 0, st>>>(p); break;
         case EPI_SNAKE: gemm_simt_kernel<EPI_SNAKE><<<grid, 256, 0, st>>>(p); break;
         case EPI_HEAD: gemm_simt_kernel<EPI_HEAD><<<grid, 256, 0, st>>>(p); break;
+        case EPI_QKV: gemm_simt_kernel<EPI_QKV><<<grid, 256, 0, st>>>(p); break;
         default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

@@ -73,11 +73,15 @@ cudaError_t launch_gather(const float * table, const int32_t * codes_padded, flo
 cudaError_t launch_layernorm(const float * x, int rows, int D, float eps, const float * w, const float * b,
                              const float * mod, int mod_ld, int shift_off, int scale_off, const row_map & rm, int row_div,
                              __half * out_hi, __half * out_lo, float * out_f32, cudaStream_t st);
-// banded local attention with RoPE (adjacent pairs) on q,k. qkv: [rows][3*D] fp32; out: split fp16 [rows][D]
-cudaError_t launch_attention(const float * qkv, int rows, int D, int n_head, int window, const float * rope,
-                             int rope_max_pos, const row_map & rm, int row_div, __half * out_hi, __half * out_lo,
-                             cudaStream_t st);
+// banded local attention on the rotated / scaled / split q|k|v written by EPI_QKV.  qkv_*: [rows][3*D] fp16;
+// out: split fp16 [rows][D].  _tc: TMA + ldmatrix + warp MMA (attention.cu, product path); _simt: fp32 validation.
+cudaError_t launch_attention_tc(const CUtensorMap & tm_in_hi, const CUtensorMap & tm_in_lo, const CUtensorMap & tm_out_hi,
+                                const CUtensorMap & tm_out_lo, int rows, int D, int n_head, int window, const row_map & rm,
+                                int row_div, cudaStream_t st);
+cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, int rows, int D, int n_head, int window,
+                                  const row_map & rm, int row_div, __half * out_hi, __half * out_lo, cudaStream_t st);
 cudaError_t attention_init();
+cudaError_t attention_tc_init();
 // GroupNorm statistics: stats[utt][32][2] (sum, sum of squares; double), rows at resolution row_div
 cudaError_t launch_gn_stats(const float * x, int rows, int C, const row_map & rm, int row_div, double * stats,
                             cudaStream_t st);

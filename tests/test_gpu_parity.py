@@ -84,7 +84,7 @@ def test_stages_before_first_conv_are_fp32_accurate(assets, weights, mode):
     c.decode_wave(codes, emb)
     T = len(codes)
     lim = {"tc3": 90.0, "tc2": 90.0, "tc1": 90.0, "simt": 105.0}[mode]
-    for name, r in [("embed", 1), ("pre0_qkv", 1), ("pre0_attn", 1), ("pre0_out", 1), ("prenet_out", 1), ("upsample", 2)]:
+    for name, r in [("embed", 1), ("pre0_qkv_rope", 1), ("pre0_attn", 1), ("pre0_out", 1), ("prenet_out", 1), ("upsample", 2)]:
         got = c.debug_read(name).reshape(-1, inter[name].shape[1])[: T * r]
         s = snr_db(got, inter[name])
         print(f"{mode} {name}: {s:.1f} dB")
@@ -165,6 +165,21 @@ def test_simt_and_tensor_core_paths_agree(assets, codec):
     from miocodec_b200 import binding, synth
     codes, emb = synth.synth_codes(50, 8), _voice(2)
     simt = binding.MioCodec(assets[0], 0, gemm="simt")
+    a, b = simt.decode_wave(codes, emb), codec.decode_wave(codes, emb)
+    assert snr_db(b, a) > WAVE_SNR_MIN
+    simt.close()
+
+
+def test_attention_validation_kernel_agrees(assets, codec):
+    """MIO_ATTN=simt selects the fp32 CUDA-core attention; the TMA + ldmatrix + warp-MMA kernel must agree with it."""
+    import os
+    from miocodec_b200 import binding, synth
+    codes, emb = synth.synth_codes(150, 9), _voice(1)
+    os.environ["MIO_ATTN"] = "simt"
+    try:
+        simt = binding.MioCodec(assets[0], 0)
+    finally:
+        del os.environ["MIO_ATTN"]
     a, b = simt.decode_wave(codes, emb), codec.decode_wave(codes, emb)
     assert snr_db(b, a) > WAVE_SNR_MIN
     simt.close()

@@ -40,7 +40,7 @@ def main():
     t0 = time.time()
     wave = c.decode_wave(codes, emb)
     print(f"[{mode}] decode_wave T={T}: {time.time() - t0:.3f}s launches={c.kernel_launches()}", flush=True)
-    res = {"embed": 1, "pre0_qkv": 1, "pre0_attn": 1, "pre0_x_attn": 1, "pre0_out": 1, "prenet_x": 1, "prenet_out": 1,
+    res = {"embed": 1, "pre0_qkv_rope": 1, "pre0_attn": 1, "pre0_x_attn": 1, "pre0_out": 1, "prenet_x": 1, "prenet_out": 1,
            "upsample": 2, "prior": 2, "dec0_out": 2, "decoder_x": 2, "final_norm": 2, "post": 2, "up0_snake": 6, "up0": 6,
            "up1": 18, "spec": 18}
     for name, r in res.items():
