@@ -198,6 +198,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gemm", default=None)
+    ap.add_argument("--chunk", type=int, default=None, help="max_chunk_codes of the context (workspace rows)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 0)
     if args.impl == "reference":
@@ -221,7 +222,7 @@ def main():
     gguf, _ = synth.ensure_assets()
     if world > 1:
         dist.barrier()
-    codec = binding.MioCodec(gguf, local, gemm=args.gemm)
+    codec = binding.MioCodec(gguf, local, gemm=args.gemm, max_chunk_codes=args.chunk)
     stream = torch.cuda.current_stream()
     codec.set_stream(stream.cuda_stream)
     wl = make_workload(args.workload, rank, world)

@@ -31,7 +31,7 @@ __device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
 }
 __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+    asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                  : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
@@ -102,19 +102,21 @@ __global__ void __launch_bounds__(128, 2) attention_tc_kernel(
             ldsm_x4(ah, sQh + sw128(r, c));
             ldsm_x4(al, sQl + sw128(r, c));
         }
+        // all ten key tiles of this k-step first, then three passes over ten independent accumulators (the three
+        // MMAs that feed one accumulator are ten instructions apart, so the tensor pipe never waits on a dependency)
+        uint32_t bh[5][4], bl[5][4];
 #pragma unroll
         for (int np = 0; np < 5; np++) {            // pairs of key tiles
-            uint32_t bh[4], bl[4];
             const int r = kw + np * 16 + (lane & 7) + ((lane >> 4) & 1) * 8, c = 2 * ks + ((lane >> 3) & 1);
-            ldsm_x4(bh, sKh + sw128(r, c));
-            ldsm_x4(bl, sKl + sw128(r, c));
-            mma16816(s[2 * np], al, bh[0], bh[1]);
-            mma16816(s[2 * np], ah, bl[0], bl[1]);
-            mma16816(s[2 * np], ah, bh[0], bh[1]);
-            mma16816(s[2 * np + 1], al, bh[2], bh[3]);
-            mma16816(s[2 * np + 1], ah, bl[2], bl[3]);
-            mma16816(s[2 * np + 1], ah, bh[2], bh[3]);
+            ldsm_x4(bh[np], sKh + sw128(r, c));
+            ldsm_x4(bl[np], sKl + sw128(r, c));
         }
+#pragma unroll
+        for (int np = 0; np < 5; np++) { mma16816(s[2 * np], al, bh[np][0], bh[np][1]); mma16816(s[2 * np + 1], al, bh[np][2], bh[np][3]); }
+#pragma unroll
+        for (int np = 0; np < 5; np++) { mma16816(s[2 * np], ah, bl[np][0], bl[np][1]); mma16816(s[2 * np + 1], ah, bl[np][2], bl[np][3]); }
+#pragma unroll
+        for (int np = 0; np < 5; np++) { mma16816(s[2 * np], ah, bh[np][0], bh[np][1]); mma16816(s[2 * np + 1], ah, bh[np][2], bh[np][3]); }
     }
     // ---- masked softmax on the fragments (softmax over keys: subtract row max, expf, normalise; ops.cpp:5286-5323)
     float m0 = -INFINITY, m1 = -INFINITY;
@@ -158,19 +160,19 @@ __global__ void __launch_bounds__(128, 2) attention_tc_kernel(
         split_pack2(s[2 * ks][2] * inv1, s[2 * ks][3] * inv1, ph[1], pl[1]);
         split_pack2(s[2 * ks + 1][0] * inv0, s[2 * ks + 1][1] * inv0, ph[2], pl[2]);
         split_pack2(s[2 * ks + 1][2] * inv1, s[2 * ks + 1][3] * inv1, ph[3], pl[3]);
+        uint32_t bh[4][4], bl[4][4];
 #pragma unroll
         for (int dp = 0; dp < 4; dp++) {            // pairs of d tiles
-            uint32_t bh[4], bl[4];
             const int r = kw + ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, c = 2 * dp + (lane >> 4);
-            ldsm_x4_t(bh, sVh + sw128(r, c));
-            ldsm_x4_t(bl, sVl + sw128(r, c));
-            mma16816(o[2 * dp], pl, bh[0], bh[1]);
-            mma16816(o[2 * dp], ph, bl[0], bl[1]);
-            mma16816(o[2 * dp], ph, bh[0], bh[1]);
-            mma16816(o[2 * dp + 1], pl, bh[2], bh[3]);
-            mma16816(o[2 * dp + 1], ph, bl[2], bl[3]);
-            mma16816(o[2 * dp + 1], ph, bh[2], bh[3]);
+            ldsm_x4_t(bh[dp], sVh + sw128(r, c));
+            ldsm_x4_t(bl[dp], sVl + sw128(r, c));
         }
+#pragma unroll
+        for (int dp = 0; dp < 4; dp++) { mma16816(o[2 * dp], pl, bh[dp][0], bh[dp][1]); mma16816(o[2 * dp + 1], pl, bh[dp][2], bh[dp][3]); }
+#pragma unroll
+        for (int dp = 0; dp < 4; dp++) { mma16816(o[2 * dp], ph, bl[dp][0], bl[dp][1]); mma16816(o[2 * dp + 1], ph, bl[dp][2], bl[dp][3]); }
+#pragma unroll
+        for (int dp = 0; dp < 4; dp++) { mma16816(o[2 * dp], ph, bh[dp][0], bh[dp][1]); mma16816(o[2 * dp + 1], ph, bh[dp][2], bh[dp][3]); }
     }
     // ---- split to fp16 hi/lo into the warp's own Q rows (dead since the S loop), then two TMA stores
     __syncwarp();

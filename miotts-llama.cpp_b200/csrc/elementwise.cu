@@ -279,8 +279,9 @@ cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, 
 // ---------------------------------------------------------------------------------------------
 // GroupNorm statistics over (all rows of an utterance) x (C/32 channels)
 // (conv_group_norm, src/miocodec.cpp:358-371; ggml_compute_forward_group_norm_f32, ggml-cpu/ops.cpp:3955-4028).
-// Block = C/4 threads (one float4 of channels each) x GN_ROWS rows; partial sums are flushed with fp64 atomics
-// whenever the utterance changes inside the chunk.
+// Block = C/4 threads (one float4 of channels each) x GN_ROWS rows, read 8 rows at a time so eight independent
+// 16-byte loads are in flight per thread; partial sums are flushed with fp64 atomics whenever the utterance changes
+// inside the block's rows.
 constexpr int GN_ROWS = 64;
 
 __global__ void gn_stats_kernel(const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt,
@@ -305,16 +306,21 @@ __global__ void gn_stats_kernel(const float * __restrict__ x, int rows, int C, c
         }
         s = 0.f; q = 0.f;
     };
-    for (int r = r0; r < r1; r++) {
-        const int u = row_utt[r / row_div];        // block-uniform
-        if (u != cur) {
-            flush(cur);
-            cur = u;
+    for (int rb = r0; rb < r1; rb += 8) {
+        float4 v[8];
+        int uu[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const int r = rb + k;
+            uu[k] = (r < r1) ? row_utt[r / row_div] : -2;      // block-uniform; -2 = past the end
+            v[k] = (uu[k] >= 0) ? __ldg((const float4 *) (x + (size_t) r * C + c4 * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        if (u >= 0) {
-            const float4 v = *(const float4 *) (x + (size_t) r * C + c4 * 4);
-            s += (v.x + v.y) + (v.z + v.w);
-            q += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            if (uu[k] == -2) break;
+            if (uu[k] != cur) { flush(cur); cur = uu[k]; }
+            s += (v[k].x + v[k].y) + (v[k].z + v[k].w);
+            q += (v[k].x * v[k].x + v[k].y * v[k].y) + (v[k].z * v[k].z + v[k].w * v[k].w);
         }
     }
     flush(cur);
@@ -330,48 +336,58 @@ cudaError_t launch_gn_stats(const float * x, int rows, int C, const row_map & rm
 
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
 
+// (sum, sum of squares) in fp64 -> (mean, 1/sqrt(var + eps)) in fp32, once per (utterance, group): keeps the fp64
+// arithmetic (slow on this part) out of the per-element kernel.  var = sum((x-mean)^2)/n with the float-rounded
+// mean, like the reference's second pass (ops.cpp:3990-4010).
+__global__ void gn_finalize_kernel(const double * __restrict__ stats, const int32_t * __restrict__ len, int n_utts, int row_div,
+                                   int cpg, float eps, float2 * __restrict__ mr) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n_utts * 32) return;
+    const int u = idx >> 5;
+    const double n = (double) len[u] * row_div * cpg;
+    const double sum = stats[(size_t) idx * 2], sq = stats[(size_t) idx * 2 + 1];
+    const float mean = (float) (sum / n);
+    const double md = (double) mean;
+    const float var = (float) ((sq - 2.0 * md * sum) / n + md * md);
+    mr[idx] = make_float2(mean, 1.0f / sqrtf(var + eps));
+}
+
 // GroupNorm apply + SiLU + round to fp16 (the conv operand: ggml_conv_1d's im2col rounds activations to F16,
 // ggml-cpu/ops.cpp:6232-6256, so this rounding is the reference's own, not an approximation).
-__global__ void gn_apply_silu_kernel(const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt,
-                                     const int32_t * __restrict__ len, int row_div, const double * __restrict__ stats,
-                                     float eps, const float * __restrict__ w, const float * __restrict__ b,
-                                     __half * __restrict__ out) {
-    const int C4 = C / 4;
-    const size_t total = (size_t) rows * C4;
+// One thread = 8 channels of one row (two float4 loads, one 16-byte store).
+__global__ void __launch_bounds__(256) gn_apply_silu_kernel(
+        const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt, int row_div,
+        const float2 * __restrict__ mr, const float * __restrict__ w, const float * __restrict__ b, __half * __restrict__ out) {
+    const int C8 = C / 8;
+    const size_t total = (size_t) rows * C8;
     const int cpg = C / 32;
     for (size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t) gridDim.x * blockDim.x) {
-        const int r = (int) (idx / C4);
-        const int c = (int) (idx % C4) * 4;
+        const int r = (int) (idx / C8);
+        const int c = (int) (idx - (size_t) r * C8) * 8;
         const int u = row_utt[r / row_div];
-        __half h[4];
-        if (u < 0) {
-            h[0] = h[1] = h[2] = h[3] = __float2half_rn(0.f);
-        } else {
-            const int g = c / cpg;
-            const double n = (double) len[u] * row_div * cpg;
-            const double sum = stats[((size_t) u * 32 + g) * 2], sq = stats[((size_t) u * 32 + g) * 2 + 1];
-            const float mean = (float) (sum / n);
-            // sum((x-mean)^2)/n with the float-rounded mean, like the reference's second pass
-            const double md = (double) mean;
-            const float var = (float) ((sq - 2.0 * md * sum) / n + md * md);
-            const float rstd = 1.0f / sqrtf(var + eps);
-            const float4 v = *(const float4 *) (x + (size_t) r * C + c);
-            const float4 ww = *(const float4 *) (w + c), bb = *(const float4 *) (b + c);
-            h[0] = __float2half_rn(silu_f((v.x - mean) * rstd * ww.x + bb.x));
-            h[1] = __float2half_rn(silu_f((v.y - mean) * rstd * ww.y + bb.y));
-            h[2] = __float2half_rn(silu_f((v.z - mean) * rstd * ww.z + bb.z));
-            h[3] = __float2half_rn(silu_f((v.w - mean) * rstd * ww.w + bb.w));
+        uint4 o = make_uint4(0u, 0u, 0u, 0u);
+        if (u >= 0) {
+            const float4 v0 = __ldg((const float4 *) (x + (size_t) r * C + c)), v1 = __ldg((const float4 *) (x + (size_t) r * C + c + 4));
+            const float4 w0 = __ldg((const float4 *) (w + c)), w1 = __ldg((const float4 *) (w + c + 4));
+            const float4 b0 = __ldg((const float4 *) (b + c)), b1 = __ldg((const float4 *) (b + c + 4));
+            const float2 m0 = __ldg(mr + (size_t) u * 32 + c / cpg), m1 = __ldg(mr + (size_t) u * 32 + (c + 4) / cpg);
+            const __half2 h0 = __floats2half2_rn(silu_f((v0.x - m0.x) * m0.y * w0.x + b0.x), silu_f((v0.y - m0.x) * m0.y * w0.y + b0.y));
+            const __half2 h1 = __floats2half2_rn(silu_f((v0.z - m0.x) * m0.y * w0.z + b0.z), silu_f((v0.w - m0.x) * m0.y * w0.w + b0.w));
+            const __half2 h2 = __floats2half2_rn(silu_f((v1.x - m1.x) * m1.y * w1.x + b1.x), silu_f((v1.y - m1.x) * m1.y * w1.y + b1.y));
+            const __half2 h3 = __floats2half2_rn(silu_f((v1.z - m1.x) * m1.y * w1.z + b1.z), silu_f((v1.w - m1.x) * m1.y * w1.w + b1.w));
+            o = make_uint4(*(const uint32_t *) &h0, *(const uint32_t *) &h1, *(const uint32_t *) &h2, *(const uint32_t *) &h3);
         }
-        *(uint2 *) (out + (size_t) r * C + c) = *(uint2 *) h;
+        *(uint4 *) (out + (size_t) r * C + c) = o;
     }
 }
 
 cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double * stats,
-                                 float eps, const float * w, const float * b, __half * out, cudaStream_t st) {
+                                 float eps, const float * w, const float * b, float2 * mr_scratch, __half * out, cudaStream_t st) {
     if (rows <= 0) return cudaSuccess;
-    const size_t total = (size_t) rows * (C / 4);
+    gn_finalize_kernel<<<(rm.n_utts * 32 + 255) / 256, 256, 0, st>>>(stats, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
+    const size_t total = (size_t) rows * (C / 8);
     const int grid = (int) min((size_t) 148 * 16, (total + 255) / 256);
-    gn_apply_silu_kernel<<<grid, 256, 0, st>>>(x, rows, C, rm.row_utt, rm.len, row_div, stats, eps, w, b, out);
+    gn_apply_silu_kernel<<<grid, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out);
     return cudaGetLastError();
 }
 

@@ -114,7 +114,7 @@ engine::~engine() {
     if (stream && own_stream) cudaStreamSynchronize(stream);
     auto F = [](void * p) { if (p) cudaFree(p); };
     F(x768); F(qkv_hi); F(qkv_lo); F(x512); F(y512); F(x256); F(y256); F(x128); F(y128); F(spec); F(mod); F(peak);
-    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_stats); F(err_flag);
+    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_stats); F(gn_mr); F(err_flag);
     F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_out_off); F(d_voice_table); F(d_wave);
     for (void * p : w_allocs) F(p);
     F(d_emit); F(d_emit_jobs);
@@ -535,6 +535,7 @@ std::string engine::ensure_workspace() {
     A(aA_hi, R1 * 1024); A(aA_lo, R1 * 1024); A(aFF_hi, R1 * 3072); A(aFF_lo, R1 * 3072);
     A(c16, R1 * 2304); A(h512_hi, R18 * 512); A(h512_lo, R18 * 512);
     A(gn_stats, (size_t) GN_SLOTS * max_utts * 64);
+    A(gn_mr, (size_t) max_utts * 32);
     A(mod, (size_t) max_voices * w.cond_rows);
     A(peak, (size_t) max_utts);
     A(err_flag, 1);
@@ -793,12 +794,12 @@ std::string engine::run_resblock(const resblock_w & R, float * x, float * y, con
     gemm_params p;
     // GN -> SiLU -> conv1 + bias
     CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(x, rows, C, rm, row_div, st1, stream));
-    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(x, rows, C, rm, row_div, st1, hp.gn_eps, R.n1w, R.n1b, vc.hi, stream));
+    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(x, rows, C, rm, row_div, st1, hp.gn_eps, R.n1w, R.n1b, gn_mr, vc.hi, stream)); launches++;
     p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = y; p.ld_out = C; p.bias = R.c1b;
     CKG(gemm(R.c1, vc, rows, p));
     // GN -> SiLU -> conv2 + bias + residual
     CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(y, rows, C, rm, row_div, st2, stream));
-    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(y, rows, C, rm, row_div, st2, hp.gn_eps, R.n2w, R.n2b, vc.hi, stream));
+    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(y, rows, C, rm, row_div, st2, hp.gn_eps, R.n2w, R.n2b, gn_mr, vc.hi, stream)); launches++;
     p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x; p.ld_out = C; p.bias = R.c2b;
     CKG(gemm(R.c2, vc, rows, p));
     return {};

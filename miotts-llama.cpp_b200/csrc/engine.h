@@ -50,7 +50,7 @@ struct engine {
     bool own_stream = false;
     bool use_simt = false;
     int gemm_gen = 3;                // 1: one CTA per tile; 2: persistent CTA pairs (cta_group::2); 3: + TMA-store epilogue (default)
-    int max_rows1 = 16384 + 512;     // workspace rows at code resolution (codes + pad rows)
+    int max_rows1 = 65536 + 4096;    // workspace rows at code resolution (codes + one pad row per utterance), ~8.5 GB
     bool ws_ready = false;
     bool istft_only = false;         // created by mio_istft_ctx_create: no decoder weights, ISTFT workspace only
     bool debug_snap = false;
@@ -65,6 +65,7 @@ struct engine {
            *h512_hi = nullptr, *h512_lo = nullptr, *qkv_hi = nullptr, *qkv_lo = nullptr;
     bool attn_simt = false;           // MIO_ATTN=simt: CUDA-core validation kernel
     double * gn_stats = nullptr;      // [GN_SLOTS][max_utts][32][2]
+    float2 * gn_mr = nullptr;         // [max_utts][32] (mean, rstd) of the GroupNorm being applied
     int * err_flag = nullptr;
     a_view vA768, vA512, vFF2048, vFF1536, vFF256, vFF128, vFF512, vC512, vC256, vC128, vH512;
     bool vFF512_ready = false;

@@ -123,8 +123,8 @@ __device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int c
             for (int i = 0; i < 32; i++) {
                 if (full || col0 + i < p.N) {
                     const float ea = __ldg(p.snake_ea + cb + i), eb = __ldg(p.snake_eb + cb + i);
-                    const float s = sinf(v[i] * ea);
-                    v[i] = v[i] + (s * s) / eb;
+                    const float s = fast_sinf(v[i] * ea);
+                    v[i] = v[i] + __fdividef(s * s, eb);
                 }
             }
         }
@@ -142,7 +142,7 @@ __device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int c
         for (int i = 0; i < 32; i += 2) {
             const float mag = fminf(fmaxf(expf(v[i]), 0.0f), 100.0f);
             float sn, cs;
-            sincosf(v[i + 1], &sn, &cs);
+            fast_sincosf(v[i + 1], &sn, &cs);
             v[i] = mag * cs;
             v[i + 1] = mag * sn;
         }

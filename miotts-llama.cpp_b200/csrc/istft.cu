@@ -3,13 +3,16 @@
 // Replaces istft() / irfft() of the reference (src/istft.cpp:43-108).  Each spectrogram frame is read once from
 // HBM (plus a 4-frame halo per block) and each output sample is written exactly once.
 //
-// Block = 128 threads.  A block produces ISTFT_SEG_PER_BLOCK output hops (98 samples each) of one utterance and
+// Block = 256 threads.  A block produces ISTFT_SEG_PER_BLOCK output hops (98 samples each) of one utterance and
 // therefore needs the frames g0-2 .. g0+G+1 (G+4 = 32 frame slots in shared memory, 1680 B each).
-//   phase 0: cooperative coalesced load of the spectra into the slots
-//   phase 1: every 14-lane group transforms one frame in place (2 frames per warp at a time)
+//   phase 0: one bulk async copy (cp.async.bulk, 1600 B = one padded spectrogram row) per frame, issued by the lanes
+//            of warp 0 behind one mbarrier: no per-element load instructions, all rows in flight at once
+//   phase 1: every 16-lane group (14 active lanes) transforms one frame in place, 16 frames at a time
 //   phase 2: each output sample sums its <= 4 windowed contributions in ascending frame order (the order of the
 //            reference's accumulation loop, src/istft.cpp:84-93), divides by the window-square sum and is stored.
+// The kernel is instruction-bound (about 350 warp instructions per frame for the FFT), not HBM-bound: see DESIGN.md.
 #include "kernels.cuh"
+#include "ptx.cuh"
 #include "istft_math.h"
 
 namespace mio {
@@ -18,15 +21,24 @@ constexpr int IST_NFFT = 392, IST_HOP = 98, IST_NFREQ = 197, IST_PAD = 147;
 constexpr int IST_G = ISTFT_SEG_PER_BLOCK;
 constexpr int IST_SLOTS = IST_G + 4;                       // 32
 constexpr int IST_SLOT_FLOATS = 2 * IFFT_SLOT_F2;          // 420
-constexpr size_t IST_SMEM = (size_t) (IST_SLOTS * IST_SLOT_FLOATS + 2 * 196 * 2 + IST_NFFT) * sizeof(float);
+constexpr int IST_THREADS = 256;
+constexpr size_t IST_SMEM = (size_t) (IST_SLOTS * IST_SLOT_FLOATS + 2 * 196 * 2 + IST_NFFT + 100) * sizeof(float) + 16;
 
-__global__ void __launch_bounds__(128) istft_kernel(istft_params p, const float * __restrict__ tw392g,
-                                                    const float * __restrict__ tw196g) {
-    extern __shared__ float ist_smem[];
+__device__ __forceinline__ void bulk_load_1d(void * dst, const void * src, uint32_t bytes, uint64_t * bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+__global__ void __launch_bounds__(IST_THREADS) istft_kernel(istft_params p, const float * __restrict__ tw392g,
+                                                            const float * __restrict__ tw196g) {
+    extern __shared__ __align__(16) float ist_smem[];
     float * slots = ist_smem;
     float * tw392 = slots + IST_SLOTS * IST_SLOT_FLOATS;
     float * tw196 = tw392 + 2 * 196;
     float * hann = tw196 + 2 * 196;
+    float * wsum4 = hann + IST_NFFT;                       // [98] envelope of interior samples
+    uint64_t * bar = (uint64_t *) (wsum4 + 100);
 
     // block -> (utterance, chunk)
     int lo = 0, hi = p.n_utts;                             // largest u with chunk_cu[u] <= blockIdx.x
@@ -42,28 +54,36 @@ __global__ void __launch_bounds__(128) istft_kernel(istft_params p, const float 
     const int f_lo = max(0, g0 - 2), f_hi = min(F, g1 + 2);   // frames needed [f_lo, f_hi)
     const int nfr = f_hi - f_lo;
     const float * spec = p.spec + ((size_t) p.start[u] * p.frames_per_code + f_lo) * p.spec_ld;
+    const uint32_t row_bytes = (uint32_t) p.spec_ld * 4u;  // 1600: whole padded row, multiple of 16
 
-    for (int i = threadIdx.x; i < 2 * 196; i += blockDim.x) { tw392[i] = tw392g[i]; tw196[i] = tw196g[i]; }
-    for (int i = threadIdx.x; i < IST_NFFT; i += blockDim.x) hann[i] = p.hann[i];
-    // phase 0: frame rows are spec_ld floats apart (8-byte aligned) -> float2 stream
-    {
-        const float2 * src = (const float2 *) spec;
-        const int total = nfr * IST_NFREQ;
-        const int ld2 = p.spec_ld >> 1;
-        for (int i = threadIdx.x; i < total; i += blockDim.x) {
-            const int fr = i / IST_NFREQ, k = i - fr * IST_NFREQ;
-            const float2 v = __ldg(src + (size_t) fr * ld2 + k);
-            *(float2 *) (slots + fr * IST_SLOT_FLOATS + 2 * k) = v;
-        }
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_expect_tx(bar, (uint32_t) nfr * row_bytes);
     }
     __syncthreads();
+    if (threadIdx.x < nfr) bulk_load_1d(slots + threadIdx.x * IST_SLOT_FLOATS, spec + (size_t) threadIdx.x * p.spec_ld, row_bytes, bar);
+    // tables while the rows fly
+    for (int i = threadIdx.x; i < 2 * 196; i += IST_THREADS) { tw392[i] = tw392g[i]; tw196[i] = tw196g[i]; }
+    for (int i = threadIdx.x; i < IST_NFFT; i += IST_THREADS) hann[i] = p.hann[i];
+    __syncthreads();
+    if (threadIdx.x < IST_HOP) {
+        // interior envelope: the four overlapping frames in ascending frame order == descending window index
+        const int r = threadIdx.x;
+        const int j0 = (r < 49) ? r + 343 : r + 245;
+        float ws = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; k++) { const float w = hann[j0 - 98 * k]; ws += w * w; }
+        wsum4[r] = ws;
+    }
+    mbar_wait(bar, 0);
 
     // phase 1
     {
-        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-        const int sub = lane >> 4, t14 = lane & 15;        // two 14-lane groups per warp
-        for (int base = 0; base < IST_SLOTS; base += 8) {
-            const int fr = base + warp * 2 + sub;
+        const int grp = threadIdx.x >> 4, t14 = threadIdx.x & 15;   // 16 groups of 16 lanes
+#pragma unroll 1
+        for (int base = 0; base < IST_SLOTS; base += 16) {
+            const int fr = base + grp;
             const bool active = (t14 < 14) && (fr < nfr);
             float * slot = slots + fr * IST_SLOT_FLOATS;
             cpx a[14], b[14];
@@ -78,25 +98,36 @@ __global__ void __launch_bounds__(128) istft_kernel(istft_params p, const float 
     }
     __syncthreads();
 
-    // phase 2: trimmed output sample s (0 <= s < 98 F) sits at untrimmed position P = s + 147
+    // phase 2: trimmed output sample s = 98 H + r sits at untrimmed position P = s + 147 = 98 (H + 1) + (r + 49):
+    // frames H-2 .. H+1 (r < 49) or H-1 .. H+2 (r >= 49) cover it with window indices j0, j0-98, j0-196, j0-294
     {
         float * out = p.wave + p.out_off[u];
-        const int s0 = g0 * IST_HOP, s1 = g1 * IST_HOP;
-        for (int s = s0 + threadIdx.x; s < s1; s += blockDim.x) {
-            const int P = s + IST_PAD;
-            int t_hi = P / IST_HOP;                         // last frame covering P
-            int t_lo = (P - (IST_NFFT - 1) + IST_HOP - 1) / IST_HOP;   // ceil((P-391)/98), P-391 may be negative
-            if (P - (IST_NFFT - 1) < 0) t_lo = 0;
-            t_hi = min(t_hi, F - 1);
-            float acc = 0.f, wsum = 0.f;
-            for (int t = t_lo; t <= t_hi; t++) {
-                const int j = P - t * IST_HOP;
-                acc += slots[(t - f_lo) * IST_SLOT_FLOATS + j];
-                const float w = hann[j];
-                wsum += w * w;
+        const int n_out = (g1 - g0) * IST_HOP;
+        for (int e = threadIdx.x; e < n_out; e += IST_THREADS) {
+            const int hh = e / IST_HOP, r = e - hh * IST_HOP;
+            const int H = g0 + hh;
+            const int up = (r >= 49) ? 1 : 0;
+            const int t0 = H - 2 + up, j0 = r + 343 - 98 * up;
+            float acc = 0.f, wsum;
+            if (t0 >= 0 && t0 + 3 < F) {
+                const float * sl = slots + (t0 - f_lo) * IST_SLOT_FLOATS + j0;
+#pragma unroll
+                for (int k = 0; k < 4; k++) acc += sl[k * (IST_SLOT_FLOATS - IST_HOP)];
+                wsum = wsum4[r];
+            } else {
+                wsum = 0.f;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const int t = t0 + k, j = j0 - IST_HOP * k;
+                    if (t >= 0 && t < F) {
+                        acc += slots[(t - f_lo) * IST_SLOT_FLOATS + j];
+                        const float w = hann[j];
+                        wsum += w * w;
+                    }
+                }
             }
             if (wsum > 1e-8f) acc /= wsum;
-            out[s] = acc;
+            out[(size_t) H * IST_HOP + r] = acc;
         }
     }
 }
@@ -126,9 +157,10 @@ static cudaError_t ensure_tables() {
 
 cudaError_t launch_istft(const istft_params & p, cudaStream_t st) {
     if (p.total_chunks <= 0) return cudaSuccess;
+    if (p.spec_ld % 4 != 0 || p.spec_ld < 2 * IST_NFREQ) return cudaErrorInvalidValue;   // 16-byte rows for the bulk copies
     cudaError_t e = ensure_tables();
     if (e != cudaSuccess) return e;
-    istft_kernel<<<p.total_chunks, 128, IST_SMEM, st>>>(p, g_tw, g_tw + 392);
+    istft_kernel<<<p.total_chunks, IST_THREADS, IST_SMEM, st>>>(p, g_tw, g_tw + 392);
     return cudaGetLastError();
 }
 

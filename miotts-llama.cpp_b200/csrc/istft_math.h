@@ -20,7 +20,7 @@
 
 namespace mio {
 
-struct cpx { float re, im; };
+struct alignas(8) cpx { float re, im; };   // 8-byte aligned: shared-memory accesses compile to 64-bit LDS/STS
 
 MIO_HD cpx cmul(cpx a, cpx b) { return {a.re * b.re - a.im * b.im, a.re * b.im + a.im * b.re}; }
 
@@ -88,12 +88,13 @@ MIO_HD void ifft_load_z(const float * X, int k1, const float * tw392, cpx * z) {
 #endif
     for (int k2 = 0; k2 < 14; k2++) {
         const int k = k1 + 14 * k2;
-        cpx a = {X[2 * k], X[2 * k + 1]};
-        cpx b = {X[2 * (196 - k)], -X[2 * (196 - k) + 1]};     // conj(X[196-k])
+        cpx a = *(const cpx *) (X + 2 * k);
+        cpx b = *(const cpx *) (X + 2 * (196 - k));
+        b.im = -b.im;                                           // conj(X[196-k])
         if (k == 0) { a.im = 0.f; b.im = 0.f; }                 // Im X0, Im X196 ignored by the reference
         const cpx xe = {a.re + b.re, a.im + b.im};
         const cpx d = {a.re - b.re, a.im - b.im};
-        const cpx w = {tw392[2 * k], tw392[2 * k + 1]};
+        const cpx w = *(const cpx *) (tw392 + 2 * k);
         const cpx xo = cmul(d, w);
         z[k2] = {xe.re - xo.im, xe.im + xo.re};
     }
@@ -106,10 +107,8 @@ MIO_HD void ifft_store_y(const cpx * y, int k1, const float * tw196, float * slo
 #endif
     for (int m2 = 0; m2 < 14; m2++) {
         const int t = k1 * m2;
-        const cpx w = {tw196[2 * t], tw196[2 * t + 1]};
-        const cpx v = cmul(y[m2], w);
-        slot[2 * (k1 * 15 + m2)] = v.re;
-        slot[2 * (k1 * 15 + m2) + 1] = v.im;
+        const cpx w = *(const cpx *) (tw196 + 2 * t);
+        *(cpx *) (slot + 2 * (k1 * 15 + m2)) = cmul(y[m2], w);
     }
 }
 
@@ -118,7 +117,7 @@ MIO_HD void ifft_load_y(const float * slot, int m2, cpx * y) {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-    for (int k1 = 0; k1 < 14; k1++) y[k1] = {slot[2 * (k1 * 15 + m2)], slot[2 * (k1 * 15 + m2) + 1]};
+    for (int k1 = 0; k1 < 14; k1++) y[k1] = *(const cpx *) (slot + 2 * (k1 * 15 + m2));
 }
 
 // thread m2: z[m1] = x[2(14 m1 + m2)] + i x[2(14 m1 + m2)+1] (unnormalised). Store x/392 * hann in place.
@@ -130,8 +129,9 @@ MIO_HD void ifft_store_time(const cpx * z, int m2, const float * hann, float inv
 #endif
     for (int m1 = 0; m1 < 14; m1++) {
         const int n = 2 * (14 * m1 + m2);
-        slot[n] = (z[m1].re * inv_n) * hann[n];
-        slot[n + 1] = (z[m1].im * inv_n) * hann[n + 1];
+        const cpx h = *(const cpx *) (hann + n);
+        const cpx o = {(z[m1].re * inv_n) * h.re, (z[m1].im * inv_n) * h.im};
+        *(cpx *) (slot + n) = o;
     }
 }
 

@@ -86,8 +86,9 @@ cudaError_t attention_tc_init();
 cudaError_t launch_gn_stats(const float * x, int rows, int C, const row_map & rm, int row_div, double * stats,
                             cudaStream_t st);
 // y = fp16( silu( (x-mean)*rstd*w + b ) ), zeros on pad rows
+// (two launches: per-(utterance, group) mean / rstd into mr_scratch[n_utts*32], then the per-element pass)
 cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double * stats,
-                                 float eps, const float * w, const float * b, __half * out, cudaStream_t st);
+                                 float eps, const float * w, const float * b, float2 * mr_scratch, __half * out, cudaStream_t st);
 cudaError_t launch_split(const float * x, int rows, int C, const row_map & rm, int row_div, __half * hi, __half * lo,
                          cudaStream_t st);
 // mod[voice][cond_rows] = W[cond_rows][128] * silu(emb[voice]) + b

@@ -150,6 +150,28 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t * bar) {
                  : "memory");
 }
 
+// sin / cos for the fused epilogues (Snake, ISTFT head): three-constant Cody-Waite reduction by 2*pi with FMAs
+// (exact products), then the SFU approximation on [-pi, pi] (absolute error <= 2^-21.4 there, CUDA C Programming
+// Guide "intrinsic functions").  Total absolute error ~5e-7, i.e. -126 dB of a unit-amplitude signal; arguments
+// beyond 1e5 (never seen in this decoder) take the libdevice path so the result stays correct for any phase.
+__device__ __forceinline__ float reduce_2pi(float x) {
+    const float k = rintf(x * 0.15915494309189535f);
+    float r = fmaf(-k, 6.28125f, x);                       // 2*pi = 6.28125 + 1.9350052e-3 + 3.0198e-7 + ...
+    r = fmaf(-k, 1.9350051879882812e-3f, r);
+    r = fmaf(-k, 3.0199159819567e-07f, r);
+    return r;
+}
+__device__ __forceinline__ float fast_sinf(float x) {
+    if (fabsf(x) > 1.0e5f) return sinf(x);
+    return __sinf(reduce_2pi(x));
+}
+__device__ __forceinline__ void fast_sincosf(float x, float * sn, float * cs) {
+    if (fabsf(x) > 1.0e5f) { sincosf(x, sn, cs); return; }
+    const float r = reduce_2pi(x);
+    *sn = __sinf(r);
+    *cs = __cosf(r);
+}
+
 __device__ __forceinline__ void split_half2(float x, __half & hi, __half & lo) {
     hi = __float2half_rn(x);
     lo = __float2half_rn(x - __half2float(hi));
