@@ -445,7 +445,7 @@ std::string engine::load(const std::string & path, int dev) {
         if (!L.get("istft_head.out.weight", hw) || !L.get("istft_head.out.bias", hb)) return L.err;
         const int P = hp.out_proj_dim, NF = hp.n_freq;
         if (hw.size() != (size_t) 2 * NF * P || hb.size() != (size_t) 2 * NF) return "bad istft_head tensor size";
-        std::vector<float> B((size_t) 2 * NF * P), bb(2 * NF);
+        std::vector<float> B((size_t) 2 * NF * P), bb((2 * NF + 31) / 32 * 32, 0.f);   // bias padded to whole 32-column chunks
         for (int f = 0; f < NF; f++) {
             memcpy(&B[(size_t) (2 * f) * P], &hw[(size_t) f * P], P * sizeof(float));
             memcpy(&B[(size_t) (2 * f + 1) * P], &hw[(size_t) (NF + f) * P], P * sizeof(float));

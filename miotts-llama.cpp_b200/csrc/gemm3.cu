@@ -68,19 +68,15 @@ __device__ __forceinline__ void stage_f16_row(uint8_t * stage, int lane, int fir
 template <int EPI>
 __device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int col0, float (&v)[32], uint8_t * stage,
                                            int lane, int part) {
-    const bool full = (col0 + 32 <= p.N);
+    // Per-column parameter vectors (bias, snake) are readable up to the end of the 32-column chunk (the engine pads
+    // them), so there are no per-element bounds checks: columns >= N are computed and then clipped by the TMA store.
     const int cb = col0 % p.bias_mod;
     if (p.bias != nullptr) {
-        if (full) {
 #pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-                const float4 b = __ldg((const float4 *) (p.bias + cb + i));
-                v[i] = v[i] * p.out_scale + b.x; v[i + 1] = v[i + 1] * p.out_scale + b.y;
-                v[i + 2] = v[i + 2] * p.out_scale + b.z; v[i + 3] = v[i + 3] * p.out_scale + b.w;
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < 32; i++) v[i] = v[i] * p.out_scale + ((col0 + i < p.N) ? __ldg(p.bias + cb + i) : 0.f);
+        for (int i = 0; i < 32; i += 4) {
+            const float4 b = __ldg((const float4 *) (p.bias + cb + i));
+            v[i] = v[i] * p.out_scale + b.x; v[i + 1] = v[i + 1] * p.out_scale + b.y;
+            v[i + 2] = v[i + 2] * p.out_scale + b.z; v[i + 3] = v[i + 3] * p.out_scale + b.w;
         }
     } else {
 #pragma unroll
@@ -120,12 +116,13 @@ __device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int c
         if (p.snake_ea != nullptr) {
             // snake(x) = x + sin^2(e^alpha x) / e^beta  (snake_activation, src/miocodec.cpp:410-420, :717-725)
 #pragma unroll
-            for (int i = 0; i < 32; i++) {
-                if (full || col0 + i < p.N) {
-                    const float ea = __ldg(p.snake_ea + cb + i), eb = __ldg(p.snake_eb + cb + i);
-                    const float s = fast_sinf(v[i] * ea);
-                    v[i] = v[i] + __fdividef(s * s, eb);
-                }
+            for (int i = 0; i < 32; i += 4) {
+                const float4 ea = __ldg((const float4 *) (p.snake_ea + cb + i)), eb = __ldg((const float4 *) (p.snake_eb + cb + i));
+                float s;
+                s = fast_sinf(v[i] * ea.x);         v[i] += __fdividef(s * s, eb.x);
+                s = fast_sinf(v[i + 1] * ea.y);     v[i + 1] += __fdividef(s * s, eb.y);
+                s = fast_sinf(v[i + 2] * ea.z);     v[i + 2] += __fdividef(s * s, eb.z);
+                s = fast_sinf(v[i + 3] * ea.w);     v[i + 3] += __fdividef(s * s, eb.w);
             }
         }
         if constexpr (EPI == EPI_SNAKE) {

@@ -152,21 +152,19 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t * bar) {
 
 // sin / cos for the fused epilogues (Snake, ISTFT head): three-constant Cody-Waite reduction by 2*pi with FMAs
 // (exact products), then the SFU approximation on [-pi, pi] (absolute error <= 2^-21.4 there, CUDA C Programming
-// Guide "intrinsic functions").  Total absolute error ~5e-7, i.e. -126 dB of a unit-amplitude signal; arguments
-// beyond 1e5 (never seen in this decoder) take the libdevice path so the result stays correct for any phase.
+// Guide "intrinsic functions").  Absolute error ~5e-7 for |x| < 1e3 (-126 dB of a unit-amplitude signal), growing
+// to ~2e-6 at |x| = 1e5; far below the fp32 ulp of such an argument, where cos/sin are ill-conditioned anyway.
+// Deliberately branch-free: a libdevice slow path inlined 32x per chunk thrashed the instruction cache
+// (profiles/r1g: 13 % stall_no_inst in the out_proj epilogue).  inf / NaN propagate to NaN like sinf/cosf.
 __device__ __forceinline__ float reduce_2pi(float x) {
     const float k = rintf(x * 0.15915494309189535f);
-    float r = fmaf(-k, 6.28125f, x);                       // 2*pi = 6.28125 + 1.9350052e-3 + 3.0198e-7 + ...
+    float r = fmaf(-k, 6.28125f, x);                       // 2*pi = 6.28125 + 1.9350052e-3 + 3.0199160e-7 + ...
     r = fmaf(-k, 1.9350051879882812e-3f, r);
     r = fmaf(-k, 3.0199159819567e-07f, r);
     return r;
 }
-__device__ __forceinline__ float fast_sinf(float x) {
-    if (fabsf(x) > 1.0e5f) return sinf(x);
-    return __sinf(reduce_2pi(x));
-}
+__device__ __forceinline__ float fast_sinf(float x) { return __sinf(reduce_2pi(x)); }
 __device__ __forceinline__ void fast_sincosf(float x, float * sn, float * cs) {
-    if (fabsf(x) > 1.0e5f) { sincosf(x, sn, cs); return; }
     const float r = reduce_2pi(x);
     *sn = __sinf(r);
     *cs = __cosf(r);
