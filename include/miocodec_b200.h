@@ -53,8 +53,10 @@ int  mio_ctx_vocab(const mio_ctx * ctx);
 int  mio_ctx_device(const mio_ctx * ctx);
 
 /* options: "gemm" = "tc" (tcgen05, default) | "simt" (fp32 CUDA-core validation path, still on the GPU);
- *          "max_chunk_codes" = integer, workspace rows at code resolution (default 65536, ~8.5 GB of HBM).
- * Must be called before the first decode. */
+ *          "max_chunk_codes" = integer, workspace rows at code resolution (default 65536, ~8.5 GB of HBM); must be
+ *          set before the first decode;
+ *          "fetch_chunk_codes" = integer (default 24576): mio_decode_wave_batch cuts the batch into chunks of about
+ *          this many codes and copies chunk i to the host on a second stream while chunk i+1 computes. */
 int  mio_ctx_set_option(mio_ctx * ctx, const char * key, const char * value);
 /* run all kernels of this context on an existing CUDA stream (cudaStream_t as void*), e.g. torch's */
 int  mio_ctx_set_stream(mio_ctx * ctx, void * cuda_stream);

@@ -121,6 +121,8 @@ engine::~engine() {
     if (h_emit) cudaFreeHost(h_emit);
     if (h_stage) cudaFreeHost(h_stage);
     if (stream && own_stream) cudaStreamDestroy(stream);
+    if (chunk_done) cudaEventDestroy(chunk_done);
+    if (copy_stream) cudaStreamDestroy(copy_stream);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -571,8 +573,10 @@ row_map engine::rmap() const {
 // batch upload: builds the padded row space, split into chunks of whole utterances that fit the workspace
 // ---------------------------------------------------------------------------------------------
 std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts, const float * voice_table, int nv,
-                           const int32_t * voice_ids) {
+                           const int32_t * voice_ids, int chunk_rows_limit) {
     batch_uploaded = false; batch_ran = false;
+    // chunk_rows_limit > 0: cut chunks at that many rows (pipelined host delivery), never above the workspace
+    const int row_cap = (chunk_rows_limit > 0 && chunk_rows_limit < max_rows1) ? chunk_rows_limit : max_rows1;
     if (istft_only) return "bad argument: this context was created by mio_istft_ctx_create and has no decoder weights";
     if (n_utts < 0 || (n_utts > 0 && (!codes || !cu || !voice_table || !voice_ids)) || nv <= 0) return "bad argument";
     if (nv > max_voices) return "too many voices (max " + std::to_string(max_voices) + ")";
@@ -596,7 +600,7 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
             if (T < 0) return "cu_seqlens must be non-decreasing";
             if (T + 1 > max_rows1) return "utterance of " + std::to_string(T) + " codes exceeds max_chunk_codes";
             if (voice_ids[u] < 0 || voice_ids[u] >= nv) return "voice id out of range";
-            if (rows + T + 1 > max_rows1 || (u - c.utt0) >= max_utts) break;
+            if ((rows + T + 1 > row_cap && rows > 0) || rows + T + 1 > max_rows1 || (u - c.utt0) >= max_utts) break;
             lay.start.push_back(rows); lay.len.push_back(T); lay.voice.push_back(voice_ids[u]);
             lay.out_off.push_back((int64_t) cu[u] * hp.samples_per_token);
             for (int i = 0; i < T; i++) {
@@ -964,24 +968,40 @@ std::string engine::view512_ff(a_view & v) {
     return {};
 }
 
-std::string engine::run(bool peak_normalize) {
+std::string engine::run(bool peak_normalize, float * host_dst) {
     if (!batch_uploaded) return "mio_batch_run before mio_batch_upload";
     CK(cudaSetDevice(device));
     launches = 0;
     snaps.clear();
     // AdaLN conditioning vectors of every voice of the batch (compute_adaln3, src/miocodec.cpp:310-319)
     if (lay.n_utts > 0) CKR(CAT_COND, 0.0, launch_cond(d_voice_table, n_voices, hp.adaln_dim, w.cond_w, w.cond_b, w.cond_rows, mod, stream));
+    if (host_dst && !copy_stream) {
+        CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&chunk_done, cudaEventDisableTiming));
+    }
     for (const chunk_info & c : chunks) {
         std::string e = run_chunk(c);
         if (!e.empty()) return e;
-    }
-    if (peak_normalize && lay.n_utts > 0) {
-        for (const chunk_info & c : chunks) {
+        if (peak_normalize) {
             CKR(CAT_PEAK, (double) wave_samples * 12.0, launch_peak_normalize(d_wave, d_len + c.utt0, d_out_off + c.utt0, c.n_utts, hp.samples_per_token, peak, stream));
             launches++;   // two kernels
         }
+        if (host_dst) {
+            // deliver this chunk's waveform while the next chunk computes: the chunk's utterances are contiguous in
+            // the output, and chunks write disjoint ranges of d_wave
+            int64_t codes = 0;
+            for (int u = 0; u < c.n_utts; u++) codes += lay.len[c.utt0 + u];
+            const int64_t off = lay.out_off[c.utt0], n = codes * hp.samples_per_token;
+            CK(cudaEventRecord(chunk_done, stream));
+            CK(cudaStreamWaitEvent(copy_stream, chunk_done, 0));
+            if (n > 0) CK(cudaMemcpyAsync(host_dst + off, d_wave + off, (size_t) n * sizeof(float), cudaMemcpyDeviceToHost, copy_stream));
+        }
     }
     batch_ran = true;
+    if (host_dst) {
+        CK(cudaStreamSynchronize(copy_stream));
+        return sync();
+    }
     return {};
 }
 

@@ -100,8 +100,12 @@ struct engine {
     std::string ensure_workspace();
     // layout + H2D. codes_concat/cu_seqlens in the caller's (unpadded) indexing.
     std::string upload(const int32_t * codes, const int32_t * cu, int n_utts, const float * voice_table, int n_voices,
-                       const int32_t * voice_ids);
-    std::string run(bool peak_normalize);                 // enqueue all kernels of the uploaded batch
+                       const int32_t * voice_ids, int chunk_rows_limit = 0);
+    // enqueue all kernels of the uploaded batch; host_dst != nullptr: also copy each chunk's waveform to the host on a
+    // second stream as soon as it is complete (overlaps with the next chunk) and return when everything has landed
+    std::string run(bool peak_normalize, float * host_dst = nullptr);
+    cudaStream_t copy_stream = nullptr; cudaEvent_t chunk_done = nullptr;
+    int fetch_chunk_codes = 24576;   // chunk size of the host-delivery pipeline (mio_decode_wave_batch)
     std::string run_istft_only(const float * spec_host, int n_frames);   // mio_istft
     std::string sync();                                   // stream sync + error flag
     std::string fetch_wave(float * out, int64_t cap);
