@@ -59,6 +59,21 @@ def make_workload(name: str, rank: int, world: int):
     return dict(desc=desc, lens=lens, cu=cu, codes=codes, voice_table=vt, voice_ids=vids)
 
 
+class stdout_to_stderr:
+    """Route C-level stdout (fd 1) to stderr while NCCL initialises: its version banner goes to stdout and the
+    contract is ONE JSON line there."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def __exit__(self, *a):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -269,11 +284,16 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        with stdout_to_stderr():
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+            dist.barrier()                       # first collective: communicator set-up (and NCCL's banner) happens here
+            torch.cuda.synchronize()
 
-    gguf, _ = synth.ensure_assets()
+    if rank == 0:
+        synth.ensure_assets()
     if world > 1:
         dist.barrier()
+    gguf, _ = synth.ensure_assets()
     codec = binding.MioCodec(gguf, local, gemm=args.gemm, max_chunk_codes=args.chunk)
     stream = torch.cuda.current_stream()
     codec.set_stream(stream.cuda_stream)

@@ -204,12 +204,17 @@ def ensure_assets(seed: int = 0, n_voices: int = 16) -> tuple[str, list[str]]:
     """Create (once) the synthetic codec GGUF and voice files; returns their paths."""
     d = asset_dir()
     g = os.path.join(d, f"miocodec_synth_seed{seed}.gguf")
+    # several ranks may get here at once: write to a private name, then publish atomically
     if not os.path.exists(g):
-        write_codec_gguf(g, seed)
+        tmp = f"{g}.tmp{os.getpid()}"
+        write_codec_gguf(tmp, seed)
+        os.replace(tmp, g)
     voices = []
     for v in range(n_voices):
         p = os.path.join(d, f"voice_{v}.emb.gguf")
         if not os.path.exists(p):
-            write_voice_gguf(p, synth_voice(v))
+            tmp = f"{p}.tmp{os.getpid()}"
+            write_voice_gguf(tmp, synth_voice(v))
+            os.replace(tmp, p)
         voices.append(p)
     return g, voices
