@@ -354,40 +354,65 @@ __global__ void gn_finalize_kernel(const double * __restrict__ stats, const int3
 
 // GroupNorm apply + SiLU + round to fp16 (the conv operand: ggml_conv_1d's im2col rounds activations to F16,
 // ggml-cpu/ops.cpp:6232-6256, so this rounding is the reference's own, not an approximation).
-// One thread = 8 channels of one row (two float4 loads, one 16-byte store).
+// One thread owns 8 fixed channels (affine parameters live in registers) and walks the block's rows four at a time, so
+// four independent 32-byte loads are in flight per thread; SiLU uses the SFU exp/reciprocal (relative error ~2^-20,
+// far below the fp16 rounding that follows).
+constexpr int GNA_ROWS = 64;                     // rows per block
+
+__device__ __forceinline__ float silu_fast(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+
 __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
         const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt, int row_div,
         const float2 * __restrict__ mr, const float * __restrict__ w, const float * __restrict__ b, __half * __restrict__ out) {
-    const int C8 = C / 8;
-    const size_t total = (size_t) rows * C8;
+    const int C8 = C >> 3;                       // threads per row: 64, 32 or 16
+    const int rpp = 256 / C8;                    // rows per pass of the block
+    const int c = (threadIdx.x % C8) * 8;
+    const int rl = threadIdx.x / C8;
     const int cpg = C / 32;
-    for (size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t) gridDim.x * blockDim.x) {
-        const int r = (int) (idx / C8);
-        const int c = (int) (idx - (size_t) r * C8) * 8;
-        const int u = row_utt[r / row_div];
-        uint4 o = make_uint4(0u, 0u, 0u, 0u);
-        if (u >= 0) {
-            const float4 v0 = __ldg((const float4 *) (x + (size_t) r * C + c)), v1 = __ldg((const float4 *) (x + (size_t) r * C + c + 4));
-            const float4 w0 = __ldg((const float4 *) (w + c)), w1 = __ldg((const float4 *) (w + c + 4));
-            const float4 b0 = __ldg((const float4 *) (b + c)), b1 = __ldg((const float4 *) (b + c + 4));
-            const float2 m0 = __ldg(mr + (size_t) u * 32 + c / cpg), m1 = __ldg(mr + (size_t) u * 32 + (c + 4) / cpg);
-            const __half2 h0 = __floats2half2_rn(silu_f((v0.x - m0.x) * m0.y * w0.x + b0.x), silu_f((v0.y - m0.x) * m0.y * w0.y + b0.y));
-            const __half2 h1 = __floats2half2_rn(silu_f((v0.z - m0.x) * m0.y * w0.z + b0.z), silu_f((v0.w - m0.x) * m0.y * w0.w + b0.w));
-            const __half2 h2 = __floats2half2_rn(silu_f((v1.x - m1.x) * m1.y * w1.x + b1.x), silu_f((v1.y - m1.x) * m1.y * w1.y + b1.y));
-            const __half2 h3 = __floats2half2_rn(silu_f((v1.z - m1.x) * m1.y * w1.z + b1.z), silu_f((v1.w - m1.x) * m1.y * w1.w + b1.w));
-            o = make_uint4(*(const uint32_t *) &h0, *(const uint32_t *) &h1, *(const uint32_t *) &h2, *(const uint32_t *) &h3);
+    const int g0 = c / cpg, g1 = (c + 4) / cpg;
+    const float4 w0 = __ldg((const float4 *) (w + c)), w1 = __ldg((const float4 *) (w + c + 4));
+    const float4 b0 = __ldg((const float4 *) (b + c)), b1 = __ldg((const float4 *) (b + c + 4));
+    const int r_begin = blockIdx.x * GNA_ROWS, r_end = min(rows, r_begin + GNA_ROWS);
+    for (int rb = r_begin + rl; rb < r_end; rb += 4 * rpp) {
+        int u[4];
+        float4 v0[4], v1[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int r = rb + k * rpp;
+            u[k] = (r < r_end) ? __ldg(row_utt + r / row_div) : -2;
         }
-        *(uint4 *) (out + (size_t) r * C + c) = o;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int r = rb + k * rpp;
+            if (u[k] >= 0) {
+                v0[k] = __ldg((const float4 *) (x + (size_t) r * C + c));
+                v1[k] = __ldg((const float4 *) (x + (size_t) r * C + c + 4));
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int r = rb + k * rpp;
+            if (u[k] == -2) continue;
+            uint4 o = make_uint4(0u, 0u, 0u, 0u);
+            if (u[k] >= 0) {
+                const float2 m0 = __ldg(mr + (size_t) u[k] * 32 + g0), m1 = __ldg(mr + (size_t) u[k] * 32 + g1);
+                const __half2 h0 = __floats2half2_rn(silu_fast((v0[k].x - m0.x) * m0.y * w0.x + b0.x), silu_fast((v0[k].y - m0.x) * m0.y * w0.y + b0.y));
+                const __half2 h1 = __floats2half2_rn(silu_fast((v0[k].z - m0.x) * m0.y * w0.z + b0.z), silu_fast((v0[k].w - m0.x) * m0.y * w0.w + b0.w));
+                const __half2 h2 = __floats2half2_rn(silu_fast((v1[k].x - m1.x) * m1.y * w1.x + b1.x), silu_fast((v1[k].y - m1.x) * m1.y * w1.y + b1.y));
+                const __half2 h3 = __floats2half2_rn(silu_fast((v1[k].z - m1.x) * m1.y * w1.z + b1.z), silu_fast((v1[k].w - m1.x) * m1.y * w1.w + b1.w));
+                o = make_uint4(*(const uint32_t *) &h0, *(const uint32_t *) &h1, *(const uint32_t *) &h2, *(const uint32_t *) &h3);
+            }
+            *(uint4 *) (out + (size_t) r * C + c) = o;
+        }
     }
 }
 
 cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double * stats,
                                  float eps, const float * w, const float * b, float2 * mr_scratch, __half * out, cudaStream_t st) {
     if (rows <= 0) return cudaSuccess;
+    if (C % 128 != 0 || C > 2048) return cudaErrorInvalidValue;
     gn_finalize_kernel<<<(rm.n_utts * 32 + 255) / 256, 256, 0, st>>>(stats, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
-    const size_t total = (size_t) rows * (C / 8);
-    const int grid = (int) min((size_t) 148 * 16, (total + 255) / 256);
-    gn_apply_silu_kernel<<<grid, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out);
+    gn_apply_silu_kernel<<<(rows + GNA_ROWS - 1) / GNA_ROWS, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out);
     return cudaGetLastError();
 }
 

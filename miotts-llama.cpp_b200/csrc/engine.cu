@@ -114,7 +114,7 @@ engine::~engine() {
     if (stream && own_stream) cudaStreamSynchronize(stream);
     auto F = [](void * p) { if (p) cudaFree(p); };
     F(x768); F(qkv_hi); F(qkv_lo); F(x512); F(y512); F(x256); F(y256); F(x128); F(y128); F(spec); F(mod); F(peak);
-    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_stats); F(gn_mr); F(err_flag);
+    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_stats); F(gn_mr); F(attn_b1); F(attn_b2); F(err_flag);
     F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_out_off); F(d_voice_table); F(d_wave);
     for (void * p : w_allocs) F(p);
     F(d_emit); F(d_emit_jobs);
@@ -538,6 +538,7 @@ std::string engine::ensure_workspace() {
     A(c16, R1 * 2304); A(h512_hi, R18 * 512); A(h512_lo, R18 * 512);
     A(gn_stats, (size_t) GN_SLOTS * max_utts * 64);
     A(gn_mr, (size_t) max_utts * 32);
+    A(attn_b1, R1); A(attn_b2, R2);
     A(mod, (size_t) max_voices * w.cond_rows);
     A(peak, (size_t) max_utts);
     A(err_flag, 1);
@@ -819,7 +820,7 @@ gemm_params engine::qkv_params(const row_map & rm, int D, int row_div) {
 }
 
 // banded attention over the q|k|v written by the QKV epilogue; bytes: 12*D read (hi+lo of q,k,v) + 4*D written per row
-std::string engine::run_attention(int rows, int D, int n_head, int window, int row_div, const a_view & out) {
+std::string engine::run_attention(int rows, int D, int n_head, int window, int row_div, const a_view & out, const int2 * bounds) {
     const row_map rm = rmap();
     if (attn_simt) {
         CKR(CAT_ATTN, (double) rows * 16.0 * D, launch_attention_simt(qkv_hi, qkv_lo, rows, D, n_head, window, rm, row_div, out.hi, out.lo, stream));
@@ -830,7 +831,7 @@ std::string engine::run_attention(int rows, int D, int n_head, int window, int r
     const CUtensorMap * oh = out_map(out.hi, 2, rows, D, (size_t) D * 2, 64, 16);
     const CUtensorMap * ol = out_map(out.lo, 2, rows, D, (size_t) D * 2, 64, 16);
     if (!ih || !il || !oh || !ol) return err;
-    CKR(CAT_ATTN, (double) rows * 16.0 * D, launch_attention_tc(*ih, *il, *oh, *ol, rows, D, n_head, window, rm, row_div, stream));
+    CKR(CAT_ATTN, (double) rows * 16.0 * D, launch_attention_tc(*ih, *il, *oh, *ol, rows, D, n_head, window, bounds, stream));
     return {};
 }
 
@@ -844,6 +845,11 @@ std::string engine::run_chunk(const chunk_info & c) {
     CKG(cudaMemsetAsync(gn_stats, 0, (size_t) GN_SLOTS * max_utts * 64 * sizeof(double), stream));
     int gn_slot = 0;
 
+    // valid key ranges of the banded attention, once per chunk and resolution (all layers reuse them)
+    if (!attn_simt) {
+        CKR(CAT_ATTN, 0.0, launch_attn_bounds(rm, R1, 1, hp.prenet_window, attn_b1, stream));
+        CKR(CAT_ATTN, 0.0, launch_attn_bounds(rm, R2, 2, hp.dec_window, attn_b2, stream));
+    }
     // 1. token gather
     CKR(CAT_GATHER, (double) (R1) * (4.0 + 8.0 * (D)), launch_gather(w.token_embd, d_codes + c.row0, x768, R1, D, hp.vocab, err_flag, stream));
     snap_f32("embed", x768, (size_t) R1 * D);
@@ -854,7 +860,7 @@ std::string engine::run_chunk(const chunk_info & c) {
         p = qkv_params(rm, D, 1);
         CKG(gemm(l.qkv, vA768, R1, p));
         if (i == 0) snap_f16("pre0_qkv_rope", qkv_hi, qkv_lo, (size_t) R1 * 3 * D);
-        if (!(e = run_attention(R1, D, hp.prenet_heads, hp.prenet_window, 1, vA768)).empty()) return e;
+        if (!(e = run_attention(R1, D, hp.prenet_heads, hp.prenet_window, 1, vA768, attn_b1)).empty()) return e;
         if (i == 0) snap_f16("pre0_attn", vA768.hi, vA768.lo, (size_t) R1 * D);
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
         CKG(gemm(l.wo, vA768, R1, p));
@@ -894,7 +900,7 @@ std::string engine::run_chunk(const chunk_info & c) {
         CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, oa, oa + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream));
         p = qkv_params(rm, C, 2);
         CKG(gemm(l.qkv, vA512, R2, p));
-        if (!(e = run_attention(R2, C, hp.dec_heads, hp.dec_window, 2, vA512)).empty()) return e;
+        if (!(e = run_attention(R2, C, hp.dec_heads, hp.dec_window, 2, vA512, attn_b2)).empty()) return e;
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x512; p.ld_out = C;
         p.gate = mod + oa + 2 * C; p.gate_ld = w.cond_rows; p.row_utt = rm.row_utt; p.row_div = 2; p.gate_voice = rm.voice;
         CKG(gemm(l.wo, vA512, R2, p));

@@ -66,6 +66,8 @@ struct engine {
     bool attn_simt = false;           // MIO_ATTN=simt: CUDA-core validation kernel
     double * gn_stats = nullptr;      // [GN_SLOTS][max_utts][32][2]
     float2 * gn_mr = nullptr;         // [max_utts][32] (mean, rstd) of the GroupNorm being applied
+    int2 * attn_b1 = nullptr;         // [max_rows1]   valid key range per prenet row (attn_bounds_kernel)
+    int2 * attn_b2 = nullptr;         // [2*max_rows1] valid key range per decoder row
     int * err_flag = nullptr;
     a_view vA768, vA512, vFF2048, vFF1536, vFF256, vFF128, vFF512, vC512, vC256, vC128, vH512;
     bool vFF512_ready = false;
@@ -120,7 +122,7 @@ struct engine {
     // box {box_c, box_r}; swizzle = box_c * esize (128-byte or 64-byte box rows)
     const CUtensorMap * out_map(const void * base, int esize, int rows, int cols, size_t ld_bytes, int box_c = 32, int box_r = 32);
     gemm_params qkv_params(const row_map & rm, int D, int row_div);
-    std::string run_attention(int rows, int D, int n_head, int window, int row_div, const a_view & out);
+    std::string run_attention(int rows, int D, int n_head, int window, int row_div, const a_view & out, const int2 * bounds);
     // profiling
     bool profiling = false;
     std::vector<cudaEvent_t> prof_events; size_t prof_used = 0;

@@ -34,11 +34,12 @@ struct gemm3_cfg {
 };
 
 __device__ __forceinline__ uint32_t pack_split_hi_lo(float a, float b, uint32_t & lo) {
-    __half ah, al, bh, bl;
-    split_half2(a, ah, al);
-    split_half2(b, bh, bl);
-    lo = pack_h2(al, bl);
-    return pack_h2(ah, bh);
+    // same roundings as split_half2 on each value, with the packed converts (one F2FP per pair)
+    const __half2 h = __floats2half2_rn(a, b);
+    const float2 hf = __half22float2(h);
+    const __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
+    lo = *(const uint32_t *) &l;
+    return *(const uint32_t *) &h;
 }
 
 // fp32 staging tile: [32 rows][128 B], SWIZZLE_128B (16-byte chunk index ^= row & 7)

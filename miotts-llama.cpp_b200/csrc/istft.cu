@@ -30,7 +30,7 @@ __device__ __forceinline__ void bulk_load_1d(void * dst, const void * src, uint3
                  : "memory");
 }
 
-__global__ void __launch_bounds__(IST_THREADS) istft_kernel(istft_params p, const float * __restrict__ tw392g,
+__global__ void __launch_bounds__(IST_THREADS, 3) istft_kernel(istft_params p, const float * __restrict__ tw392g,
                                                             const float * __restrict__ tw196g) {
     extern __shared__ __align__(16) float ist_smem[];
     float * slots = ist_smem;

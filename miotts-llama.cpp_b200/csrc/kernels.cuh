@@ -75,9 +75,11 @@ cudaError_t launch_layernorm(const float * x, int rows, int D, float eps, const 
                              __half * out_hi, __half * out_lo, float * out_f32, cudaStream_t st);
 // banded local attention on the rotated / scaled / split q|k|v written by EPI_QKV.  qkv_*: [rows][3*D] fp16;
 // out: split fp16 [rows][D].  _tc: TMA + ldmatrix + warp MMA (attention.cu, product path); _simt: fp32 validation.
+// bounds[i] = (first valid key, number of valid keys) of query row i, written once per chunk by launch_attn_bounds.
+cudaError_t launch_attn_bounds(const row_map & rm, int rows, int row_div, int window, int2 * bounds, cudaStream_t st);
 cudaError_t launch_attention_tc(const CUtensorMap & tm_in_hi, const CUtensorMap & tm_in_lo, const CUtensorMap & tm_out_hi,
-                                const CUtensorMap & tm_out_lo, int rows, int D, int n_head, int window, const row_map & rm,
-                                int row_div, cudaStream_t st);
+                                const CUtensorMap & tm_out_lo, int rows, int D, int n_head, int window, const int2 * bounds,
+                                cudaStream_t st);
 cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, int rows, int D, int n_head, int window,
                                   const row_map & rm, int row_div, __half * out_hi, __half * out_lo, cudaStream_t st);
 cudaError_t attention_init();
