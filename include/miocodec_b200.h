@@ -104,6 +104,29 @@ int64_t mio_batch_kernel_launches(const mio_ctx * ctx);   /* kernels launched by
 /* device pointer of the resident waveform of the last batch (float, samples_per_token*sum(T)) */
 void * mio_batch_wave_device(mio_ctx * ctx);
 
+/* ---- the steps either side of the path --------------------------------------
+ * F2, pre-path ingest: replaces parse_speech_tokens (src/token-parser.h:8, src/token-parser.cpp:5-28): every
+ * "<|s_N|>" in the text yields int(strtol(N)) with the reference's exact acceptance rule (optional whitespace / sign as
+ * strtol takes them, at least one digit, "|>" must follow and must not end at the last byte + 1 of the text; the scan
+ * stops at an embedded NUL like strstr on c_str()).  Returns the number of codes found (which may exceed cap) and
+ * writes the first min(count, cap) of them; <0 on a bad argument. */
+int64_t mio_parse_speech_tokens(const char * text, int64_t text_len, int32_t * codes_out, int64_t cap);
+
+/* F1, post-path epilogue: peak normalisation (src/test-to-speech.cpp:289-300) + float -> PCM16 conversion
+ * int16(clamp(s * 32767, -32768, 32767)) (truncation; src/wav-writer.cpp:39-42) run on the device behind the ISTFT,
+ * so 2 bytes per sample cross PCIe instead of 4 and the two host passes of the reference disappear.
+ * mio_decode_pcm16_batch = mio_decode_wave_batch delivering PCM16 (same chunked, overlapped D2H);
+ * mio_batch_fetch_pcm16  = mio_batch_fetch delivering PCM16 of the resident waveform. */
+int  mio_decode_pcm16_batch(mio_ctx * ctx, const int32_t * codes_concat, const int32_t * cu_seqlens, int n_utts,
+                            const float * voice_table, int n_voices, const int32_t * voice_ids,
+                            int peak_normalize, int16_t * pcm_out, int64_t pcm_cap);
+int  mio_batch_fetch_pcm16(mio_ctx * ctx, int16_t * pcm_out, int64_t pcm_cap);
+/* The 44-byte RIFF/WAVE header wav_write emits (src/wav-writer.cpp:7-37): PCM, mono, 16 bit. */
+int  mio_wav_header(int sample_rate, int64_t n_samples, uint8_t out44[44]);
+/* header + samples to a file: byte-identical to wav_write(path, samples, sample_rate) when pcm came from the
+ * conversion above (src/wav-writer.cpp:24-45). */
+int  mio_wav_write_pcm16(const char * path, const int16_t * pcm, int64_t n_samples, int sample_rate);
+
 /* ---- streaming policy on top of the decoder: replaces the LLM-branch of
  * TestToSpeech::synthesize_stream_profiled (src/test-to-speech.cpp:430-625): commit holdback (32 codes),
  * min commit step (24), check cadence (every 20 pushed codes), full-prefix re-decode, llround() sample

@@ -238,6 +238,70 @@ int mio_decode_wave_batch(mio_ctx * c, const int32_t * codes, const int32_t * cu
     return MIO_OK;
 }
 
+int mio_decode_pcm16_batch(mio_ctx * c, const int32_t * codes, const int32_t * cu, int n_utts, const float * vt, int nv,
+                           const int32_t * vids, int peak_normalize, int16_t * out, int64_t cap) {
+    if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
+    TRY(c->E.upload(codes, cu, n_utts, vt, nv, vids, c->E.fetch_chunk_codes + c->E.fetch_chunk_codes / 16));
+    if (cap < c->E.wave_samples) return fail(MIO_ERR_ARG, "capacity too small");
+    TRY(c->E.run(peak_normalize != 0, nullptr, out));
+    return MIO_OK;
+}
+int mio_batch_fetch_pcm16(mio_ctx * c, int16_t * out, int64_t cap) {
+    if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
+    TRY(c->E.fetch_pcm16(out, cap));
+    return MIO_OK;
+}
+
+// ---- host-side neighbours of the path
+int64_t mio_parse_speech_tokens(const char * text, int64_t text_len, int32_t * out, int64_t cap) {
+    if (!text || text_len < 0 || cap < 0 || (!out && cap > 0)) return fail(MIO_ERR_ARG, "bad argument");
+    // A private NUL-terminated copy: the reference scans text.c_str() with strstr/strtol (src/token-parser.cpp:9-16),
+    // which is where "stops at an embedded NUL" and strtol's whitespace/sign/overflow behaviour come from.
+    const std::string buf(text, (size_t) text_len);
+    const char * p = buf.c_str();
+    const char * const end = p + buf.size();
+    int64_t n = 0;
+    while (p < end) {
+        const char * tag = strstr(p, "<|s_");
+        if (!tag) break;
+        const char * digits = tag + 4;
+        char * after = nullptr;
+        const long v = strtol(digits, &after, 10);
+        const bool closed = after && after > digits && after + 1 < end && after[0] == '|' && after[1] == '>';
+        if (closed) {
+            if (n < cap) out[n] = (int32_t) (int) v;
+            n++;
+            p = after + 2;
+        } else {
+            p = tag + 1;
+        }
+    }
+    return n;
+}
+
+int mio_wav_header(int sample_rate, int64_t n_samples, uint8_t * h) {
+    if (!h || sample_rate <= 0 || n_samples < 0) return fail(MIO_ERR_ARG, "bad argument");
+    auto u32 = [&](int at, uint32_t v) { for (int i = 0; i < 4; i++) h[at + i] = (uint8_t) (v >> (8 * i)); };
+    auto u16 = [&](int at, uint16_t v) { h[at] = (uint8_t) v; h[at + 1] = (uint8_t) (v >> 8); };
+    const uint32_t data = (uint32_t) ((uint64_t) n_samples * 2u);      // the reference's uint32 field wraps the same way
+    memcpy(h + 0, "RIFF", 4); u32(4, 36u + data); memcpy(h + 8, "WAVE", 4); memcpy(h + 12, "fmt ", 4);
+    u32(16, 16); u16(20, 1); u16(22, 1); u32(24, (uint32_t) sample_rate); u32(28, (uint32_t) sample_rate * 2u);
+    u16(32, 2); u16(34, 16); memcpy(h + 36, "data", 4); u32(40, data);
+    return MIO_OK;
+}
+
+int mio_wav_write_pcm16(const char * path, const int16_t * pcm, int64_t n, int sample_rate) {
+    if (!path || (!pcm && n > 0) || n < 0) return fail(MIO_ERR_ARG, "bad argument");
+    uint8_t h[44];
+    if (mio_wav_header(sample_rate, n, h) != MIO_OK) return MIO_ERR_ARG;
+    FILE * f = fopen(path, "wb");
+    if (!f) return fail(MIO_ERR_IO, std::string("cannot open ") + path + " for writing");
+    bool ok = fwrite(h, 1, 44, f) == 44;
+    if (ok && n > 0) ok = fwrite(pcm, sizeof(int16_t), (size_t) n, f) == (size_t) n;
+    ok = (fclose(f) == 0) && ok;
+    return ok ? MIO_OK : fail(MIO_ERR_IO, std::string("short write to ") + path);
+}
+
 // ---- streaming
 void mio_stream_default_config(const mio_ctx * c, mio_stream_config * cfg) {
     if (c && cfg) stream_default_config(c->E, cfg);

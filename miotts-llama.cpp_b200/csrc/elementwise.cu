@@ -4,6 +4,7 @@
 // (formulae: SURVEY.md Appendix A).
 #include "kernels.cuh"
 
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 
@@ -502,6 +503,42 @@ cudaError_t launch_peak_normalize(float * wave, const int32_t * len, const int64
     dim3 grid(32, n_utts);
     peak_max_kernel<<<grid, 256, 0, st>>>(wave, len, out_off, samples_per_code, peak_scratch);
     peak_scale_kernel<<<grid, 256, 0, st>>>(wave, len, out_off, samples_per_code, peak_scratch);
+    return cudaGetLastError();
+}
+
+// float -> PCM16 exactly as the reference's WAV writer does on the host (src/wav-writer.cpp:39-42):
+// int16(clamp(s * 32767.0f, -32768.0f, 32767.0f)), i.e. truncation toward zero after the clamp.  Eight samples per
+// thread (two 16-byte loads, one 16-byte store); the tail is handled per element.  NaN maps to -32768.
+__device__ __forceinline__ int pcm16_of(float s) { return __float2int_rz(fminf(fmaxf(s * 32767.0f, -32768.0f), 32767.0f)); }
+
+__global__ void __launch_bounds__(256) pcm16_kernel(const float * __restrict__ wave, int16_t * __restrict__ pcm,
+                                                    int64_t begin, int64_t end) {
+    // absolute sample indices: [va, vb) is the 8-sample-aligned body (bases are 256-byte aligned allocations)
+    int64_t va = (begin + 7) & ~(int64_t) 7, vb = end & ~(int64_t) 7;
+    if (va > vb) { va = end; vb = end; }
+    const int64_t i0 = va >> 3, i1 = vb >> 3;
+    for (int64_t i = i0 + (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < i1; i += (int64_t) gridDim.x * blockDim.x) {
+        const float4 a = __ldg((const float4 *) wave + 2 * i), b = __ldg((const float4 *) wave + 2 * i + 1);
+        uint4 o;
+        o.x = (uint32_t) (pcm16_of(a.x) & 0xffff) | ((uint32_t) pcm16_of(a.y) << 16);
+        o.y = (uint32_t) (pcm16_of(a.z) & 0xffff) | ((uint32_t) pcm16_of(a.w) << 16);
+        o.z = (uint32_t) (pcm16_of(b.x) & 0xffff) | ((uint32_t) pcm16_of(b.y) << 16);
+        o.w = (uint32_t) (pcm16_of(b.z) & 0xffff) | ((uint32_t) pcm16_of(b.w) << 16);
+        ((uint4 *) pcm)[i] = o;
+    }
+    if (blockIdx.x == 0) {                                  // unaligned head and tail: fewer than 8 samples each
+        const int64_t h = begin + threadIdx.x, t = vb + threadIdx.x;
+        if (threadIdx.x < 8 && h < va) pcm[h] = (int16_t) pcm16_of(wave[h]);
+        if (threadIdx.x < 8 && t >= va && t < end) pcm[t] = (int16_t) pcm16_of(wave[t]);
+    }
+}
+
+// converts samples [begin, end) of wave into the same positions of pcm (both base pointers of cudaMalloc allocations)
+cudaError_t launch_pcm16(const float * wave, int16_t * pcm, int64_t begin, int64_t end, cudaStream_t st) {
+    if (end <= begin) return cudaSuccess;
+    const int64_t n8 = (end - begin) >> 3;
+    const int grid = (int) std::min<int64_t>((int64_t) 148 * 8, std::max<int64_t>(1, (n8 + 255) / 256));
+    pcm16_kernel<<<grid, 256, 0, st>>>(wave, pcm, begin, end);
     return cudaGetLastError();
 }
 

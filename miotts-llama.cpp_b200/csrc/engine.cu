@@ -117,7 +117,7 @@ engine::~engine() {
     F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_stats); F(gn_mr); F(attn_b1); F(attn_b2); F(err_flag);
     F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_out_off); F(d_voice_table); F(d_wave);
     for (void * p : w_allocs) F(p);
-    F(d_emit); F(d_emit_jobs);
+    F(d_emit); F(d_emit_jobs); F(d_pcm);
     if (h_emit) cudaFreeHost(h_emit);
     if (h_stage) cudaFreeHost(h_stage);
     if (stream && own_stream) cudaStreamDestroy(stream);
@@ -974,14 +974,23 @@ std::string engine::view512_ff(a_view & v) {
     return {};
 }
 
-std::string engine::run(bool peak_normalize, float * host_dst) {
+std::string engine::ensure_pcm() {
+    if (pcm_cap >= wave_samples && d_pcm) return {};
+    if (d_pcm) cudaFree(d_pcm);
+    d_pcm = nullptr;
+    pcm_cap = wave_samples + 64;
+    return dev_alloc(&d_pcm, (size_t) pcm_cap);
+}
+
+std::string engine::run(bool peak_normalize, float * host_dst, int16_t * host_pcm) {
     if (!batch_uploaded) return "mio_batch_run before mio_batch_upload";
     CK(cudaSetDevice(device));
     launches = 0;
     snaps.clear();
     // AdaLN conditioning vectors of every voice of the batch (compute_adaln3, src/miocodec.cpp:310-319)
     if (lay.n_utts > 0) CKR(CAT_COND, 0.0, launch_cond(d_voice_table, n_voices, hp.adaln_dim, w.cond_w, w.cond_b, w.cond_rows, mod, stream));
-    if (host_dst && !copy_stream) {
+    if (host_pcm) { std::string e = ensure_pcm(); if (!e.empty()) return e; }
+    if ((host_dst || host_pcm) && !copy_stream) {
         CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&chunk_done, cudaEventDisableTiming));
     }
@@ -992,19 +1001,21 @@ std::string engine::run(bool peak_normalize, float * host_dst) {
             CKR(CAT_PEAK, (double) wave_samples * 12.0, launch_peak_normalize(d_wave, d_len + c.utt0, d_out_off + c.utt0, c.n_utts, hp.samples_per_token, peak, stream));
             launches++;   // two kernels
         }
-        if (host_dst) {
+        if (host_dst || host_pcm) {
             // deliver this chunk's waveform while the next chunk computes: the chunk's utterances are contiguous in
             // the output, and chunks write disjoint ranges of d_wave
             int64_t codes = 0;
             for (int u = 0; u < c.n_utts; u++) codes += lay.len[c.utt0 + u];
             const int64_t off = lay.out_off[c.utt0], n = codes * hp.samples_per_token;
+            if (host_pcm) CKR(CAT_PEAK, (double) n * 6.0, launch_pcm16(d_wave, d_pcm, off, off + n, stream));
             CK(cudaEventRecord(chunk_done, stream));
             CK(cudaStreamWaitEvent(copy_stream, chunk_done, 0));
-            if (n > 0) CK(cudaMemcpyAsync(host_dst + off, d_wave + off, (size_t) n * sizeof(float), cudaMemcpyDeviceToHost, copy_stream));
+            if (n > 0 && host_dst) CK(cudaMemcpyAsync(host_dst + off, d_wave + off, (size_t) n * sizeof(float), cudaMemcpyDeviceToHost, copy_stream));
+            if (n > 0 && host_pcm) CK(cudaMemcpyAsync(host_pcm + off, d_pcm + off, (size_t) n * sizeof(int16_t), cudaMemcpyDeviceToHost, copy_stream));
         }
     }
     batch_ran = true;
-    if (host_dst) {
+    if (host_dst || host_pcm) {
         CK(cudaStreamSynchronize(copy_stream));
         return sync();
     }
@@ -1030,6 +1041,19 @@ std::string engine::fetch_wave(float * out, int64_t cap) {
     std::string e = sync();
     if (!e.empty()) return e;
     if (wave_samples > 0) CK(cudaMemcpy(out, d_wave, (size_t) wave_samples * sizeof(float), cudaMemcpyDeviceToHost));
+    return {};
+}
+
+// PCM16 image of the resident waveform of the last batch (mio_batch_fetch_pcm16)
+std::string engine::fetch_pcm16(int16_t * out, int64_t cap) {
+    if (!batch_ran) return "mio_batch_fetch before mio_batch_run";
+    if (cap < wave_samples) return "output capacity too small";
+    CK(cudaSetDevice(device));
+    std::string e = ensure_pcm();
+    if (!e.empty()) return e;
+    CKR(CAT_PEAK, (double) wave_samples * 6.0, launch_pcm16(d_wave, d_pcm, 0, wave_samples, stream));
+    if (!(e = sync()).empty()) return e;
+    if (wave_samples > 0) CK(cudaMemcpy(out, d_pcm, (size_t) wave_samples * sizeof(int16_t), cudaMemcpyDeviceToHost));
     return {};
 }
 

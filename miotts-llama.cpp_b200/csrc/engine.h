@@ -105,7 +105,11 @@ struct engine {
                        const int32_t * voice_ids, int chunk_rows_limit = 0);
     // enqueue all kernels of the uploaded batch; host_dst != nullptr: also copy each chunk's waveform to the host on a
     // second stream as soon as it is complete (overlaps with the next chunk) and return when everything has landed
-    std::string run(bool peak_normalize, float * host_dst = nullptr);
+    // host_pcm != nullptr: the same pipeline delivering PCM16 (converted on the device, half the D2H bytes)
+    std::string run(bool peak_normalize, float * host_dst = nullptr, int16_t * host_pcm = nullptr);
+    std::string fetch_pcm16(int16_t * out, int64_t cap);
+    int16_t * d_pcm = nullptr; int64_t pcm_cap = 0;       // PCM16 image of d_wave (grown on demand)
+    std::string ensure_pcm();
     cudaStream_t copy_stream = nullptr; cudaEvent_t chunk_done = nullptr;
     int fetch_chunk_codes = 24576;   // chunk size of the host-delivery pipeline (mio_decode_wave_batch)
     std::string run_istft_only(const float * spec_host, int n_frames);   // mio_istft

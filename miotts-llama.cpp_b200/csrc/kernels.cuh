@@ -116,5 +116,7 @@ cudaError_t launch_istft(const istft_params & p, cudaStream_t st);
 // per-utterance peak normalisation 0.95/max|s| (src/test-to-speech.cpp:289-300)
 cudaError_t launch_peak_normalize(float * wave, const int32_t * len, const int64_t * out_off, int n_utts,
                                   int samples_per_code, float * peak_scratch, cudaStream_t st);
+// float -> PCM16 with the reference WAV writer's clamp + truncation (src/wav-writer.cpp:39-42)
+cudaError_t launch_pcm16(const float * wave, int16_t * pcm, int64_t begin, int64_t end, cudaStream_t st);
 
 }  // namespace mio

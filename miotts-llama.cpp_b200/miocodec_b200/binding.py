@@ -27,6 +27,7 @@ EXPORTS = [
     "mio_stream_close", "mio_stream_push_codes", "mio_stream_finish", "mio_streams_step", "mio_stream_read",
     "mio_stream_stats", "mio_debug_read", "mio_last_error", "mio_version", "mio_host_alloc", "mio_host_free",
     "mio_profile_enable", "mio_profile_categories", "mio_profile_name", "mio_profile_read", "mio_batch_h2d_bytes",
+    "mio_parse_speech_tokens", "mio_decode_pcm16_batch", "mio_batch_fetch_pcm16", "mio_wav_header", "mio_wav_write_pcm16",
 ]
 
 
@@ -98,6 +99,12 @@ def lib() -> C.CDLL:
     L.mio_profile_read.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(i64)]
     L.mio_batch_h2d_bytes.argtypes = [vp]
     L.mio_batch_h2d_bytes.restype = i64
+    L.mio_parse_speech_tokens.argtypes = [C.c_char_p, i64, i32p, i64]
+    L.mio_parse_speech_tokens.restype = i64
+    L.mio_decode_pcm16_batch.argtypes = [vp, i32p, i32p, C.c_int, f32p, C.c_int, i32p, C.c_int, vp, i64]
+    L.mio_batch_fetch_pcm16.argtypes = [vp, vp, i64]
+    L.mio_wav_header.argtypes = [C.c_int, i64, vp]
+    L.mio_wav_write_pcm16.argtypes = [C.c_char_p, vp, i64, C.c_int]
     L.mio_debug_read.argtypes = [vp, C.c_char_p, f32p, i64]
     L.mio_debug_read.restype = i64
     _lib = L
@@ -129,6 +136,28 @@ def _i32(a) -> np.ndarray:
 
 def _f32(a) -> np.ndarray:
     return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def parse_speech_tokens(text) -> np.ndarray:
+    """parse_speech_tokens (src/token-parser.h:8): the integer codes of every "<|s_N|>" in the text."""
+    raw = text.encode("utf-8") if isinstance(text, str) else bytes(text)
+    n = lib().mio_parse_speech_tokens(raw, len(raw), None, 0)
+    _check(n)
+    out = np.empty(n, dtype=np.int32)
+    if n:
+        _check(lib().mio_parse_speech_tokens(raw, len(raw), out.ctypes.data, n))
+    return out
+
+
+def wav_header(sample_rate: int, n_samples: int) -> bytes:
+    h = (C.c_uint8 * 44)()
+    _check(lib().mio_wav_header(sample_rate, n_samples, h))
+    return bytes(h)
+
+
+def wav_write_pcm16(path: str, pcm, sample_rate: int):
+    pcm = np.ascontiguousarray(pcm, dtype=np.int16)
+    _check(lib().mio_wav_write_pcm16(path.encode(), pcm.ctypes.data, pcm.size, sample_rate))
 
 
 class MioCodec:
@@ -228,6 +257,22 @@ class MioCodec:
             out = np.empty(total, dtype=np.float32)
         _check(lib().mio_decode_wave_batch(self._h, c.ctypes.data, cu.ctypes.data, len(cu) - 1, vt.ctypes.data, vt.shape[0],
                                            vi.ctypes.data, int(peak_normalize), out.ctypes.data, out.size))
+        return out
+
+    def decode_pcm16_batch(self, codes_concat, cu_seqlens, voice_table, voice_ids, peak_normalize=False, out=None):
+        """decode_codes_to_audio + the PCM16 conversion of wav_write (src/wav-writer.cpp:39-42), converted on the device."""
+        c, cu, vt, vi = _i32(codes_concat), _i32(cu_seqlens), _f32(voice_table), _i32(voice_ids)
+        total = int(cu[-1]) * self.samples_per_token
+        if out is None:
+            out = np.empty(total, dtype=np.int16)
+        _check(lib().mio_decode_pcm16_batch(self._h, c.ctypes.data, cu.ctypes.data, len(cu) - 1, vt.ctypes.data, vt.shape[0],
+                                            vi.ctypes.data, int(peak_normalize), out.ctypes.data, out.size))
+        return out
+
+    def batch_fetch_pcm16(self, out: np.ndarray | None = None) -> np.ndarray:
+        if out is None:
+            out = np.empty(self._total, dtype=np.int16)
+        _check(lib().mio_batch_fetch_pcm16(self._h, out.ctypes.data, out.size))
         return out
 
     def profile_enable(self, on: bool = True):

@@ -45,6 +45,9 @@ build_variant() {
   # the reference hot path itself + our C wrapper
   g++ -std=gnu++17 -O2 -fPIC "${arch[@]}" "${INCS[@]}" -I"$REF/src" -c "$REF/src/miocodec.cpp" -o "$obj/ref_miocodec.o" & pids+=($!)
   g++ -std=gnu++17 -O2 -fPIC "${arch[@]}" -I"$REF/src" -c "$REF/src/istft.cpp" -o "$obj/ref_istft.o" & pids+=($!)
+  # the steps either side of the path: token parser and WAV writer, also unmodified
+  g++ -std=gnu++17 -O2 -fPIC "${arch[@]}" -I"$REF/src" -c "$REF/src/token-parser.cpp" -o "$obj/ref_token_parser.o" & pids+=($!)
+  g++ -std=gnu++17 -O2 -fPIC "${arch[@]}" -I"$REF/src" -c "$REF/src/wav-writer.cpp" -o "$obj/ref_wav_writer.o" & pids+=($!)
   g++ -std=gnu++17 -O2 -fPIC "${arch[@]}" -I"$REF/src" -c "$HERE/ref_capi.cpp" -o "$obj/ref_capi.o" & pids+=($!)
   for p in "${pids[@]}"; do wait "$p"; done
   g++ -shared -o "$OUT/libmio_ref_$tag.so" "$obj"/*.o -lpthread -lm -ldl

@@ -148,3 +148,25 @@ def ref_istft_only(spec: np.ndarray, n_fft: int = 392, hop: int = 98) -> np.ndar
     if n < 0:
         return np.empty(0, dtype=np.float32)
     return out[:n].copy()
+
+
+def ref_parse_speech_tokens(text) -> np.ndarray:
+    """The reference's parse_speech_tokens (src/token-parser.cpp:5-28), compiled unmodified into oracle/_ref."""
+    L = C.CDLL(lib_path())
+    L.mio_ref_parse_speech_tokens.argtypes = [C.c_char_p, C.c_long, C.c_void_p, C.c_long]
+    L.mio_ref_parse_speech_tokens.restype = C.c_long
+    raw = text.encode("utf-8") if isinstance(text, str) else bytes(text)
+    n = L.mio_ref_parse_speech_tokens(raw, len(raw), None, 0)
+    out = np.empty(n, dtype=np.int32)
+    if n:
+        L.mio_ref_parse_speech_tokens(raw, len(raw), out.ctypes.data, n)
+    return out
+
+
+def ref_wav_write(path: str, samples: np.ndarray, sample_rate: int) -> None:
+    """The reference's wav_write (src/wav-writer.cpp:24-45)."""
+    L = C.CDLL(lib_path())
+    L.mio_ref_wav_write.argtypes = [C.c_char_p, C.c_void_p, C.c_long, C.c_int]
+    s = np.ascontiguousarray(samples, dtype=np.float32)
+    if L.mio_ref_wav_write(path.encode(), s.ctypes.data, s.size, sample_rate) != 0:
+        raise OSError("reference wav_write failed")

@@ -10,6 +10,8 @@
 // timed CPU baseline.
 #include "miocodec.h"   // reference header, found via -I/root/reference/src
 #include "istft.h"      // reference header
+#include "token-parser.h"   // reference header (pre-path ingest)
+#include "wav-writer.h"     // reference header (post-path epilogue)
 
 #include <chrono>
 #include <cstdio>
@@ -110,6 +112,19 @@ int mio_ref_load_voice(const char * path, float * out, int cap) {
     if (e.empty() || (int) e.size() > cap) return -1;
     memcpy(out, e.data(), e.size() * sizeof(float));
     return (int) e.size();
+}
+
+// parse_speech_tokens (/root/reference/src/token-parser.cpp:5-28). Returns the number of codes found; writes
+// min(count, cap) of them.
+long mio_ref_parse_speech_tokens(const char * text, long text_len, int * out, long cap) {
+    std::vector<int> codes = parse_speech_tokens(std::string(text, (size_t) text_len));
+    for (long i = 0; i < (long) codes.size() && i < cap; i++) out[i] = codes[i];
+    return (long) codes.size();
+}
+
+// wav_write (/root/reference/src/wav-writer.cpp:24-45): 44-byte RIFF header + PCM16 (clamp(s*32767) truncated).
+int mio_ref_wav_write(const char * path, const float * samples, long n, int sample_rate) {
+    return wav_write(std::string(path), std::vector<float>(samples, samples + n), sample_rate) ? 0 : -1;
 }
 
 }  // extern "C"
