@@ -382,6 +382,12 @@ def main():
                 s.update(bound="hbm", achieved=v["bytes"] / (v["ms"] / 1e3) / 1e9, unit="GB/s")
                 s["frac"] = s["achieved"] / peaks["hbm"]
             stages[k] = s
+        # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this workload
+        traffic, traffic_src = None, None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if args.workload == "c3" and os.path.exists(tpath):
+            tj = json.load(open(tpath))
+            traffic, traffic_src = tj["gemm_split3"]["dram_bytes_per_launch"], tj["source"]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -395,7 +401,8 @@ def main():
             "clocks": clocks,
             "roofline": {"kernel": "gemm_tc_kernel (tcgen05 split-precision tap-GEMM, all linear/ConvT layers)",
                          "bound": "tensor", "achieved": ach_tf, "peak": peaks["tf_sus"], "unit": "TFLOP/s",
-                         "frac": ach_tf / peaks["tf_sus"], "traffic": None,
+                         "frac": ach_tf / peaks["tf_sus"], "traffic": traffic,
+                         "executed_mma_frac": 3.0 * ach_tf / peaks["tf_sus"], "traffic_source": traffic_src,
                          "note": f"algorithmic FLOPs 2*M*N*K*taps per launch (3 MMA passes executed per algorithmic FLOP); "
                                  f"peak = {peaks['src']} sustained dense bf16; avg launch {g['ms'] / max(1, g['launches']):.3f} ms "
                                  f"over {int(g['launches'])} launches (separate event-instrumented pass of {prof_steps} steps, {prof_ms / prof_steps:.1f} ms/step); "

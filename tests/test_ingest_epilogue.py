@@ -118,7 +118,12 @@ def test_pcm16_batch_is_the_reference_conversion_of_the_float_batch(codec, asset
     # small chunks: every chunk boundary lands on an utterance boundary, not on an 8-sample boundary
     codec.set_option("fetch_chunk_codes", "64")
     try:
-        assert np.array_equal(codec.decode_pcm16_batch(codes, cu, voices, vids, peak_normalize=True), pcm)
+        wave_s = codec.decode_wave_batch(codes, cu, voices, vids, peak_normalize=True)
+        pcm_s = codec.decode_pcm16_batch(codes, cu, voices, vids, peak_normalize=True)
+        bad = np.flatnonzero(pcm_s != _pcm16_numpy(wave_s))
+        assert bad.size == 0, (bad[:8], pcm_s[bad[:8]], _pcm16_numpy(wave_s)[bad[:8]])
+        # chunking changes which rows share a GEMM tile, not the arithmetic of a row
+        assert np.abs(wave_s - wave).max() < 1e-5, np.abs(wave_s - wave).max()
     finally:
         codec.set_option("fetch_chunk_codes", "24576")
     from oracle import ref
