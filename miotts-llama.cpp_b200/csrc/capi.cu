@@ -112,6 +112,12 @@ int mio_ctx_set_option(mio_ctx * c, const char * key, const char * value) {
         c->E.fetch_chunk_codes = (int) v;
         return MIO_OK;
     }
+    if (!strcmp(key, "fetch_tail_percent")) {
+        const long v = strtol(value, nullptr, 10);
+        if (v < 0 || v > 50) return fail(MIO_ERR_ARG, "bad argument: fetch_tail_percent out of range");
+        c->E.fetch_tail_percent = (int) v;
+        return MIO_OK;
+    }
     if (!strcmp(key, "debug_snapshots")) {
         c->E.debug_snap = strcmp(value, "0") != 0;
         return MIO_OK;
@@ -230,7 +236,7 @@ void * mio_batch_wave_device(mio_ctx * c) { return c ? (void *) c->E.d_wave : nu
 int mio_decode_wave_batch(mio_ctx * c, const int32_t * codes, const int32_t * cu, int n_utts, const float * vt, int nv,
                           const int32_t * vids, int peak_normalize, float * out, int64_t cap) {
     if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
-    // pipelined delivery: the batch is cut into chunks of ~fetch_chunk_codes codes; chunk i's D2H copy runs on a
+    // pipelined delivery (engine::upload: chunks as large as the workspace allows + one tail split); chunk i's D2H copy runs on a
     // second stream while chunk i+1 computes
     TRY(c->E.upload(codes, cu, n_utts, vt, nv, vids, c->E.fetch_chunk_codes + c->E.fetch_chunk_codes / 16));
     if (cap < c->E.wave_samples) return fail(MIO_ERR_ARG, "capacity too small");

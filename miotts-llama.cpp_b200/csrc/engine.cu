@@ -590,18 +590,30 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
     const int fpc = hp.frames_per_code;
     int64_t rows_total = 0;
     std::vector<int32_t> chunk_cu_all;   // per chunk: local prefix of istft chunk counts (n+1 entries each)
+    // Pipelined delivery: chunk i's D2H copy runs while chunk i+1 computes, so only the LAST copy is exposed.  Every
+    // extra chunk costs ~1 ms of launch tails (160 kernels), so the batch is cut as rarely as the workspace allows and
+    // the final chunk is split once more into (100 - p) % and p %: with p = fetch_tail_percent ~ D2H time / (compute +
+    // D2H time) the small tail computes exactly while the big piece is copied, and only the tail's own copy is exposed.
+    int64_t rows_left = 0;
+    for (int i = 0; i < n_utts; i++) rows_left += (int64_t) std::max(0, cu[i + 1] - cu[i]) + 1;
+    bool tail_split_done = false;
     int u = 0;
     while (u < n_utts) {
         chunk_info c;
         c.utt0 = u; c.row0 = (int) rows_total; c.cu0 = (int) chunk_cu_all.size();
         int rows = 0, blocks = 0;
         chunk_cu_all.push_back(0);
+        int row_cap_c = row_cap;
+        if (chunk_rows_limit > 0 && fetch_tail_percent > 0 && !tail_split_done && rows_left <= row_cap && rows_left >= 4096) {
+            row_cap_c = (int) (rows_left - rows_left * fetch_tail_percent / 100);
+            tail_split_done = true;
+        }
         while (u < n_utts) {
             const int T = cu[u + 1] - cu[u];
             if (T < 0) return "cu_seqlens must be non-decreasing";
             if (T + 1 > max_rows1) return "utterance of " + std::to_string(T) + " codes exceeds max_chunk_codes";
             if (voice_ids[u] < 0 || voice_ids[u] >= nv) return "voice id out of range";
-            if ((rows + T + 1 > row_cap && rows > 0) || rows + T + 1 > max_rows1 || (u - c.utt0) >= max_utts) break;
+            if ((rows + T + 1 > row_cap_c && rows > 0) || rows + T + 1 > max_rows1 || (u - c.utt0) >= max_utts) break;
             lay.start.push_back(rows); lay.len.push_back(T); lay.voice.push_back(voice_ids[u]);
             lay.out_off.push_back((int64_t) cu[u] * hp.samples_per_token);
             for (int i = 0; i < T; i++) {
@@ -618,7 +630,7 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
             u++;
         }
         c.n_utts = u - c.utt0; c.rows1 = rows; c.istft_blocks = blocks;
-        rows_total += rows;
+        rows_total += rows; rows_left -= rows;
         chunks.push_back(c);
     }
     lay.rows1 = (int) rows_total;

@@ -111,7 +111,8 @@ struct engine {
     int16_t * d_pcm = nullptr; int64_t pcm_cap = 0;       // PCM16 image of d_wave (grown on demand)
     std::string ensure_pcm();
     cudaStream_t copy_stream = nullptr; cudaEvent_t chunk_done = nullptr;
-    int fetch_chunk_codes = 24576;   // chunk size of the host-delivery pipeline (mio_decode_wave_batch)
+    int fetch_tail_percent = 12;     // size of the last chunk of the host-delivery pipeline, % of the final workspace chunk
+    int fetch_chunk_codes = 1 << 20; // optional extra cap on the chunk size of the host-delivery pipeline
     std::string run_istft_only(const float * spec_host, int n_frames);   // mio_istft
     std::string sync();                                   // stream sync + error flag
     std::string fetch_wave(float * out, int64_t cap);

@@ -3,11 +3,12 @@
 // Replaces istft() / irfft() of the reference (src/istft.cpp:43-108).  Each spectrogram frame is read once from
 // HBM (plus a 4-frame halo per block) and each output sample is written exactly once.
 //
-// Block = 256 threads.  A block produces ISTFT_SEG_PER_BLOCK output hops (98 samples each) of one utterance and
-// therefore needs the frames g0-2 .. g0+G+1 (G+4 = 32 frame slots in shared memory, 1680 B each).
+// Block = 384 threads.  A block produces ISTFT_SEG_PER_BLOCK output hops (98 samples each) of one utterance and
+// therefore needs the frames g0-2 .. g0+G+1 (G+4 = 48 frame slots in shared memory, 1680 B each; 9 % of the FFTs are
+// halo recomputation, two blocks = 24 warps per SM).
 //   phase 0: one bulk async copy (cp.async.bulk, 1600 B = one padded spectrogram row) per frame, issued by the lanes
 //            of warp 0 behind one mbarrier: no per-element load instructions, all rows in flight at once
-//   phase 1: every 16-lane group (14 active lanes) transforms one frame in place, 16 frames at a time
+//   phase 1: every 16-lane group (14 active lanes) transforms one frame in place, 24 frames at a time
 //   phase 2: each output sample sums its <= 4 windowed contributions in ascending frame order (the order of the
 //            reference's accumulation loop, src/istft.cpp:84-93), divides by the window-square sum and is stored.
 // The kernel is instruction-bound (about 350 warp instructions per frame for the FFT), not HBM-bound: see DESIGN.md.
@@ -19,9 +20,9 @@ namespace mio {
 
 constexpr int IST_NFFT = 392, IST_HOP = 98, IST_NFREQ = 197, IST_PAD = 147;
 constexpr int IST_G = ISTFT_SEG_PER_BLOCK;
-constexpr int IST_SLOTS = IST_G + 4;                       // 32
+constexpr int IST_SLOTS = IST_G + 4;                       // 48
 constexpr int IST_SLOT_FLOATS = 2 * IFFT_SLOT_F2;          // 420
-constexpr int IST_THREADS = 256;
+constexpr int IST_THREADS = 384;                          // 24 groups of 16 lanes: the 48 slots in two passes
 constexpr size_t IST_SMEM = (size_t) (IST_SLOTS * IST_SLOT_FLOATS + 2 * 196 * 2 + IST_NFFT + 100) * sizeof(float) + 16;
 
 __device__ __forceinline__ void bulk_load_1d(void * dst, const void * src, uint32_t bytes, uint64_t * bar) {
@@ -30,7 +31,7 @@ __device__ __forceinline__ void bulk_load_1d(void * dst, const void * src, uint3
                  : "memory");
 }
 
-__global__ void __launch_bounds__(IST_THREADS, 3) istft_kernel(istft_params p, const float * __restrict__ tw392g,
+__global__ void __launch_bounds__(IST_THREADS, 2) istft_kernel(istft_params p, const float * __restrict__ tw392g,
                                                             const float * __restrict__ tw196g) {
     extern __shared__ __align__(16) float ist_smem[];
     float * slots = ist_smem;
@@ -80,9 +81,9 @@ __global__ void __launch_bounds__(IST_THREADS, 3) istft_kernel(istft_params p, c
 
     // phase 1
     {
-        const int grp = threadIdx.x >> 4, t14 = threadIdx.x & 15;   // 16 groups of 16 lanes
+        const int grp = threadIdx.x >> 4, t14 = threadIdx.x & 15;   // IST_THREADS / 16 groups of 16 lanes
 #pragma unroll 1
-        for (int base = 0; base < IST_SLOTS; base += 16) {
+        for (int base = 0; base < IST_SLOTS; base += IST_THREADS / 16) {
             const int fr = base + grp;
             const bool active = (t14 < 14) && (fr < nfr);
             float * slot = slots + fr * IST_SLOT_FLOATS;
@@ -101,15 +102,16 @@ __global__ void __launch_bounds__(IST_THREADS, 3) istft_kernel(istft_params p, c
     // phase 2: trimmed output sample s = 98 H + r sits at untrimmed position P = s + 147 = 98 (H + 1) + (r + 49):
     // frames H-2 .. H+1 (r < 49) or H-1 .. H+2 (r >= 49) cover it with window indices j0, j0-98, j0-196, j0-294.
     // A thread owns one r (so the frame offset, the window index and the envelope are loop invariants) and walks
-    // every second hop of the block: 196 of the 256 threads, ~10 instructions per sample.
-    if (threadIdx.x < 2 * IST_HOP) {
+    // every third hop of the block: 294 of the 384 threads, ~10 instructions per sample.
+    constexpr int P2 = IST_THREADS / IST_HOP;             // hop phases: 3
+    if (threadIdx.x < P2 * IST_HOP) {
         float * out = p.wave + p.out_off[u];
         const int r = threadIdx.x % IST_HOP, par = threadIdx.x / IST_HOP;
         const int up = (r >= 49) ? 1 : 0;
         const int j0 = r + 343 - 98 * up;
         const float ws4 = wsum4[r];
         const float * col = slots + j0;                   // + (frame - f_lo) * IST_SLOT_FLOATS - 98 * k
-        for (int H = g0 + par; H < g1; H += 2) {
+        for (int H = g0 + par; H < g1; H += P2) {
             const int t0 = H - 2 + up;
             float acc = 0.f, wsum;
             if (t0 >= 0 && t0 + 3 < F) {

@@ -111,7 +111,7 @@ struct istft_params {
     int frames_per_code;         // 18
     int total_chunks;
 };
-constexpr int ISTFT_SEG_PER_BLOCK = 28;   // output hops (98 samples) per block; +4 halo frames
+constexpr int ISTFT_SEG_PER_BLOCK = 44;   // output hops (98 samples) per block; +4 halo frames
 cudaError_t launch_istft(const istft_params & p, cudaStream_t st);
 // per-utterance peak normalisation 0.95/max|s| (src/test-to-speech.cpp:289-300)
 cudaError_t launch_peak_normalize(float * wave, const int32_t * len, const int64_t * out_off, int n_utts,

@@ -122,10 +122,12 @@ def test_pcm16_batch_is_the_reference_conversion_of_the_float_batch(codec, asset
         pcm_s = codec.decode_pcm16_batch(codes, cu, voices, vids, peak_normalize=True)
         bad = np.flatnonzero(pcm_s != _pcm16_numpy(wave_s))
         assert bad.size == 0, (bad[:8], pcm_s[bad[:8]], _pcm16_numpy(wave_s)[bad[:8]])
-        # chunking changes which rows share a GEMM tile, not the arithmetic of a row
-        assert np.abs(wave_s - wave).max() < 1e-5, np.abs(wave_s - wave).max()
+        # another chunking regroups the fp32 partial sums of the GroupNorm statistics: same tolerance as
+        # test_gpu_parity.test_multi_chunk_batches
+        from conftest import snr_db
+        assert snr_db(wave_s, wave) > 55.0
     finally:
-        codec.set_option("fetch_chunk_codes", "24576")
+        codec.set_option("fetch_chunk_codes", str(1 << 20))
     from oracle import ref
     if ref.available():                                              # file == the reference writer's file for the same floats
         a, b = tmp_path / "ref.wav", tmp_path / "ours.wav"
