@@ -20,8 +20,10 @@ for p in "${pids[@]}"; do wait "$p"; done
 "$NVCC" -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT/libmiocodec_b200.so" "$OBJ"/gemm.o "$OBJ"/gemm3.o "$OBJ"/attention.o "$OBJ"/elementwise.o "$OBJ"/istft.o "$OBJ"/engine.o "$OBJ"/stream.o "$OBJ"/capi.o "$OBJ"/gguf_reader.o -cudart static
 echo "built $OUT/libmiocodec_b200.so"
 # C++ drop-in layer (reference-named entry points on top of the C ABI) + its test program
-g++ -O2 -std=c++17 -fPIC -shared -I"$HERE/shim" "$HERE/shim/miocodec_shim.cpp" -o "$OUT/libmiocodec_shim.so" \
+g++ -O2 -std=c++17 -fPIC -shared -I"$HERE/shim" "$HERE/shim/miocodec_shim.cpp" "$HERE/shim/batch_tts.cpp" -o "$OUT/libmiocodec_shim.so" \
     -L"$OUT" -lmiocodec_b200 -Wl,-rpath,'$ORIGIN'
 g++ -O2 -std=c++17 -I"$HERE/shim" "$HERE/../tests/shim_demo.cpp" -o "$OUT/shim_demo" -L"$OUT" -lmiocodec_shim -lmiocodec_b200 \
     -Wl,-rpath,'$ORIGIN'
-echo "built $OUT/libmiocodec_shim.so and $OUT/shim_demo"
+g++ -O2 -std=c++17 -I"$HERE/shim" "$HERE/../tests/batch_tts_demo.cpp" -o "$OUT/batch_tts_demo" -L"$OUT" -lmiocodec_shim -lmiocodec_b200 \
+    -Wl,-rpath,'$ORIGIN'
+echo "built $OUT/libmiocodec_shim.so, $OUT/shim_demo and $OUT/batch_tts_demo"
