@@ -261,6 +261,8 @@ def main():
     ap.add_argument("--workload", default="c3", choices=["c2", "c3", "c4", "c5"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-latency", action="store_true",
+                    help="skip C2's 100-call latency loop (use under ncu: the loop adds ~16k profiled launches)")
     ap.add_argument("--gemm", default=None)
     ap.add_argument("--chunk", type=int, default=None, help="max_chunk_codes of the context (workspace rows)")
     args = ap.parse_args()
@@ -355,7 +357,7 @@ def main():
     d2h = int(h_wave.nbytes)
     # C2 is the latency configuration: p50 / p99 of 100 synchronous single-utterance calls, host to host
     latency = None
-    if args.workload == "c2":
+    if args.workload == "c2" and not args.no_latency:
         emb = wl["voice_table"][int(wl["voice_ids"][0])]
         lat = []
         for i in range(103):

@@ -450,25 +450,46 @@ cudaError_t launch_split(const float * x, int rows, int C, const row_map & rm, i
 
 // AdaLN conditioning: mod[v][j] = b[j] + sum_k W[j][k] * silu(emb[v][k])
 // (compute_adaln3, src/miocodec.cpp:310-319 and :654-655). One warp per output row j, all voices.
-__global__ void cond_kernel(const float * __restrict__ voice_table, int n_voices, int adaln_dim,
+__global__ void cond_silu_kernel(const float * __restrict__ voice_table, int n, float * __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = silu_f(voice_table[i]);
+}
+
+// one warp per output row j (its 128 weights live in registers), looping over the voices of this blockIdx.y
+__global__ void cond_kernel(const float * __restrict__ voice_silu, int n_voices, int adaln_dim,
                             const float * __restrict__ w, const float * __restrict__ b, int cond_rows,
                             float * __restrict__ mod) {
     const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (j >= cond_rows) return;
+    const float bj = b[j];
+    if (adaln_dim == 128) {
+        const float4 wj = __ldg((const float4 *) (w + (size_t) j * 128) + lane);
+        for (int v = blockIdx.y; v < n_voices; v += gridDim.y) {
+            const float4 s = __ldg((const float4 *) (voice_silu + (size_t) v * 128) + lane);
+            // same summation order per lane as the strided loop below would not matter: fp32 dot of 128 terms,
+            // reduced over the warp; the reference's ggml_mul_mat sums in SIMD lanes of its own order
+            float acc = wj.x * s.x + wj.y * s.y + wj.z * s.z + wj.w * s.w;
+            acc = warp_sum(acc);
+            if (lane == 0) mod[(size_t) v * cond_rows + j] = acc + bj;
+        }
+        return;
+    }
     for (int v = blockIdx.y; v < n_voices; v += gridDim.y) {
         float acc = 0.f;
-        for (int k = lane; k < adaln_dim; k += 32) acc += w[(size_t) j * adaln_dim + k] * silu_f(voice_table[(size_t) v * adaln_dim + k]);
+        for (int k = lane; k < adaln_dim; k += 32) acc += w[(size_t) j * adaln_dim + k] * voice_silu[(size_t) v * adaln_dim + k];
         acc = warp_sum(acc);
-        if (lane == 0) mod[(size_t) v * cond_rows + j] = acc + b[j];
+        if (lane == 0) mod[(size_t) v * cond_rows + j] = acc + bj;
     }
 }
 
 cudaError_t launch_cond(const float * voice_table, int n_voices, int adaln_dim, const float * w, const float * b,
-                        int cond_rows, float * mod, cudaStream_t st) {
+                        int cond_rows, float * silu_scratch, float * mod, cudaStream_t st) {
     if (n_voices <= 0) return cudaSuccess;
-    dim3 grid((cond_rows + 7) / 8, min(n_voices, 64));
-    cond_kernel<<<grid, 256, 0, st>>>(voice_table, n_voices, adaln_dim, w, b, cond_rows, mod);
+    const int n = n_voices * adaln_dim;
+    cond_silu_kernel<<<(n + 255) / 256, 256, 0, st>>>(voice_table, n, silu_scratch);
+    dim3 grid((cond_rows + 7) / 8, min(n_voices, 8));
+    cond_kernel<<<grid, 256, 0, st>>>(silu_scratch, n_voices, adaln_dim, w, b, cond_rows, mod);
     return cudaGetLastError();
 }
 

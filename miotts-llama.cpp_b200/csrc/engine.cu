@@ -114,7 +114,7 @@ engine::~engine() {
     if (stream && own_stream) cudaStreamSynchronize(stream);
     auto F = [](void * p) { if (p) cudaFree(p); };
     F(x768); F(qkv_hi); F(qkv_lo); F(x512); F(y512); F(x256); F(y256); F(x128); F(y128); F(spec); F(mod); F(peak);
-    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_stats); F(gn_mr); F(attn_b1); F(attn_b2); F(err_flag);
+    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_stats); F(gn_mr); F(voice_silu); F(attn_b1); F(attn_b2); F(err_flag);
     F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_out_off); F(d_voice_table); F(d_wave);
     for (void * p : w_allocs) F(p);
     F(d_emit); F(d_emit_jobs); F(d_pcm);
@@ -200,6 +200,12 @@ struct loader {
         if (e.empty()) e = make_map(&W.tm2_hi, W.hi, N, K * taps, W.bn2 / 2);
         if (e.empty() && W.lo) e = make_map(&W.tm2_lo, W.lo, N, K * taps, W.bn2 / 2);
         if (e.empty() && !W.lo) W.tm2_lo = W.tm2_hi;
+        if (e.empty()) e = make_map(&W.tm128_hi, W.hi, N, K * taps, 64);
+        if (e.empty() && W.lo) e = make_map(&W.tm128_lo, W.lo, N, K * taps, 64);
+        if (e.empty() && !W.lo) W.tm128_lo = W.tm128_hi;
+        if (e.empty()) e = make_map(&W.tm64_hi, W.hi, N, K * taps, 32);
+        if (e.empty() && W.lo) e = make_map(&W.tm64_lo, W.lo, N, K * taps, 32);
+        if (e.empty() && !W.lo) W.tm64_lo = W.tm64_hi;
         if (!e.empty()) { err = e; return false; }
         return true;
     }
@@ -289,6 +295,7 @@ std::string engine::load(const std::string & path, int dev) {
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, dev));
     if (prop.major != 10) return std::string("device '") + prop.name + "' is not sm_100 (B200); this build contains sm_100a code only";
+    num_sms = prop.multiProcessorCount;
 
     gguf_file g;
     std::string e = g.open(path);
@@ -540,6 +547,7 @@ std::string engine::ensure_workspace() {
     A(gn_mr, (size_t) max_utts * 32);
     A(attn_b1, R1); A(attn_b2, R2);
     A(mod, (size_t) max_voices * w.cond_rows);
+    A(voice_silu, (size_t) max_voices * hp.adaln_dim);
     A(peak, (size_t) max_utts);
     A(err_flag, 1);
 #undef A
@@ -747,7 +755,15 @@ cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_pa
             o0 = o1 = out_map(p.out_f32, 4, M, ncols, (size_t) p.ld_out * 4);
         }
         if (!o0 || !o1) { prof_end(); return cudaErrorInvalidValue; }
-        ce = launch_gemm_tc3(p, A.tm_hi, A.tm_lo, W.tm2_hi, W.tm2_lo, *o0, *o1, W.bn2, stream);
+        // tile width: the widest of {bn2, 128, 64} that still gives every CTA pair a tile (small M = latency mode);
+        // SwiGLU pairs need >= 64 accumulator columns per epilogue warp, i.e. BN >= 128
+        const int tiles_m = (M + 255) / 256, pairs = num_sms / 2;
+        int bn = W.bn2;
+        const int bn_min = (p.epi == EPI_SWIGLU) ? 128 : 64;
+        while (bn > bn_min && tiles_m * ((W.N + bn - 1) / bn) < pairs) bn >>= 1;
+        const CUtensorMap & bh = bn == W.bn2 ? W.tm2_hi : (bn == 128 ? W.tm128_hi : W.tm64_hi);
+        const CUtensorMap & bl = bn == W.bn2 ? W.tm2_lo : (bn == 128 ? W.tm128_lo : W.tm64_lo);
+        ce = launch_gemm_tc3(p, A.tm_hi, A.tm_lo, bh, bl, *o0, *o1, bn, stream);
     } else if (gemm_gen == 2) ce = launch_gemm_tc2(p, A.tm_hi, A.tm_lo, W.tm2_hi, W.tm2_lo, W.bn2, stream);
     else ce = launch_gemm_tc(p, A.tm_hi, A.tm_lo, W.tm_hi, W.tm_lo, W.box_n, stream);
     prof_end();
@@ -1000,7 +1016,8 @@ std::string engine::run(bool peak_normalize, float * host_dst, int16_t * host_pc
     launches = 0;
     snaps.clear();
     // AdaLN conditioning vectors of every voice of the batch (compute_adaln3, src/miocodec.cpp:310-319)
-    if (lay.n_utts > 0) CKR(CAT_COND, 0.0, launch_cond(d_voice_table, n_voices, hp.adaln_dim, w.cond_w, w.cond_b, w.cond_rows, mod, stream));
+    if (lay.n_utts > 0) CKR(CAT_COND, 0.0, launch_cond(d_voice_table, n_voices, hp.adaln_dim, w.cond_w, w.cond_b, w.cond_rows, voice_silu, mod, stream));
+    if (lay.n_utts > 0) launches++;   // two kernels (silu of the embeddings, then the GEMV rows)
     if (host_pcm) { std::string e = ensure_pcm(); if (!e.empty()) return e; }
     if ((host_dst || host_pcm) && !copy_stream) {
         CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));

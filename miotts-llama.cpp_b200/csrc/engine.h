@@ -49,6 +49,7 @@ struct engine {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     bool use_simt = false;
+    int num_sms = 148;               // multiProcessorCount of the device (tile-width choice of the GEMM dispatch)
     int gemm_gen = 3;                // 1: one CTA per tile; 2: persistent CTA pairs (cta_group::2); 3: + TMA-store epilogue (default)
     int max_rows1 = 65536 + 4096;    // workspace rows at code resolution (codes + one pad row per utterance), ~8.5 GB
     bool ws_ready = false;
@@ -65,6 +66,7 @@ struct engine {
            *h512_hi = nullptr, *h512_lo = nullptr, *qkv_hi = nullptr, *qkv_lo = nullptr;
     bool attn_simt = false;           // MIO_ATTN=simt: CUDA-core validation kernel
     double * gn_stats = nullptr;      // [GN_SLOTS][max_utts][32][2]
+    float * voice_silu = nullptr;     // [max_voices][128] silu(voice embedding), input of cond_kernel
     float2 * gn_mr = nullptr;         // [max_utts][32] (mean, rstd) of the GroupNorm being applied
     int2 * attn_b1 = nullptr;         // [max_rows1]   valid key range per prenet row (attn_bounds_kernel)
     int2 * attn_b2 = nullptr;         // [2*max_rows1] valid key range per decoder row

@@ -391,7 +391,8 @@ static cudaError_t launch_tc3_epi(const gemm_params & p, const CUtensorMap & a_h
         switch (p.epi) {
             case EPI_SWIGLU:
                 if (p.N % 64 != 0) return cudaErrorInvalidValue;
-                return launch_tc3_inst<BN, 3, EPI_SWIGLU>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+                if constexpr (BN >= 128) return launch_tc3_inst<BN, 3, EPI_SWIGLU>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+                else return cudaErrorInvalidValue;   // a (gate, up) pair row needs 64 accumulator columns per warp
             case EPI_SPLIT: return launch_tc3_inst<BN, 3, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
             case EPI_SNAKE: return launch_tc3_inst<BN, 3, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
             case EPI_HEAD: return launch_tc3_inst<BN, 3, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
@@ -414,6 +415,10 @@ cudaError_t launch_gemm_tc3(const gemm_params & p, const CUtensorMap & tmA_hi, c
     if (bn == 128) {
         if (p.npass == 3) return launch_tc3_epi<128, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
         return launch_tc3_epi<128, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
+    }
+    if (bn == 64) {   // latency mode: small M, more (narrower) tiles
+        if (p.npass == 3) return launch_tc3_epi<64, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
+        return launch_tc3_epi<64, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
     }
     return cudaErrorInvalidValue;
 }

@@ -95,7 +95,7 @@ cudaError_t launch_split(const float * x, int rows, int C, const row_map & rm, i
                          cudaStream_t st);
 // mod[voice][cond_rows] = W[cond_rows][128] * silu(emb[voice]) + b
 cudaError_t launch_cond(const float * voice_table, int n_voices, int adaln_dim, const float * w, const float * b,
-                        int cond_rows, float * mod, cudaStream_t st);
+                        int cond_rows, float * silu_scratch /*[n_voices*adaln_dim]*/, float * mod, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------ ISTFT
 struct istft_params {

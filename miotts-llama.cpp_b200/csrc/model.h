@@ -38,6 +38,9 @@ struct gemm_weight {
     int box_n = 0;
     CUtensorMap tm2_hi, tm2_lo;       // box {64, bn2 / 2}     (generation-2 kernel, CTA pair per 256 x bn2 tile)
     int bn2 = 0;
+    // narrower tiles for small M (a single short utterance has too few 256 x bn2 tiles to fill 74 CTA pairs):
+    // box {64, 64} and {64, 32} for 256 x 128 and 256 x 64 tiles
+    CUtensorMap tm128_hi, tm128_lo, tm64_hi, tm64_lo;
 };
 
 struct resblock_w {
