@@ -414,7 +414,7 @@ def main():
                     "ms_per_step": e2e_ms_max / args.steps},
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": {"kernel": "gemm_tc_kernel (tcgen05 split-precision tap-GEMM, all linear/ConvT layers)",
+            "roofline": {"kernel": "gemm_tc3_kernel<BN, 3, epilogue> (tcgen05 split-precision tap-GEMM, all linear/ConvT layers)",
                          "bound": "tensor", "achieved": ach_tf, "peak": peaks["tf_sus"], "unit": "TFLOP/s",
                          "frac": ach_tf / peaks["tf_sus"], "traffic": traffic,
                          "executed_mma_frac": 3.0 * ach_tf / peaks["tf_sus"], "traffic_source": traffic_src,

@@ -196,7 +196,9 @@ struct loader {
         std::string e = make_map(&W.tm_hi, W.hi, N, K * taps, W.box_n);
         if (e.empty() && W.lo) e = make_map(&W.tm_lo, W.lo, N, K * taps, W.box_n);
         if (e.empty() && !W.lo) W.tm_lo = W.tm_hi;
-        W.bn2 = (N % 256 == 0) ? 256 : 128;
+        // 256-wide tiles whenever they pad N no further than 128-wide ones would (e.g. the head, N = 394 -> 512 either
+        // way): half as many passes over the A operand
+        W.bn2 = ((N + 255) / 256 * 256 == (N + 127) / 128 * 128) ? 256 : 128;
         if (e.empty()) e = make_map(&W.tm2_hi, W.hi, N, K * taps, W.bn2 / 2);
         if (e.empty() && W.lo) e = make_map(&W.tm2_lo, W.lo, N, K * taps, W.bn2 / 2);
         if (e.empty() && !W.lo) W.tm2_lo = W.tm2_hi;
