@@ -286,13 +286,13 @@ cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, 
 constexpr int GN_ROWS = 64;
 
 __global__ void gn_stats_kernel(const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt,
-                                int row_div, double * __restrict__ stats) {
+                                int row_div, double * __restrict__ stats, int rows_per_block) {
     const int c4 = threadIdx.x;                    // float4 index within the row
     const int cpg = C / 32;                        // channels per group: 16, 8 or 4
     const int tpg = cpg / 4;                       // threads per group: 4, 2 or 1
     const int group = (c4 * 4) / cpg;
-    const int r0 = blockIdx.x * GN_ROWS;
-    const int r1 = min(rows, r0 + GN_ROWS);
+    const int r0 = blockIdx.x * rows_per_block;
+    const int r1 = min(rows, r0 + rows_per_block);
     float s = 0.f, q = 0.f;
     int cur = -1;
     auto flush = [&](int utt) {
@@ -331,7 +331,9 @@ cudaError_t launch_gn_stats(const float * x, int rows, int C, const row_map & rm
                             cudaStream_t st) {
     if (rows <= 0) return cudaSuccess;
     if (C % 128 != 0) return cudaErrorInvalidValue;
-    gn_stats_kernel<<<(rows + GN_ROWS - 1) / GN_ROWS, C / 4, 0, st>>>(x, rows, C, rm.row_utt, row_div, stats);
+    // few rows (a single short utterance): shorter row runs per block so the serial load rounds do not set the latency
+    const int rpb = (rows >= GN_ROWS * 148 * 4) ? GN_ROWS : 16;
+    gn_stats_kernel<<<(rows + rpb - 1) / rpb, C / 4, 0, st>>>(x, rows, C, rm.row_utt, row_div, stats, rpb);
     return cudaGetLastError();
 }
 
@@ -364,7 +366,8 @@ __device__ __forceinline__ float silu_fast(float x) { return __fdividef(x, 1.0f 
 
 __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
         const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt, int row_div,
-        const float2 * __restrict__ mr, const float * __restrict__ w, const float * __restrict__ b, __half * __restrict__ out) {
+        const float2 * __restrict__ mr, const float * __restrict__ w, const float * __restrict__ b, __half * __restrict__ out,
+        int rows_per_block) {
     const int C8 = C >> 3;                       // threads per row: 64, 32 or 16
     const int rpp = 256 / C8;                    // rows per pass of the block
     const int c = (threadIdx.x % C8) * 8;
@@ -373,7 +376,7 @@ __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
     const int g0 = c / cpg, g1 = (c + 4) / cpg;
     const float4 w0 = __ldg((const float4 *) (w + c)), w1 = __ldg((const float4 *) (w + c + 4));
     const float4 b0 = __ldg((const float4 *) (b + c)), b1 = __ldg((const float4 *) (b + c + 4));
-    const int r_begin = blockIdx.x * GNA_ROWS, r_end = min(rows, r_begin + GNA_ROWS);
+    const int r_begin = blockIdx.x * rows_per_block, r_end = min(rows, r_begin + rows_per_block);
     for (int rb = r_begin + rl; rb < r_end; rb += 4 * rpp) {
         int u[4];
         float4 v0[4], v1[4];
@@ -413,7 +416,8 @@ cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map
     if (rows <= 0) return cudaSuccess;
     if (C % 128 != 0 || C > 2048) return cudaErrorInvalidValue;
     gn_finalize_kernel<<<(rm.n_utts * 32 + 255) / 256, 256, 0, st>>>(stats, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
-    gn_apply_silu_kernel<<<(rows + GNA_ROWS - 1) / GNA_ROWS, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out);
+    const int rpb = (rows >= GNA_ROWS * 148 * 2) ? GNA_ROWS : 16;      // few rows: more, shorter blocks (latency mode)
+    gn_apply_silu_kernel<<<(rows + rpb - 1) / rpb, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb);
     return cudaGetLastError();
 }
 
