@@ -252,6 +252,28 @@ def run_streaming(args):
     codec.close()
 
 
+def bind_to_gpu_numa_node(local: int):
+    """One process per GPU: pin this rank (and the pinned host buffers it is about to allocate) to the CPUs NVML reports
+    as local to its GPU, so that with several ranks per box every D2H copy stays on its own socket.  Best effort:
+    returns the CPU count bound to, or None when NVML / the cpuset does not allow it."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        p = torch.cuda.get_device_properties(local)
+        bus = f"{p.pci_domain_id:08x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------------------------------------ our arm
 def main():
     ap = argparse.ArgumentParser()
@@ -284,6 +306,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: the product path has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         with stdout_to_stderr():
@@ -408,7 +431,7 @@ def main():
             "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f16x2-split operands, f32 accumulate (f16 operands in conv1d like the reference)", "data": "synthetic",
             "config": {"workload": wl["desc"], "codes_per_gpu_per_step": total_codes, "audio_s_per_gpu_per_step": audio_s,
-                       "weights": "random-init miocodec.gguf layout, seed 0", "parallelism": f"utterance-sharded x{world}",
+                       "weights": "random-init miocodec.gguf layout, seed 0", "parallelism": f"utterance-sharded x{world}", "cpus_bound_per_rank": numa,
                        "l2": "per-step working set (GBs of activations) far exceeds the 126 MB L2; no explicit flush"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms_max / args.steps},
