@@ -234,3 +234,34 @@ def test_streaming_matches_reference_policy(codec):
         assert out.shape == ref_out.shape == (N[i] * 1764,)            # sample_diff == 0 (stream-compare.cpp:258-262)
         assert snr_db(out, ref_out) > 58.0, snr_db(out, ref_out)
         s.close()
+
+
+def test_c3_and_c5_full_batches_sampled_against_live_reference(assets, codec):
+    """BASELINE configs C3 (256 x 250 codes, 16 voices) and a C5-shaped ragged batch (50-750 codes): the full batch runs
+    on the GPU, a sample of its utterances is decoded by the compiled reference on the host.  Size-independent properties
+    at full size: exact sample counts and offsets, finiteness, and independence of an utterance from its batch."""
+    import bench
+    from oracle import ref
+    for name, picks in (("c3", [0, 100, 255]), ("c5", None)):
+        wl = bench.make_workload(name, 0, 1)
+        cu, codes, vt, vids = wl["cu"], wl["codes"], wl["voice_table"], wl["voice_ids"]
+        if name == "c5":                                         # the first 256 utterances of the sweep keep the test short
+            n = 256
+            cu, vids = cu[: n + 1], vids[:n]
+            codes = codes[: int(cu[-1])]
+            lens = np.diff(cu)
+            picks = [int(np.argmin(lens)), int(np.argmax(lens)), 7]
+        wave = codec.decode_wave_batch(codes, cu, vt, vids)
+        assert wave.shape == (int(cu[-1]) * 1764,) and np.isfinite(wave).all()
+        R = ref.Reference(assets[0]) if ref.available() else None
+        for b in picks:
+            got = wave[1764 * int(cu[b]): 1764 * int(cu[b + 1])]
+            alone = codec.decode_wave(codes[cu[b]:cu[b + 1]], vt[vids[b]])
+            assert got.shape == alone.shape and snr_db(got, alone) > 55.0, (name, b)
+            if R is not None:
+                w_ref = R.decode_wave(codes[cu[b]:cu[b + 1]], vt[vids[b]])
+                s = snr_db(got, w_ref)
+                print(f"{name} utterance {b} ({int(cu[b + 1] - cu[b])} codes): SNR {s:.1f} dB, max-abs {np.abs(got - w_ref).max():.2e}")
+                assert w_ref.shape == got.shape and s > WAVE_SNR_MIN, (name, b, s)
+        if R is not None:
+            R.close()
