@@ -55,10 +55,12 @@ int  mio_ctx_device(const mio_ctx * ctx);
 /* options: "gemm" = "tc" (tcgen05, default) | "simt" (fp32 CUDA-core validation path, still on the GPU);
  *          "max_chunk_codes" = integer, workspace rows at code resolution (default 65536, ~8.5 GB of HBM); must be
  *          set before the first decode;
- *          "fetch_tail_percent" = integer 0..50 (default 12): mio_decode_wave_batch / mio_decode_pcm16_batch copy chunk
+ *          "fetch_tail_percent" = integer -1..50 (default -1 = auto): mio_decode_wave_batch / mio_decode_pcm16_batch copy chunk
  *          i to the host on a second stream while chunk i+1 computes; the batch is cut where the workspace forces it
  *          and the final chunk once more into (100-p) % and p %, so that the small tail computes while the big piece is
- *          copied and only the tail's own copy is exposed (p ~ D2H time / (compute + D2H time)); 0 = no split;
+ *          copied and only the tail's own copy is exposed (p ~ D2H time / (compute + D2H time)); 0 = no split; -1 = start
+ *          at 12 % and re-estimate p after every call from the measured compute and copy times of the big piece (the
+ *          copy is slower when several GPUs of one host deliver at once);
  *          "fetch_chunk_codes" = integer: optional extra cap on the chunk size of that pipeline (default: none). */
 int  mio_ctx_set_option(mio_ctx * ctx, const char * key, const char * value);
 /* run all kernels of this context on an existing CUDA stream (cudaStream_t as void*), e.g. torch's */

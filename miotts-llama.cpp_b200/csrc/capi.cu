@@ -114,7 +114,7 @@ int mio_ctx_set_option(mio_ctx * c, const char * key, const char * value) {
     }
     if (!strcmp(key, "fetch_tail_percent")) {
         const long v = strtol(value, nullptr, 10);
-        if (v < 0 || v > 50) return fail(MIO_ERR_ARG, "bad argument: fetch_tail_percent out of range");
+        if (v < -1 || v > 50) return fail(MIO_ERR_ARG, "bad argument: fetch_tail_percent out of range");
         c->E.fetch_tail_percent = (int) v;
         return MIO_OK;
     }

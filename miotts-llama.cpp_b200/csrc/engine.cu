@@ -122,6 +122,7 @@ engine::~engine() {
     if (h_stage) cudaFreeHost(h_stage);
     if (stream && own_stream) cudaStreamDestroy(stream);
     if (chunk_done) cudaEventDestroy(chunk_done);
+    for (cudaEvent_t ev : tune_ev) if (ev) cudaEventDestroy(ev);
     if (copy_stream) cudaStreamDestroy(copy_stream);
 }
 
@@ -607,6 +608,7 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
     int64_t rows_left = 0;
     for (int i = 0; i < n_utts; i++) rows_left += (int64_t) std::max(0, cu[i + 1] - cu[i]) + 1;
     bool tail_split_done = false;
+    big_piece_chunk = -1;
     int u = 0;
     while (u < n_utts) {
         chunk_info c;
@@ -614,9 +616,11 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
         int rows = 0, blocks = 0;
         chunk_cu_all.push_back(0);
         int row_cap_c = row_cap;
-        if (chunk_rows_limit > 0 && fetch_tail_percent > 0 && !tail_split_done && rows_left <= row_cap && rows_left >= 4096) {
-            row_cap_c = (int) (rows_left - rows_left * fetch_tail_percent / 100);
+        const int tail_pct = fetch_tail_percent >= 0 ? fetch_tail_percent : (int) (tail_auto_pct + 0.5f);
+        if (chunk_rows_limit > 0 && tail_pct > 0 && !tail_split_done && rows_left <= row_cap && rows_left >= 4096) {
+            row_cap_c = (int) (rows_left - rows_left * tail_pct / 100);
             tail_split_done = true;
+            big_piece_chunk = (int) chunks.size();
         }
         while (u < n_utts) {
             const int T = cu[u + 1] - cu[u];
@@ -1024,8 +1028,14 @@ std::string engine::run(bool peak_normalize, float * host_dst, int16_t * host_pc
     if ((host_dst || host_pcm) && !copy_stream) {
         CK(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&chunk_done, cudaEventDisableTiming));
+        for (cudaEvent_t & ev : tune_ev) CK(cudaEventCreate(&ev));
     }
-    for (const chunk_info & c : chunks) {
+    // auto-tuned tail split: time the compute and the copy of the piece in front of the tail
+    const bool tune = (host_dst || host_pcm) && fetch_tail_percent < 0 && big_piece_chunk >= 0 && big_piece_chunk + 1 < (int) chunks.size();
+    for (size_t ci = 0; ci < chunks.size(); ci++) {
+        const chunk_info & c = chunks[ci];
+        const bool timed = tune && (int) ci == big_piece_chunk;
+        if (timed) CK(cudaEventRecord(tune_ev[0], stream));
         std::string e = run_chunk(c);
         if (!e.empty()) return e;
         if (peak_normalize) {
@@ -1039,16 +1049,30 @@ std::string engine::run(bool peak_normalize, float * host_dst, int16_t * host_pc
             for (int u = 0; u < c.n_utts; u++) codes += lay.len[c.utt0 + u];
             const int64_t off = lay.out_off[c.utt0], n = codes * hp.samples_per_token;
             if (host_pcm) CKR(CAT_PEAK, (double) n * 6.0, launch_pcm16(d_wave, d_pcm, off, off + n, stream));
+            if (timed) CK(cudaEventRecord(tune_ev[1], stream));
             CK(cudaEventRecord(chunk_done, stream));
             CK(cudaStreamWaitEvent(copy_stream, chunk_done, 0));
+            if (timed) CK(cudaEventRecord(tune_ev[2], copy_stream));
             if (n > 0 && host_dst) CK(cudaMemcpyAsync(host_dst + off, d_wave + off, (size_t) n * sizeof(float), cudaMemcpyDeviceToHost, copy_stream));
             if (n > 0 && host_pcm) CK(cudaMemcpyAsync(host_pcm + off, d_pcm + off, (size_t) n * sizeof(int16_t), cudaMemcpyDeviceToHost, copy_stream));
+            if (timed) CK(cudaEventRecord(tune_ev[3], copy_stream));
         }
     }
     batch_ran = true;
     if (host_dst || host_pcm) {
         CK(cudaStreamSynchronize(copy_stream));
-        return sync();
+        std::string e = sync();
+        if (e.empty() && tune) {
+            // the tail (fraction f of the rows) should compute exactly while the big piece is copied:
+            // f * t_compute = (1 - f) * t_copy per row  ->  f = t_copy / (t_compute + t_copy)
+            float t_c = 0.f, t_d = 0.f;
+            if (cudaEventElapsedTime(&t_c, tune_ev[0], tune_ev[1]) == cudaSuccess &&
+                cudaEventElapsedTime(&t_d, tune_ev[2], tune_ev[3]) == cudaSuccess && t_c > 0.f && t_d > 0.f) {
+                const float f = 100.f * t_d / (t_c + t_d);
+                tail_auto_pct = 0.5f * tail_auto_pct + 0.5f * std::min(40.f, std::max(5.f, f));
+            }
+        }
+        return e;
     }
     return {};
 }

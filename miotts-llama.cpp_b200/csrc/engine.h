@@ -113,7 +113,12 @@ struct engine {
     int16_t * d_pcm = nullptr; int64_t pcm_cap = 0;       // PCM16 image of d_wave (grown on demand)
     std::string ensure_pcm();
     cudaStream_t copy_stream = nullptr; cudaEvent_t chunk_done = nullptr;
-    int fetch_tail_percent = 12;     // size of the last chunk of the host-delivery pipeline, % of the final workspace chunk
+    int fetch_tail_percent = -1;     // size of the last chunk of the host-delivery pipeline, % of the final workspace chunk;
+                                     // < 0: auto = tail_auto_pct, re-estimated after every delivery from the measured
+                                     // compute and copy times of the big piece (copy / (compute + copy))
+    float tail_auto_pct = 12.f;
+    int big_piece_chunk = -1;        // index of the chunk in front of the split tail (-1: no split in this batch)
+    cudaEvent_t tune_ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int fetch_chunk_codes = 1 << 20; // optional extra cap on the chunk size of the host-delivery pipeline
     std::string run_istft_only(const float * spec_host, int n_frames);   // mio_istft
     std::string sync();                                   // stream sync + error flag
