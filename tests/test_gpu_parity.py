@@ -265,3 +265,28 @@ def test_c3_and_c5_full_batches_sampled_against_live_reference(assets, codec):
                 assert w_ref.shape == got.shape and s > WAVE_SNR_MIN, (name, b, s)
         if R is not None:
             R.close()
+
+
+def test_delivery_pipeline_splits_do_not_change_the_result(codec):
+    """mio_decode_wave_batch cuts the batch for the overlapped D2H (one tail split whose fraction is fixed or
+    auto-tuned): every variant must deliver the same waveform in the same layout."""
+    from miocodec_b200 import synth
+    lens = [250] * 80                                              # 20 080 rows: large enough for the tail split
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    codes = synth.synth_codes(int(cu[-1]), 77)
+    vt = np.stack([_voice(v) for v in range(4)])
+    vids = (np.arange(len(lens)) % 4).astype(np.int32)
+    outs = {}
+    try:
+        for pct in (0, 12, 30, -1):
+            codec.set_option("fetch_tail_percent", str(pct))
+            outs[pct] = codec.decode_wave_batch(codes, cu, vt, vids)
+            assert outs[pct].shape == (int(cu[-1]) * 1764,) and np.isfinite(outs[pct]).all()
+    finally:
+        codec.set_option("fetch_tail_percent", "-1")
+    for pct in (12, 30, -1):
+        # not bit-identical: the chunk size regroups the fp32 partial sums of the GroupNorm statistics
+        for b in (0, 40, 79):
+            a0 = outs[0][1764 * cu[b]: 1764 * cu[b + 1]]
+            a1 = outs[pct][1764 * cu[b]: 1764 * cu[b + 1]]
+            assert snr_db(a1, a0) > 55.0, (pct, b, snr_db(a1, a0))
