@@ -229,8 +229,11 @@ def run_streaming(args):
                     s.finish()
             codec.step_streams(streams)
             for s in streams:
-                a, _ = s.read()
-                emitted += a.size
+                while True:                       # 256k-sample reads: a 16 MB buffer per read costs more than the copy
+                    a, _ = s.read(1 << 18)
+                    emitted += a.size
+                    if a.size < (1 << 18):
+                        break
         dt = time.perf_counter() - t0
         st = streams[0].stats()
         for s in streams:
