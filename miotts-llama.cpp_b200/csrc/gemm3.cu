@@ -66,9 +66,11 @@ __device__ __forceinline__ void stage_f16_row(uint8_t * stage, int lane, int fir
 
 // One row (this thread's), 32 accumulator columns starting at col0: fused math + write into the staging tile.
 // `part` is the half of an fp16 output row this chunk fills (EPI_SWIGLU only: 32 accumulators -> 16 outputs).
+// `aux` is the per-row value the tile loop resolved once, while waiting for the accumulator: the RoPE position of the
+// row (EPI_QKV) or the voice whose gate vector applies (gated EPI_RESID); -1 on pad rows / rows past M.
 template <int EPI>
 __device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int col0, float (&v)[32], uint8_t * stage,
-                                           int lane, int part) {
+                                           int lane, int part, int aux) {
     // Per-column parameter vectors (bias, snake) are readable up to the end of the 32-column chunk (the engine pads
     // them), so there are no per-element bounds checks: columns >= N are computed and then clipped by the TMA store.
     const int cb = col0 % p.bias_mod;
@@ -88,12 +90,11 @@ __device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int c
     } else if constexpr (EPI == EPI_RESID) {
         // x += gate[utt] * y: the add itself is done by the TMA reduce; pad rows of gated layers contribute 0
         if (p.gate != nullptr) {
-            const int u = (row < p.M) ? p.row_utt[row / p.row_div] : -1;
-            if (u < 0) {
+            if (aux < 0) {
 #pragma unroll
                 for (int i = 0; i < 32; i++) v[i] = 0.f;
             } else {
-                const float * g = p.gate + (size_t) p.gate_voice[u] * p.gate_ld + col0;
+                const float * g = p.gate + (size_t) aux * p.gate_ld + col0;
 #pragma unroll
                 for (int i = 0; i < 32; i += 4) {
                     const float4 gg = __ldg((const float4 *) (g + i));
@@ -108,8 +109,10 @@ __device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int c
 #pragma unroll
         for (int i = 0; i < 8; i++) {
             const float g0 = v[4 * i], u0 = v[4 * i + 1], g1 = v[4 * i + 2], u1 = v[4 * i + 3];
-            const float h0 = (g0 / (1.0f + expf(-g0))) * u0;
-            const float h1 = (g1 / (1.0f + expf(-g1))) * u1;
+            // libdevice expf; the quotient by 1 + e >= 1 through the SFU reciprocal (<= 2 ulp, below the 2^-22 of the
+            // hi/lo split that follows) instead of the IEEE divide sequence: the epilogue has to hide behind the MMAs
+            const float h0 = __fdividef(g0, 1.0f + expf(-g0)) * u0;
+            const float h1 = __fdividef(g1, 1.0f + expf(-g1)) * u1;
             hi[i] = pack_split_hi_lo(h0, h1, lo[i]);
         }
         stage_f16_row<8>(stage, lane, 2 * part, hi, lo);
@@ -149,9 +152,8 @@ __device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int c
         // RoPE mode 0 (adjacent pairs) on the q and k columns with the utterance-relative position
         // (mha_rope, src/miocodec.cpp:260-263; ggml rope cache ops.cpp:5612-5626); q pre-scaled by 1/sqrt(head_dim)
         if (col0 < p.rope_cols) {
-            const int u = (row < p.M) ? p.row_utt[row / p.row_div] : -1;
-            if (u >= 0) {
-                const int pos = min(row - p.utt_start[u] * p.row_div, p.rope_max_pos - 1);
+            if (aux >= 0) {
+                const int pos = aux;
                 const float4 * cs = (const float4 *) (p.rope + ((size_t) pos * 32 + ((col0 & 63) >> 1)) * 2);
                 const float qs = (col0 < p.q_cols) ? p.q_scale : 1.0f;
 #pragma unroll
@@ -303,6 +305,17 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             int nch = (p.N - colw + 31) / 32;                            // valid chunks (warp-uniform)
             nch = nch < 0 ? 0 : (nch > CH ? CH : nch);
             if (row0 >= p.M) nch = 0;
+            // per-row metadata of this tile, resolved while the MMAs of the tile are still running
+            int aux = -1;
+            if constexpr (EPI == EPI_QKV) {
+                const int u = (row < p.M) ? p.row_utt[row / p.row_div] : -1;
+                if (u >= 0) aux = min(row - p.utt_start[u] * p.row_div, p.rope_max_pos - 1);
+            } else if constexpr (EPI == EPI_RESID) {
+                if (p.gate != nullptr) {
+                    const int u = (row < p.M) ? p.row_utt[row / p.row_div] : -1;
+                    if (u >= 0) aux = p.gate_voice[u];
+                }
+            }
             mbar_wait(&tmem_full[b], aph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t t_addr = tmem_base + ((uint32_t) (lg * 32) << 16) + (uint32_t) (b * BN + half * (BN / 2));
@@ -320,7 +333,7 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                     if (lane == 0) tma_store_wait_read0();
                     __syncwarp();
                 }
-                epi3_chunk<EPI>(p, row, colw + c * 32, v, stage, lane, part);
+                epi3_chunk<EPI>(p, row, colw + c * 32, v, stage, lane, part, aux);
                 const bool flush = (eo::ACC_PER_OUT == 1) || part == 1 || c == nch - 1;
                 if (flush) {
                     fence_async_smem();
