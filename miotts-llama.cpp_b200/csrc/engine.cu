@@ -481,6 +481,16 @@ std::string engine::load(const std::string & path, int dev) {
             }
         }
         w.rope_pre = L.vec_host(r);
+        // the same values position-minor for the generation-3 epilogue, where lane = row = consecutive positions:
+        // rope_t[half h][i][pos] = the four floats (cos, sin, cos, sin) of pairs h*16 + 2i, 2i+1 -> a warp's float4 load
+        // covers 512 contiguous bytes instead of 32 separate lines
+        std::vector<float> rt(r.size());
+        for (int h = 0; h < 2; h++)
+            for (int i = 0; i < 8; i++)
+                for (int pos = 0; pos < w.rope_max_pos; pos++)
+                    for (int j = 0; j < 4; j++)
+                        rt[((size_t) (h * 8 + i) * w.rope_max_pos + pos) * 4 + j] = r[((size_t) pos * 32 + h * 16 + 2 * i) * 2 + j];
+        w.rope_t = L.vec_host(rt);
     }
     {   // periodic Hann window (istft_cache, src/istft.cpp:29-31)
         std::vector<float> hn(hp.n_fft);
@@ -849,7 +859,7 @@ gemm_params engine::qkv_params(const row_map & rm, int D, int row_div) {
     gemm_params p;
     p.epi = EPI_QKV; p.out_hi = qkv_hi; p.out_lo = qkv_lo; p.ld_h = 3 * D;
     p.row_utt = rm.row_utt; p.row_div = row_div; p.utt_start = rm.start;
-    p.rope = w.rope_pre; p.rope_max_pos = w.rope_max_pos; p.rope_cols = 2 * D; p.q_cols = D; p.q_scale = 0.125f;   // 1/sqrt(64)
+    p.rope = w.rope_pre; p.rope_t = w.rope_t; p.rope_max_pos = w.rope_max_pos; p.rope_cols = 2 * D; p.q_cols = D; p.q_scale = 0.125f;   // 1/sqrt(64)
     return p;
 }
 

@@ -154,11 +154,12 @@ __device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int c
         if (col0 < p.rope_cols) {
             if (aux >= 0) {
                 const int pos = aux;
-                const float4 * cs = (const float4 *) (p.rope + ((size_t) pos * 32 + ((col0 & 63) >> 1)) * 2);
+                // position-minor table: lanes (consecutive rows = consecutive positions) read contiguous float4s
+                const float4 * cs = (const float4 *) p.rope_t + (size_t) ((col0 & 63) >> 5) * 8 * p.rope_max_pos + pos;
                 const float qs = (col0 < p.q_cols) ? p.q_scale : 1.0f;
 #pragma unroll
                 for (int i = 0; i < 8; i++) {
-                    const float4 t = __ldg(cs + i);       // (cos, sin) of two consecutive pairs
+                    const float4 t = __ldg(cs + (size_t) i * p.rope_max_pos);   // (cos, sin) of two consecutive pairs
                     const float x0 = v[4 * i], x1 = v[4 * i + 1], x2 = v[4 * i + 2], x3 = v[4 * i + 3];
                     v[4 * i] = (x0 * t.x - x1 * t.y) * qs;
                     v[4 * i + 1] = (x0 * t.y + x1 * t.x) * qs;

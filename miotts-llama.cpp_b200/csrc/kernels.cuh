@@ -35,6 +35,7 @@ struct gemm_params {
     // EPI_QKV: rope[pos][32][2] (cos, sin), pos = row - utt_start[utt] * row_div; columns < rope_cols are rotated,
     // columns < q_cols additionally multiplied by q_scale
     const float * rope = nullptr; int rope_max_pos = 0; const int32_t * utt_start = nullptr;
+    const float * rope_t = nullptr;        // same values as [2][8][rope_max_pos][4] (position-minor), generation 3
     int rope_cols = 0, q_cols = 0; float q_scale = 1.f;
     // raw operand pointers (SIMT validation path; the tcgen05 path reads through the tensor maps)
     const __half * a_hi = nullptr; const __half * a_lo = nullptr; int lda = 0; int a_rows = 0;

@@ -72,6 +72,7 @@ struct weights {
     gemm_weight out_proj; float *out_proj_b, *out_snake_ea, *out_snake_eb;
     gemm_weight head; float * head_b;             // columns interleaved (logmag_f, phase_f)
     float * rope_pre = nullptr;                   // [max_pos][32][2] cos,sin
+    float * rope_t = nullptr;         // the same table position-minor: [2][8][rope_max_pos][4] (generation-3 QKV epilogue)
     int rope_max_pos = 0;
     float * hann = nullptr;                       // [n_fft]
 };
