@@ -81,13 +81,13 @@ cudaError_t launch_attn_bounds(const row_map & rm, int rows, int row_div, int wi
 __global__ void __launch_bounds__(128, 4) attention_tc_kernel(
         const __grid_constant__ CUtensorMap tm_in_hi, const __grid_constant__ CUtensorMap tm_in_lo,
         const __grid_constant__ CUtensorMap tm_out_hi, const __grid_constant__ CUtensorMap tm_out_lo,
-        int rows, int D, const int2 * __restrict__ bounds) {
+        int rows, int D, const int2 * __restrict__ bounds, int rev) {
     extern __shared__ uint8_t at_smem_raw[];
     const uint32_t raw = smem_u32(at_smem_raw);
     uint8_t * smem = at_smem_raw + ((1024u - (raw & 1023u)) & 1023u);
     // tiles: 0 Qh, 1 Ql, 2-3 Kh then Vh, 4-5 Kl then Vl
     uint64_t * bar = (uint64_t *) (smem + 6 * AT_TILE);     // [0]: q + k landed, [1]: v landed
-    const int q0 = blockIdx.x * AT_QB;
+    const int q0 = (rev ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * AT_QB;
     const int h = blockIdx.y;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int k_lo = q0 - 32;
@@ -250,11 +250,11 @@ cudaError_t attention_tc_init() {
 // tm_out_*: maps over the fp16 [rows][D] outputs, box {64, 16}, SWIZZLE_128B; bounds: launch_attn_bounds(window).
 cudaError_t launch_attention_tc(const CUtensorMap & tm_in_hi, const CUtensorMap & tm_in_lo, const CUtensorMap & tm_out_hi,
                                 const CUtensorMap & tm_out_lo, int rows, int D, int n_head, int window, const int2 * bounds,
-                                cudaStream_t st) {
+                                cudaStream_t st, bool rev) {
     if (rows <= 0) return cudaSuccess;
     if (D != n_head * 64 || window / 2 != 32) return cudaErrorInvalidValue;
     dim3 grid((rows + AT_QB - 1) / AT_QB, n_head);
-    attention_tc_kernel<<<grid, 128, AT_SMEM, st>>>(tm_in_hi, tm_in_lo, tm_out_hi, tm_out_lo, rows, D, bounds);
+    attention_tc_kernel<<<grid, 128, AT_SMEM, st>>>(tm_in_hi, tm_in_lo, tm_out_hi, tm_out_lo, rows, D, bounds, rev ? 1 : 0);
     return cudaGetLastError();
 }
 

@@ -64,10 +64,10 @@ __global__ void __launch_bounds__(256) layernorm_kernel(
         const float * __restrict__ x, int rows, float eps, const float * __restrict__ w, const float * __restrict__ b,
         const float * __restrict__ mod, int mod_ld, int shift_off, int scale_off,
         const int32_t * __restrict__ row_utt, const int32_t * __restrict__ voice, int row_div,
-        __half * __restrict__ out_hi, __half * __restrict__ out_lo, float * __restrict__ out_f32) {
+        __half * __restrict__ out_hi, __half * __restrict__ out_lo, float * __restrict__ out_f32, int rev) {
     constexpr int D = NV * 128;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int row = blockIdx.x * 8 + warp;
+    const int row = (rev ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * 8 + warp;
     if (row >= rows) return;
     const int utt = row_utt[row / row_div];
     const size_t base = (size_t) row * D;
@@ -131,15 +131,15 @@ __global__ void __launch_bounds__(256) layernorm_kernel(
 
 cudaError_t launch_layernorm(const float * x, int rows, int D, float eps, const float * w, const float * b,
                              const float * mod, int mod_ld, int shift_off, int scale_off, const row_map & rm, int row_div,
-                             __half * out_hi, __half * out_lo, float * out_f32, cudaStream_t st) {
+                             __half * out_hi, __half * out_lo, float * out_f32, cudaStream_t st, bool rev) {
     if (rows <= 0) return cudaSuccess;
     const int grid = (rows + 7) / 8;
     if (D == 768) {
         layernorm_kernel<6><<<grid, 256, 0, st>>>(x, rows, eps, w, b, mod, mod_ld, shift_off, scale_off, rm.row_utt,
-                                                  rm.voice, row_div, out_hi, out_lo, out_f32);
+                                                  rm.voice, row_div, out_hi, out_lo, out_f32, rev ? 1 : 0);
     } else if (D == 512) {
         layernorm_kernel<4><<<grid, 256, 0, st>>>(x, rows, eps, w, b, mod, mod_ld, shift_off, scale_off, rm.row_utt,
-                                                  rm.voice, row_div, out_hi, out_lo, out_f32);
+                                                  rm.voice, row_div, out_hi, out_lo, out_f32, rev ? 1 : 0);
     } else {
         return cudaErrorInvalidValue;
     }
@@ -286,12 +286,12 @@ cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, 
 constexpr int GN_ROWS = 64;
 
 __global__ void gn_stats_kernel(const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt,
-                                int row_div, double * __restrict__ stats, int rows_per_block) {
+                                int row_div, double * __restrict__ stats, int rows_per_block, int rev) {
     const int c4 = threadIdx.x;                    // float4 index within the row
     const int cpg = C / 32;                        // channels per group: 16, 8 or 4
     const int tpg = cpg / 4;                       // threads per group: 4, 2 or 1
     const int group = (c4 * 4) / cpg;
-    const int r0 = blockIdx.x * rows_per_block;
+    const int r0 = (rev ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * rows_per_block;
     const int r1 = min(rows, r0 + rows_per_block);
     float s = 0.f, q = 0.f;
     int cur = -1;
@@ -328,12 +328,12 @@ __global__ void gn_stats_kernel(const float * __restrict__ x, int rows, int C, c
 }
 
 cudaError_t launch_gn_stats(const float * x, int rows, int C, const row_map & rm, int row_div, double * stats,
-                            cudaStream_t st) {
+                            cudaStream_t st, bool rev) {
     if (rows <= 0) return cudaSuccess;
     if (C % 128 != 0) return cudaErrorInvalidValue;
     // few rows (a single short utterance): shorter row runs per block so the serial load rounds do not set the latency
     const int rpb = (rows >= GN_ROWS * 148 * 4) ? GN_ROWS : 16;
-    gn_stats_kernel<<<(rows + rpb - 1) / rpb, C / 4, 0, st>>>(x, rows, C, rm.row_utt, row_div, stats, rpb);
+    gn_stats_kernel<<<(rows + rpb - 1) / rpb, C / 4, 0, st>>>(x, rows, C, rm.row_utt, row_div, stats, rpb, rev ? 1 : 0);
     return cudaGetLastError();
 }
 
@@ -369,7 +369,7 @@ __device__ __forceinline__ float silu_sel(float x, bool precise) { return precis
 __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
         const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt, int row_div,
         const float2 * __restrict__ mr, const float * __restrict__ w, const float * __restrict__ b, __half * __restrict__ out,
-        int rows_per_block) {
+        int rows_per_block, int rev) {
     const bool pr = g_gn_precise;
     const int C8 = C >> 3;                       // threads per row: 64, 32 or 16
     const int rpp = 256 / C8;                    // rows per pass of the block
@@ -379,7 +379,7 @@ __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
     const int g0 = c / cpg, g1 = (c + 4) / cpg;
     const float4 w0 = __ldg((const float4 *) (w + c)), w1 = __ldg((const float4 *) (w + c + 4));
     const float4 b0 = __ldg((const float4 *) (b + c)), b1 = __ldg((const float4 *) (b + c + 4));
-    const int r_begin = blockIdx.x * rows_per_block, r_end = min(rows, r_begin + rows_per_block);
+    const int r_begin = (rev ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * rows_per_block, r_end = min(rows, r_begin + rows_per_block);
     for (int rb = r_begin + rl; rb < r_end; rb += 4 * rpp) {
         int u[4];
         float4 v0[4], v1[4];
@@ -415,7 +415,7 @@ __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
 }
 
 cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double * stats,
-                                 float eps, const float * w, const float * b, float2 * mr_scratch, __half * out, cudaStream_t st) {
+                                 float eps, const float * w, const float * b, float2 * mr_scratch, __half * out, cudaStream_t st, bool rev) {
     if (rows <= 0) return cudaSuccess;
     if (C % 128 != 0 || C > 2048) return cudaErrorInvalidValue;
     gn_finalize_kernel<<<(rm.n_utts * 32 + 255) / 256, 256, 0, st>>>(stats, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
@@ -427,7 +427,7 @@ cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map
         cudaMemcpyToSymbol(g_gn_precise, &v, sizeof(bool));
     }
     const int rpb = (rows >= GNA_ROWS * 148 * 2) ? GNA_ROWS : 16;      // few rows: more, shorter blocks (latency mode)
-    gn_apply_silu_kernel<<<(rows + rpb - 1) / rpb, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb);
+    gn_apply_silu_kernel<<<(rows + rpb - 1) / rpb, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb, rev ? 1 : 0);
     return cudaGetLastError();
 }
 

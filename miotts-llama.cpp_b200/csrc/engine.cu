@@ -502,6 +502,7 @@ std::string engine::load(const std::string & path, int dev) {
     own_stream = true;
     CK(attention_init());
     { const char * ev = getenv("MIO_ATTN"); attn_simt = ev && !strcmp(ev, "simt"); }
+    { const char * ev = getenv("MIO_SERPENTINE"); if (ev && ev[0] == '0') serpentine = false; }
     CK(cudaDeviceSynchronize());
     return {};
 }
@@ -752,6 +753,7 @@ void engine::snap_f16(const char * name, const __half * hi, const __half * lo, s
 // ---------------------------------------------------------------------------------------------
 cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_params p) {
     p.M = M; p.N = W.N; p.K = W.K; p.taps = W.taps; p.npass = W.npass; p.out_scale = W.out_scale;
+    p.reverse = next_dir() ? 1 : 0;
     if (p.bias_mod <= 1) p.bias_mod = W.N;
     p.a_hi = A.hi; p.a_lo = A.lo; p.lda = A.K; p.a_rows = A.rows;
     p.b_hi = W.hi; p.b_lo = W.lo;
@@ -842,13 +844,13 @@ std::string engine::run_resblock(const resblock_w & R, float * x, float * y, con
     if (gn_slot > GN_SLOTS) return "internal: GroupNorm slot overflow";
     gemm_params p;
     // GN -> SiLU -> conv1 + bias
-    CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(x, rows, C, rm, row_div, st1, stream));
-    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(x, rows, C, rm, row_div, st1, hp.gn_eps, R.n1w, R.n1b, gn_mr, vc.hi, stream)); launches++;
+    CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(x, rows, C, rm, row_div, st1, stream, next_dir()));
+    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(x, rows, C, rm, row_div, st1, hp.gn_eps, R.n1w, R.n1b, gn_mr, vc.hi, stream, next_dir())); launches++;
     p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = y; p.ld_out = C; p.bias = R.c1b;
     CKG(gemm(R.c1, vc, rows, p));
     // GN -> SiLU -> conv2 + bias + residual
-    CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(y, rows, C, rm, row_div, st2, stream));
-    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(y, rows, C, rm, row_div, st2, hp.gn_eps, R.n2w, R.n2b, gn_mr, vc.hi, stream)); launches++;
+    CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(y, rows, C, rm, row_div, st2, stream, next_dir()));
+    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(y, rows, C, rm, row_div, st2, hp.gn_eps, R.n2w, R.n2b, gn_mr, vc.hi, stream, next_dir())); launches++;
     p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x; p.ld_out = C; p.bias = R.c2b;
     CKG(gemm(R.c2, vc, rows, p));
     return {};
@@ -875,7 +877,7 @@ std::string engine::run_attention(int rows, int D, int n_head, int window, int r
     const CUtensorMap * oh = out_map(out.hi, 2, rows, D, (size_t) D * 2, 64, 16);
     const CUtensorMap * ol = out_map(out.lo, 2, rows, D, (size_t) D * 2, 64, 16);
     if (!ih || !il || !oh || !ol) return err;
-    CKR(CAT_ATTN, (double) rows * 16.0 * D, launch_attention_tc(*ih, *il, *oh, *ol, rows, D, n_head, window, bounds, stream));
+    CKR(CAT_ATTN, (double) rows * 16.0 * D, launch_attention_tc(*ih, *il, *oh, *ol, rows, D, n_head, window, bounds, stream, next_dir()));
     return {};
 }
 
@@ -900,7 +902,7 @@ std::string engine::run_chunk(const chunk_info & c) {
     // 2. prenet
     for (int i = 0; i < hp.prenet_layers; i++) {
         const prenet_layer_w & l = w.prenet[i];
-        CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.an_w, l.an_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
+        CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.an_w, l.an_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream, next_dir()));
         p = qkv_params(rm, D, 1);
         CKG(gemm(l.qkv, vA768, R1, p));
         if (i == 0) snap_f16("pre0_qkv_rope", qkv_hi, qkv_lo, (size_t) R1 * 3 * D);
@@ -909,7 +911,7 @@ std::string engine::run_chunk(const chunk_info & c) {
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
         CKG(gemm(l.wo, vA768, R1, p));
         if (i == 0) snap_f32("pre0_x_attn", x768, (size_t) R1 * D);
-        CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.fn_w, l.fn_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
+        CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.fn_w, l.fn_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream, next_dir()));
         p = gemm_params(); p.epi = EPI_SWIGLU; p.out_hi = vFF2048.hi; p.out_lo = vFF2048.lo; p.ld_h = hp.prenet_ff;
         CKG(gemm(l.gu, vA768, R1, p));
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
@@ -917,7 +919,7 @@ std::string engine::run_chunk(const chunk_info & c) {
         if (i == 0) snap_f32("pre0_out", x768, (size_t) R1 * D);
     }
     snap_f32("prenet_x", x768, (size_t) R1 * D);
-    CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, w.pre_norm_w, w.pre_norm_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream));
+    CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, w.pre_norm_w, w.pre_norm_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream, next_dir()));
     // 2b. 768 -> 512 (+bias) written straight as the split operand of the ConvTranspose GEMM
     p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = vA512.hi; p.out_lo = vA512.lo; p.ld_h = C; p.bias = w.pre_out_b;
     // the prenet LN output lives in aA viewed as [R1][768]; the 512-wide result must not overwrite it while other
@@ -941,14 +943,14 @@ std::string engine::run_chunk(const chunk_info & c) {
     for (int i = 0; i < hp.dec_layers; i++) {
         const dec_layer_w & l = w.dec[i];
         const int oa = (i * 2 + 0) * 3 * C, of = (i * 2 + 1) * 3 * C;     // shift | scale | gate
-        CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, oa, oa + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream));
+        CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, oa, oa + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream, next_dir()));
         p = qkv_params(rm, C, 2);
         CKG(gemm(l.qkv, vA512, R2, p));
         if (!(e = run_attention(R2, C, hp.dec_heads, hp.dec_window, 2, vA512, attn_b2)).empty()) return e;
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x512; p.ld_out = C;
         p.gate = mod + oa + 2 * C; p.gate_ld = w.cond_rows; p.row_utt = rm.row_utt; p.row_div = 2; p.gate_voice = rm.voice;
         CKG(gemm(l.wo, vA512, R2, p));
-        CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, of, of + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream));
+        CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, of, of + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream, next_dir()));
         p = gemm_params(); p.epi = EPI_SWIGLU; p.out_hi = vFF1536.hi; p.out_lo = vFF1536.lo; p.ld_h = hp.dec_ff;
         CKG(gemm(l.gu, vA512, R2, p));
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x512; p.ld_out = C;
@@ -960,7 +962,7 @@ std::string engine::run_chunk(const chunk_info & c) {
     // 6. final AdaLN (shift, scale only) -> fp32 in place
     {
         const int on = hp.dec_layers * 2 * 3 * C;
-        CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, on, on + C, rm, 2, nullptr, nullptr, x512, stream));
+        CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, on, on + C, rm, 2, nullptr, nullptr, x512, stream, next_dir()));
     }
     snap_f32("final_norm", x512, (size_t) R2 * C);
     // 7. post resnet blocks

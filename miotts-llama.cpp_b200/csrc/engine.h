@@ -49,6 +49,10 @@ struct engine {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     bool use_simt = false;
+    // serpentine row order: consecutive kernels of a chunk walk the rows in opposite directions, so each starts on the
+    // rows its predecessor wrote last (still in the 126 MB L2).  MIO_SERPENTINE=0 disables (A/B measurements).
+    bool serpentine = true, dir_flip = false;
+    bool next_dir() { if (!serpentine) return false; dir_flip = !dir_flip; return dir_flip; }
     int num_sms = 148;               // multiProcessorCount of the device (tile-width choice of the GEMM dispatch)
     int gemm_gen = 3;                // 1: one CTA per tile; 2: persistent CTA pairs (cta_group::2); 3: + TMA-store epilogue (default)
     int max_rows1 = 65536 + 4096;    // workspace rows at code resolution (codes + one pad row per utterance), ~8.5 GB

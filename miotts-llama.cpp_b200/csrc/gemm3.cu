@@ -235,7 +235,8 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         if (lane == 0) {
             int it = 0;
             for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-                const int tm = tile / tiles_n, tn = tile - tm * tiles_n;
+                const int t2 = p.reverse ? num_tiles - 1 - tile : tile;       // serpentine row order between kernels
+                const int tm = t2 / tiles_n, tn = t2 - tm * tiles_n;
                 const int m0 = tm * 256 + (int) rank * 128, n0 = tn * BN + (int) rank * (BN / 2);
                 for (int kb = 0; kb < num_kb; kb++, it++) {
                     const int s = it % cfg::STAGES;
@@ -297,7 +298,8 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         const uint32_t tmem_empty_leader1 = mapa_u32(smem_u32(&tmem_empty[1]), 0);
         int tile_iter = 0;
         for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, tile_iter++) {
-            const int tm = tile / tiles_n, tn = tile - tm * tiles_n;
+            const int t2 = p.reverse ? num_tiles - 1 - tile : tile;
+            const int tm = t2 / tiles_n, tn = t2 - tm * tiles_n;
             const int b = tile_iter & 1;
             const uint32_t aph = (uint32_t) (tile_iter >> 1) & 1u;
             const int row0 = tm * 256 + (int) rank * 128 + lg * 32;      // first row of this warp's 32-row slab

@@ -23,6 +23,8 @@ enum epi_kind : int {
 struct gemm_params {
     int M = 0, N = 0, K = 0, taps = 1;     // D[M][N] = sum_tap A[row + tap - (taps==3)][K] * B[N][tap*K + k]
     int npass = 3;                         // 3: (a_hi + a_lo)(b_hi + b_lo) without lo*lo; 1: a_hi * b_hi
+    int reverse = 0;                       // walk the M tiles from the last row down (generation 3): consecutive kernels
+                                           // alternate, so each starts on the rows its predecessor left in L2
     float out_scale = 1.f;
     int epi = EPI_STORE;
     float * out_f32 = nullptr; int ld_out = 0;
@@ -73,25 +75,26 @@ cudaError_t launch_gather(const float * table, const int32_t * codes_padded, flo
 // Outputs: split fp16 (out_hi/out_lo) and/or fp32 (out_f32). Pad rows produce zeros.
 cudaError_t launch_layernorm(const float * x, int rows, int D, float eps, const float * w, const float * b,
                              const float * mod, int mod_ld, int shift_off, int scale_off, const row_map & rm, int row_div,
-                             __half * out_hi, __half * out_lo, float * out_f32, cudaStream_t st);
+                             __half * out_hi, __half * out_lo, float * out_f32, cudaStream_t st, bool rev = false);
 // banded local attention on the rotated / scaled / split q|k|v written by EPI_QKV.  qkv_*: [rows][3*D] fp16;
 // out: split fp16 [rows][D].  _tc: TMA + ldmatrix + warp MMA (attention.cu, product path); _simt: fp32 validation.
 // bounds[i] = (first valid key, number of valid keys) of query row i, written once per chunk by launch_attn_bounds.
 cudaError_t launch_attn_bounds(const row_map & rm, int rows, int row_div, int window, int2 * bounds, cudaStream_t st);
 cudaError_t launch_attention_tc(const CUtensorMap & tm_in_hi, const CUtensorMap & tm_in_lo, const CUtensorMap & tm_out_hi,
                                 const CUtensorMap & tm_out_lo, int rows, int D, int n_head, int window, const int2 * bounds,
-                                cudaStream_t st);
+                                cudaStream_t st, bool rev = false);
 cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, int rows, int D, int n_head, int window,
                                   const row_map & rm, int row_div, __half * out_hi, __half * out_lo, cudaStream_t st);
 cudaError_t attention_init();
 cudaError_t attention_tc_init();
 // GroupNorm statistics: stats[utt][32][2] (sum, sum of squares; double), rows at resolution row_div
 cudaError_t launch_gn_stats(const float * x, int rows, int C, const row_map & rm, int row_div, double * stats,
-                            cudaStream_t st);
+                            cudaStream_t st, bool rev = false);
 // y = fp16( silu( (x-mean)*rstd*w + b ) ), zeros on pad rows
 // (two launches: per-(utterance, group) mean / rstd into mr_scratch[n_utts*32], then the per-element pass)
 cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double * stats,
-                                 float eps, const float * w, const float * b, float2 * mr_scratch, __half * out, cudaStream_t st);
+                                 float eps, const float * w, const float * b, float2 * mr_scratch, __half * out, cudaStream_t st,
+                                 bool rev = false);
 cudaError_t launch_split(const float * x, int rows, int C, const row_map & rm, int row_div, __half * hi, __half * lo,
                          cudaStream_t st);
 // mod[voice][cond_rows] = W[cond_rows][128] * silu(emb[voice]) + b
