@@ -363,14 +363,14 @@ __global__ void gn_finalize_kernel(const double * __restrict__ stats, const int3
 constexpr int GNA_ROWS = 64;                     // rows per block
 
 __device__ __forceinline__ float silu_fast(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
-__device__ bool g_gn_precise = false;            // MIO_GN_PRECISE=1: libdevice expf + IEEE divide (accuracy experiments)
-__device__ __forceinline__ float silu_sel(float x, bool precise) { return precise ? silu_f(x) : silu_fast(x); }
+// PRECISE (MIO_GN_PRECISE=1, accuracy experiments): libdevice expf + IEEE divide
+template <bool PRECISE> __device__ __forceinline__ float silu_pick(float x) { return PRECISE ? silu_f(x) : silu_fast(x); }
 
+template <bool PRECISE>
 __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
         const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt, int row_div,
         const float2 * __restrict__ mr, const float * __restrict__ w, const float * __restrict__ b, __half * __restrict__ out,
         int rows_per_block, int rev) {
-    const bool pr = g_gn_precise;
     const int C8 = C >> 3;                       // threads per row: 64, 32 or 16
     const int rpp = 256 / C8;                    // rows per pass of the block
     const int c = (threadIdx.x % C8) * 8;
@@ -403,10 +403,10 @@ __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
             uint4 o = make_uint4(0u, 0u, 0u, 0u);
             if (u[k] >= 0) {
                 const float2 m0 = __ldg(mr + (size_t) u[k] * 32 + g0), m1 = __ldg(mr + (size_t) u[k] * 32 + g1);
-                const __half2 h0 = __floats2half2_rn(silu_sel((v0[k].x - m0.x) * m0.y * w0.x + b0.x, pr), silu_sel((v0[k].y - m0.x) * m0.y * w0.y + b0.y, pr));
-                const __half2 h1 = __floats2half2_rn(silu_sel((v0[k].z - m0.x) * m0.y * w0.z + b0.z, pr), silu_sel((v0[k].w - m0.x) * m0.y * w0.w + b0.w, pr));
-                const __half2 h2 = __floats2half2_rn(silu_sel((v1[k].x - m1.x) * m1.y * w1.x + b1.x, pr), silu_sel((v1[k].y - m1.x) * m1.y * w1.y + b1.y, pr));
-                const __half2 h3 = __floats2half2_rn(silu_sel((v1[k].z - m1.x) * m1.y * w1.z + b1.z, pr), silu_sel((v1[k].w - m1.x) * m1.y * w1.w + b1.w, pr));
+                const __half2 h0 = __floats2half2_rn(silu_pick<PRECISE>((v0[k].x - m0.x) * m0.y * w0.x + b0.x), silu_pick<PRECISE>((v0[k].y - m0.x) * m0.y * w0.y + b0.y));
+                const __half2 h1 = __floats2half2_rn(silu_pick<PRECISE>((v0[k].z - m0.x) * m0.y * w0.z + b0.z), silu_pick<PRECISE>((v0[k].w - m0.x) * m0.y * w0.w + b0.w));
+                const __half2 h2 = __floats2half2_rn(silu_pick<PRECISE>((v1[k].x - m1.x) * m1.y * w1.x + b1.x), silu_pick<PRECISE>((v1[k].y - m1.x) * m1.y * w1.y + b1.y));
+                const __half2 h3 = __floats2half2_rn(silu_pick<PRECISE>((v1[k].z - m1.x) * m1.y * w1.z + b1.z), silu_pick<PRECISE>((v1[k].w - m1.x) * m1.y * w1.w + b1.w));
                 o = make_uint4(*(const uint32_t *) &h0, *(const uint32_t *) &h1, *(const uint32_t *) &h2, *(const uint32_t *) &h3);
             }
             *(uint4 *) (out + (size_t) r * C + c) = o;
@@ -422,12 +422,11 @@ cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map
     static int precise_set = -1;
     if (precise_set < 0) {
         const char * ev = getenv("MIO_GN_PRECISE");
-        const bool v = ev && ev[0] == '1';
-        precise_set = v ? 1 : 0;
-        cudaMemcpyToSymbol(g_gn_precise, &v, sizeof(bool));
+        precise_set = (ev && ev[0] == '1') ? 1 : 0;
     }
     const int rpb = (rows >= GNA_ROWS * 148 * 2) ? GNA_ROWS : 16;      // few rows: more, shorter blocks (latency mode)
-    gn_apply_silu_kernel<<<(rows + rpb - 1) / rpb, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb, rev ? 1 : 0);
+    if (precise_set) gn_apply_silu_kernel<true><<<(rows + rpb - 1) / rpb, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb, rev ? 1 : 0);
+    else gn_apply_silu_kernel<false><<<(rows + rpb - 1) / rpb, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb, rev ? 1 : 0);
     return cudaGetLastError();
 }
 
