@@ -159,6 +159,10 @@ int  mio_streams_step(mio_ctx * ctx, mio_stream ** streams, int n_streams);
 int64_t mio_stream_read(mio_stream * s, float * out, int64_t cap, int * is_last);
 /* counters mirroring StreamProfile (src/test-to-speech.h:28-38): decode_calls, decoded_codes, emitted_samples */
 int  mio_stream_stats(const mio_stream * s, int64_t * decode_calls, int64_t * decoded_codes, int64_t * emitted_samples);
+/* the timers of StreamProfile (codec_sec + istft_sec, src/test-to-speech.h:31-32, accumulated at :548-552): wall seconds
+ * this context has spent inside mio_streams_step (decoder + ISTFT + cut/crossfade + D2H are one fused device pass here, and
+ * one pass serves every stream that fired, so the time belongs to the context, not to a stream) and the number of passes */
+double mio_ctx_stream_seconds(const mio_ctx * ctx, int64_t * out_passes);
 
 /* ---- pinned host buffers (cudaMallocHost) so callers can hand the library transfer-friendly memory */
 void * mio_host_alloc(size_t bytes);

@@ -308,6 +308,11 @@ int mio_wav_write_pcm16(const char * path, const int16_t * pcm, int64_t n, int s
     return ok ? MIO_OK : fail(MIO_ERR_IO, std::string("short write to ") + path);
 }
 
+double mio_ctx_stream_seconds(const mio_ctx * c, int64_t * out_passes) {
+    if (out_passes) *out_passes = c ? c->E.stream_passes : 0;
+    return c ? c->E.stream_seconds : 0.0;
+}
+
 // ---- streaming
 void mio_stream_default_config(const mio_ctx * c, mio_stream_config * cfg) {
     if (c && cfg) stream_default_config(c->E, cfg);

@@ -95,6 +95,7 @@ struct engine {
     float * d_wave = nullptr; int64_t wave_cap = 0;       // resident output of the last batch
     int64_t wave_samples = 0;
     int istft_chunks = 0;
+    double stream_seconds = 0.0; int64_t stream_passes = 0;   // wall time / device passes inside streams_step
     // streaming emit buffers (stream.cu)
     void * d_emit = nullptr; void * d_emit_jobs = nullptr; void * h_emit = nullptr;
     int64_t emit_cap = 0, emit_jobs_cap = 0;

@@ -6,6 +6,8 @@
 //     (emit_range, :367-417) run in a device kernel, so only the newly committed samples cross PCIe
 #include "stream.h"
 
+#include <chrono>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -124,6 +126,7 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
         for (int i = 0; i < n_streams; i++)
             if (streams[i] && streams[i]->job_head < streams[i]->jobs.size()) act.push_back(streams[i]);
         if (act.empty()) break;
+        const auto t_pass0 = std::chrono::steady_clock::now();
         if ((int) act.size() > E.max_voices) act.resize(E.max_voices);
         std::vector<int32_t> codes, cu(1, 0), vid;
         std::vector<float> vt;
@@ -182,6 +185,8 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
             s.emitted_samples += J.end - J.begin;
             s.job_head++;
         }
+        E.stream_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - t_pass0).count();
+        E.stream_passes++;
     }
     for (int i = 0; i < n_streams; i++) {
         stream_state * s = streams[i];

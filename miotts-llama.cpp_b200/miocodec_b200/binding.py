@@ -27,7 +27,7 @@ EXPORTS = [
     "mio_stream_close", "mio_stream_push_codes", "mio_stream_finish", "mio_streams_step", "mio_stream_read",
     "mio_stream_stats", "mio_debug_read", "mio_last_error", "mio_version", "mio_host_alloc", "mio_host_free",
     "mio_profile_enable", "mio_profile_categories", "mio_profile_name", "mio_profile_read", "mio_batch_h2d_bytes",
-    "mio_parse_speech_tokens", "mio_decode_pcm16_batch", "mio_batch_fetch_pcm16", "mio_wav_header", "mio_wav_write_pcm16",
+    "mio_ctx_stream_seconds", "mio_parse_speech_tokens", "mio_decode_pcm16_batch", "mio_batch_fetch_pcm16", "mio_wav_header", "mio_wav_write_pcm16",
 ]
 
 
@@ -99,6 +99,8 @@ def lib() -> C.CDLL:
     L.mio_profile_read.argtypes = [vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(i64)]
     L.mio_batch_h2d_bytes.argtypes = [vp]
     L.mio_batch_h2d_bytes.restype = i64
+    L.mio_ctx_stream_seconds.argtypes = [vp, C.POINTER(i64)]
+    L.mio_ctx_stream_seconds.restype = C.c_double
     L.mio_parse_speech_tokens.argtypes = [C.c_char_p, i64, i32p, i64]
     L.mio_parse_speech_tokens.restype = i64
     L.mio_decode_pcm16_batch.argtypes = [vp, i32p, i32p, C.c_int, f32p, C.c_int, i32p, C.c_int, vp, i64]
@@ -304,6 +306,11 @@ class MioCodec:
 
     def open_stream(self, global_emb, cfg: StreamConfig | None = None) -> "Stream":
         return Stream(self, global_emb, cfg)
+
+    def stream_seconds(self):
+        """(seconds, passes) spent in step_streams so far: StreamProfile.codec_sec + istft_sec of the reference, fused."""
+        n = C.c_int64(0)
+        return float(lib().mio_ctx_stream_seconds(self._h, C.byref(n))), int(n.value)
 
     def step_streams(self, streams):
         arr = (C.c_void_p * len(streams))(*[s._h for s in streams])

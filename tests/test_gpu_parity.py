@@ -214,6 +214,7 @@ def test_streaming_matches_reference_policy(codec):
     codes = [synth.synth_codes(n, 70 + i) for i, n in enumerate(N)]
     streams = [codec.open_stream(e) for e in embs]
     got = [[] for _ in streams]
+    sec0, passes0 = codec.stream_seconds()
     for tick in range(max(N)):
         for i, s in enumerate(streams):
             if tick < N[i]:
@@ -234,6 +235,9 @@ def test_streaming_matches_reference_policy(codec):
         assert out.shape == ref_out.shape == (N[i] * 1764,)            # sample_diff == 0 (stream-compare.cpp:258-262)
         assert snr_db(out, ref_out) > 58.0, snr_db(out, ref_out)
         s.close()
+    # StreamProfile's codec_sec + istft_sec: one timed device pass per round in which a cadence fired
+    sec1, passes1 = codec.stream_seconds()
+    assert sec1 > sec0 and 1 <= passes1 - passes0 <= max(N)
 
 
 def test_c3_and_c5_full_batches_sampled_against_live_reference(assets, codec):
