@@ -773,12 +773,21 @@ cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_pa
             o0 = o1 = out_map(p.out_f32, 4, M, ncols, (size_t) p.ld_out * 4);
         }
         if (!o0 || !o1) { prof_end(); return cudaErrorInvalidValue; }
-        // tile width: the widest of {bn2, 128, 64} that still gives every CTA pair a tile (small M = latency mode);
-        // SwiGLU pairs need >= 64 accumulator columns per epilogue warp, i.e. BN >= 128
-        const int tiles_m = (M + 255) / 256, pairs = num_sms / 2;
-        int bn = W.bn2;
+        // tile width: of {bn2, 128, 64} the one with the least (waves of tiles over the CTA pairs) x (tile width), with
+        // an 8 % handicap per halving (narrower tiles re-read A and pay the epilogue more often).  Large M keeps bn2;
+        // small M (a short utterance, the tail piece of the delivery pipeline) gets tiles that fill the machine.
+        // SwiGLU pairs need >= 64 accumulator columns per epilogue warp, i.e. BN >= 128.
+        const int tiles_m = (M + 255) / 256, pairs = std::max(1, num_sms / 2);
         const int bn_min = (p.epi == EPI_SWIGLU) ? 128 : 64;
-        while (bn > bn_min && tiles_m * ((W.N + bn - 1) / bn) < pairs) bn >>= 1;
+        int bn = W.bn2;
+        double best = 1e30;
+        for (int cand = W.bn2; cand >= bn_min; cand >>= 1) {
+            const int tiles = tiles_m * ((W.N + cand - 1) / cand);
+            const double waves = (double) ((tiles + pairs - 1) / pairs);
+            double cost = waves * cand;
+            for (int c = cand; c < W.bn2; c <<= 1) cost *= 1.08;
+            if (cost < best) { best = cost; bn = cand; }
+        }
         const CUtensorMap & bh = bn == W.bn2 ? W.tm2_hi : (bn == 128 ? W.tm128_hi : W.tm64_hi);
         const CUtensorMap & bl = bn == W.bn2 ? W.tm2_lo : (bn == 128 ? W.tm128_lo : W.tm64_lo);
         ce = launch_gemm_tc3(p, A.tm_hi, A.tm_lo, bh, bl, *o0, *o1, bn, stream);
