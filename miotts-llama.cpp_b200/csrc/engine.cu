@@ -754,6 +754,7 @@ void engine::snap_f16(const char * name, const __half * hi, const __half * lo, s
 cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_params p) {
     p.M = M; p.N = W.N; p.K = W.K; p.taps = W.taps; p.npass = W.npass; p.out_scale = W.out_scale;
     p.reverse = next_dir() ? 1 : 0;
+    { static const int order = getenv("MIO_MMA_ORDER") ? atoi(getenv("MIO_MMA_ORDER")) : 2; p.mma_order = order; }
     if (p.bias_mod <= 1) p.bias_mod = W.N;
     p.a_hi = A.hi; p.a_lo = A.lo; p.lda = A.K; p.a_rows = A.rows;
     p.b_hi = W.hi; p.b_lo = W.lo;
