@@ -269,7 +269,7 @@ def bind_to_gpu_numa_node(local: int):
         words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
         cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
         cpus &= os.sched_getaffinity(0)
-        if not cpus:
+        if len(cpus) < 8:                       # never squeeze the 4-thread CPU baseline or the copy threads
             return None
         os.sched_setaffinity(0, cpus)
         return len(cpus)
