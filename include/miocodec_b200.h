@@ -61,7 +61,9 @@ int  mio_ctx_device(const mio_ctx * ctx);
  *          copied and only the tail's own copy is exposed (p ~ D2H time / (compute + D2H time)); 0 = no split; -1 = start
  *          at 12 % and re-estimate p after every call from the measured compute and copy times of the big piece (the
  *          copy is slower when several GPUs of one host deliver at once);
- *          "fetch_chunk_codes" = integer: optional extra cap on the chunk size of that pipeline (default: none). */
+ *          "fetch_chunk_codes" = integer: optional extra cap on the chunk size of that pipeline (default: none);
+ *          "debug_snapshots" = "1" | "0": keep a host copy of every tap of the next decodes (mio_debug_read);
+ *          "debug_snapshot_filter" = comma-separated tap names (empty = all). */
 int  mio_ctx_set_option(mio_ctx * ctx, const char * key, const char * value);
 /* run all kernels of this context on an existing CUDA stream (cudaStream_t as void*), e.g. torch's */
 int  mio_ctx_set_stream(mio_ctx * ctx, void * cuda_stream);
@@ -176,9 +178,20 @@ const char * mio_profile_name(int cat);
 int  mio_profile_read(mio_ctx * ctx, int cat, double * ms, double * flops, double * bytes, int64_t * launches);
 int64_t mio_batch_h2d_bytes(const mio_ctx * ctx);         /* bytes copied host->device by the last upload */
 
-/* ---- introspection for parity tests: copy a named intermediate of the LAST decode to the host.
- * Returns number of floats written or <0.  Names: see csrc/decode.cu (e.g. "prenet_out", "spec"). */
+/* ---- introspection for parity tests: copy a named intermediate of the LAST decode to the host (option
+ * "debug_snapshots" = "1" must be set before the decode).  Returns number of floats written or <0.  Names: the
+ * snap_* / tap() calls of engine::run_chunk in csrc/engine.cu (e.g. "prenet_out", "prior0_c1", "dec3_out", "spec"). */
 int64_t mio_debug_read(mio_ctx * ctx, const char * name, float * out, int64_t cap);
+/* teacher forcing: the next decodes REPLACE the leading n floats of the named tap with `data` when the kernel sequence
+ * reaches it and continue from there (n = 0 removes one override, mio_debug_clear all).  Lets a test feed each stage the
+ * oracle's input for that stage — the stages of miocodec_decode, src/miocodec.cpp:598-740 — and compare its output at
+ * fp32 accuracy, free of the error the earlier stages accumulated. */
+int  mio_debug_write(mio_ctx * ctx, const char * name, const float * data, int64_t n);
+int  mio_debug_clear(mio_ctx * ctx);
+/* one bare GEMM through the product tensor-core kernel: out[M][N] = A[M][K] * B[N][K]^T, operands split (npass = 3: fp16
+ * hi/lo pairs, the decoder's fp32-class layers) or rounded (npass = 1: fp16, its conv1d layers) exactly as the decoder
+ * does; K % 64 == 0.  The per-op parity test of the kernel (cf. the linear layers of src/miocodec.cpp:205-209). */
+int  mio_debug_gemm(mio_ctx * ctx, int M, int N, int K, const float * A, const float * B, int npass, float * out);
 
 const char * mio_last_error(void);
 const char * mio_version(void);

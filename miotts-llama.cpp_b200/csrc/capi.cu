@@ -58,9 +58,6 @@ int mio_ctx_create(const char * gguf_path, int device, mio_ctx ** out_ctx) {
         return fail(classify(e), e);
     }
     if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "simt")) c->E.use_simt = true;
-    if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "tc1")) c->E.gemm_gen = 1;
-    if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "tc2")) c->E.gemm_gen = 2;
-    if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "tc3")) c->E.gemm_gen = 3;
     *out_ctx = c;
     return MIO_OK;
 }
@@ -92,9 +89,7 @@ int mio_ctx_device(const mio_ctx * c) { return c ? c->E.device : -1; }
 int mio_ctx_set_option(mio_ctx * c, const char * key, const char * value) {
     if (!c || !key || !value) return fail(MIO_ERR_ARG, "bad argument");
     if (!strcmp(key, "gemm")) {
-        if (!strcmp(value, "tc") || !strcmp(value, "tc3")) { c->E.use_simt = false; c->E.gemm_gen = 3; }
-        else if (!strcmp(value, "tc1")) { c->E.use_simt = false; c->E.gemm_gen = 1; }
-        else if (!strcmp(value, "tc2")) { c->E.use_simt = false; c->E.gemm_gen = 2; }
+        if (!strcmp(value, "tc") || !strcmp(value, "tc3")) c->E.use_simt = false;
         else if (!strcmp(value, "simt")) c->E.use_simt = true;
         else return fail(MIO_ERR_ARG, "bad argument: gemm must be tc or simt");
         return MIO_OK;
@@ -116,6 +111,10 @@ int mio_ctx_set_option(mio_ctx * c, const char * key, const char * value) {
         const long v = strtol(value, nullptr, 10);
         if (v < -1 || v > 50) return fail(MIO_ERR_ARG, "bad argument: fetch_tail_percent out of range");
         c->E.fetch_tail_percent = (int) v;
+        return MIO_OK;
+    }
+    if (!strcmp(key, "debug_snapshot_filter")) {   // comma-separated tap names; empty = all
+        c->E.snap_filter = value[0] ? std::string(",") + value + "," : std::string();
         return MIO_OK;
     }
     if (!strcmp(key, "debug_snapshots")) {
@@ -393,6 +392,24 @@ int mio_profile_read(mio_ctx * c, int cat, double * ms, double * flops, double *
     return MIO_OK;
 }
 int64_t mio_batch_h2d_bytes(const mio_ctx * c) { return c ? (int64_t) c->E.h2d_bytes : 0; }
+
+int mio_debug_write(mio_ctx * c, const char * name, const float * data, int64_t n) {
+    if (!c || !name || n < 0 || (!data && n > 0)) return fail(MIO_ERR_ARG, "bad argument");
+    if (n == 0) c->E.overrides.erase(name);
+    else c->E.overrides[name].assign(data, data + n);
+    return MIO_OK;
+}
+int mio_debug_clear(mio_ctx * c) {
+    if (!c) return fail(MIO_ERR_ARG, "bad argument");
+    c->E.overrides.clear();
+    return MIO_OK;
+}
+
+int mio_debug_gemm(mio_ctx * c, int M, int N, int K, const float * A, const float * B, int npass, float * out) {
+    if (!c) return fail(MIO_ERR_ARG, "bad argument");
+    TRY(c->E.debug_gemm(M, N, K, A, B, npass, out));
+    return MIO_OK;
+}
 
 int64_t mio_debug_read(mio_ctx * c, const char * name, float * out, int64_t cap) {
     if (!c || !name) return fail(MIO_ERR_ARG, "bad argument");

@@ -280,75 +280,85 @@ cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, 
 // ---------------------------------------------------------------------------------------------
 // GroupNorm statistics over (all rows of an utterance) x (C/32 channels)
 // (conv_group_norm, src/miocodec.cpp:358-371; ggml_compute_forward_group_norm_f32, ggml-cpu/ops.cpp:3955-4028).
-// Block = C/4 threads (one float4 of channels each) x GN_ROWS rows, read 8 rows at a time so eight independent
-// 16-byte loads are in flight per thread; partial sums are flushed with fp64 atomics whenever the utterance changes
-// inside the block's rows.
-constexpr int GN_ROWS = 64;
-
-__global__ void gn_stats_kernel(const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt,
-                                int row_div, double * __restrict__ stats, int rows_per_block, int rev) {
-    const int c4 = threadIdx.x;                    // float4 index within the row
-    const int cpg = C / 32;                        // channels per group: 16, 8 or 4
-    const int tpg = cpg / 4;                       // threads per group: 4, 2 or 1
-    const int group = (c4 * 4) / cpg;
-    const int r0 = (rev ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * rows_per_block;
-    const int r1 = min(rows, r0 + rows_per_block);
+//
+// Deterministic and batch-invariant, like the reference: a fixed-order two-stage reduction whose
+// partition depends only on the utterance.  Stage 1: one block per (utterance, segment of GN_SEG_CODES codes counted
+// from the utterance's first row); thread (c4, rl) sums one float4 column over the rows rl, rl + RL, ... of the segment
+// in ascending order, the partial sums of a group are combined by an xor-shuffle tree and then over rl in ascending
+// order -> part[segment][group] = (sum, sum of squares) in fp64.  Stage 2 (gn_finalize_kernel): one thread per
+// (utterance, group) adds the segments in ascending order.  No atomics: the same utterance gives the same bits alone,
+// in any batch, at any position and under any chunking.
+__global__ void __launch_bounds__(256) gn_stats_kernel(const float * __restrict__ x, int C, const int32_t * __restrict__ start,
+                                                       const int32_t * __restrict__ len, const int32_t * __restrict__ seg_cu,
+                                                       int n_utts, int row_div, double2 * __restrict__ part, int rev) {
+    __shared__ float2 red[8][32];
+    const int sb = rev ? gridDim.x - 1 - blockIdx.x : blockIdx.x;
+    int lo = 0, hi = n_utts;                       // largest u with seg_cu[u] <= sb
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (seg_cu[mid] <= sb) lo = mid; else hi = mid;
+    }
+    const int u = lo, seg = sb - seg_cu[u];
+    const int C4 = C >> 2;                         // threads per row: 128, 64 or 32
+    const int RL = 256 / C4;                       // row lanes: 2, 4 or 8
+    const int c4 = threadIdx.x % C4, rl = threadIdx.x / C4;
+    const int cpg = C / 32, tpg = cpg / 4;         // channels / threads per group: (16,4), (8,2), (4,1)
+    const int r0 = (start[u] + seg * GN_SEG_CODES) * row_div;
+    const int nrows = min(GN_SEG_CODES, len[u] - seg * GN_SEG_CODES) * row_div;
+    const float * xp = x + (size_t) r0 * C + c4 * 4;
     float s = 0.f, q = 0.f;
-    int cur = -1;
-    auto flush = [&](int utt) {
-        float ss = s, qq = q;
-        for (int o = tpg >> 1; o > 0; o >>= 1) {
-            ss += __shfl_xor_sync(0xffffffffu, ss, o);
-            qq += __shfl_xor_sync(0xffffffffu, qq, o);
-        }
-        if (utt >= 0 && (c4 % tpg) == 0) {
-            atomicAdd(stats + ((size_t) utt * 32 + group) * 2, (double) ss);
-            atomicAdd(stats + ((size_t) utt * 32 + group) * 2 + 1, (double) qq);
-        }
-        s = 0.f; q = 0.f;
-    };
-    for (int rb = r0; rb < r1; rb += 8) {
+    for (int rb = rl; rb < nrows; rb += 8 * RL) {
         float4 v[8];
-        int uu[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            const int r = rb + k;
-            uu[k] = (r < r1) ? row_utt[r / row_div] : -2;      // block-uniform; -2 = past the end
-            v[k] = (uu[k] >= 0) ? __ldg((const float4 *) (x + (size_t) r * C + c4 * 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const int r = rb + k * RL;
+            v[k] = (r < nrows) ? __ldg((const float4 *) (xp + (size_t) r * C)) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            if (uu[k] == -2) break;
-            if (uu[k] != cur) { flush(cur); cur = uu[k]; }
             s += (v[k].x + v[k].y) + (v[k].z + v[k].w);
             q += (v[k].x * v[k].x + v[k].y * v[k].y) + (v[k].z * v[k].z + v[k].w * v[k].w);
         }
     }
-    flush(cur);
+    for (int o = tpg >> 1; o > 0; o >>= 1) {       // the tpg threads of a group are adjacent lanes of one warp
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if ((c4 % tpg) == 0) red[rl][c4 / tpg] = make_float2(s, q);
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double ds = 0.0, dq = 0.0;
+        for (int k = 0; k < RL; k++) { ds += (double) red[k][threadIdx.x].x; dq += (double) red[k][threadIdx.x].y; }
+        part[(size_t) sb * 32 + threadIdx.x] = make_double2(ds, dq);
+    }
 }
 
-cudaError_t launch_gn_stats(const float * x, int rows, int C, const row_map & rm, int row_div, double * stats,
-                            cudaStream_t st, bool rev) {
-    if (rows <= 0) return cudaSuccess;
-    if (C % 128 != 0) return cudaErrorInvalidValue;
-    // few rows (a single short utterance): shorter row runs per block so the serial load rounds do not set the latency
-    const int rpb = (rows >= GN_ROWS * 148 * 4) ? GN_ROWS : 16;
-    gn_stats_kernel<<<(rows + rpb - 1) / rpb, C / 4, 0, st>>>(x, rows, C, rm.row_utt, row_div, stats, rpb, rev ? 1 : 0);
+cudaError_t launch_gn_stats(const float * x, int C, const row_map & rm, int row_div, const int32_t * seg_cu, int total_segs,
+                            double2 * part, cudaStream_t st, bool rev) {
+    if (total_segs <= 0) return cudaSuccess;
+    if (C != 512 && C != 256 && C != 128) return cudaErrorInvalidValue;
+    gn_stats_kernel<<<total_segs, 256, 0, st>>>(x, C, rm.start, rm.len, seg_cu, rm.n_utts, row_div, part, rev ? 1 : 0);
     return cudaGetLastError();
 }
 
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
 
-// (sum, sum of squares) in fp64 -> (mean, 1/sqrt(var + eps)) in fp32, once per (utterance, group): keeps the fp64
-// arithmetic (slow on this part) out of the per-element kernel.  var = sum((x-mean)^2)/n with the float-rounded
-// mean, like the reference's second pass (ops.cpp:3990-4010).
-__global__ void gn_finalize_kernel(const double * __restrict__ stats, const int32_t * __restrict__ len, int n_utts, int row_div,
+// stage 2: segments of an utterance added in ascending order (fp64), then (sum, sum of squares) -> (mean,
+// 1/sqrt(var + eps)) in fp32, once per (utterance, group): keeps the fp64 arithmetic (slow on this part) out of the
+// per-element kernel.  var = sum((x-mean)^2)/n with the float-rounded mean, like the reference's second pass
+// (ops.cpp:3990-4010).
+__global__ void gn_finalize_kernel(const double2 * __restrict__ part, const int32_t * __restrict__ seg_cu,
+                                   const int32_t * __restrict__ len, int n_utts, int row_div,
                                    int cpg, float eps, float2 * __restrict__ mr) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= n_utts * 32) return;
-    const int u = idx >> 5;
+    const int u = idx >> 5, g = idx & 31;
+    double sum = 0.0, sq = 0.0;
+    for (int sg = seg_cu[u]; sg < seg_cu[u + 1]; sg++) {
+        const double2 p = part[(size_t) sg * 32 + g];
+        sum += p.x; sq += p.y;
+    }
     const double n = (double) len[u] * row_div * cpg;
-    const double sum = stats[(size_t) idx * 2], sq = stats[(size_t) idx * 2 + 1];
     const float mean = (float) (sum / n);
     const double md = (double) mean;
     const float var = (float) ((sq - 2.0 * md * sum) / n + md * md);
@@ -414,11 +424,12 @@ __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
     }
 }
 
-cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double * stats,
-                                 float eps, const float * w, const float * b, float2 * mr_scratch, __half * out, cudaStream_t st, bool rev) {
+cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double2 * part,
+                                 const int32_t * seg_cu, float eps, const float * w, const float * b, float2 * mr_scratch,
+                                 __half * out, cudaStream_t st, bool rev) {
     if (rows <= 0) return cudaSuccess;
     if (C % 128 != 0 || C > 2048) return cudaErrorInvalidValue;
-    gn_finalize_kernel<<<(rm.n_utts * 32 + 255) / 256, 256, 0, st>>>(stats, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
+    gn_finalize_kernel<<<(rm.n_utts * 32 + 255) / 256, 256, 0, st>>>(part, seg_cu, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
     static int precise_set = -1;
     if (precise_set < 0) {
         const char * ev = getenv("MIO_GN_PRECISE");

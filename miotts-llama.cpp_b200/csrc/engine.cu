@@ -13,7 +13,6 @@ namespace mio {
         if (_e != cudaSuccess) return std::string(#expr) + ": " + cudaGetErrorString(_e);              \
     } while (0)
 
-constexpr int GN_SLOTS = 16;
 constexpr int SPEC_LD = 400;   // spectrogram row pitch in floats: 394 padded to a 16-byte multiple (TMA store pitch rule)
 
 // ---------------------------------------------------------------------------------------------
@@ -70,15 +69,18 @@ static std::string make_out_map(CUtensorMap * tm, const void * base, int esize, 
     return {};
 }
 
-const CUtensorMap * engine::out_map(const void * base, int esize, int rows, int cols, size_t ld_bytes, int box_c, int box_r) {
+// Returns the descriptor BY VALUE (128 bytes): the cache may evict at any call without invalidating what earlier
+// calls of the same launch handed out.  Keys include the row count M, so a streaming session (a new M nearly every
+// round) keeps inserting; the cache is simply emptied when it reaches 4096 entries.
+bool engine::out_map(CUtensorMap * out, const void * base, int esize, int rows, int cols, size_t ld_bytes, int box_c, int box_r) {
     out_map_key k{base, esize, rows, cols, ld_bytes, box_c, box_r};
     auto it = out_maps.find(k);
-    if (it != out_maps.end()) return &it->second;
-    CUtensorMap tm;
-    std::string e = make_out_map(&tm, base, esize, rows, cols, ld_bytes, box_c, box_r);
-    if (!e.empty()) { err = e; return nullptr; }
-    if (out_maps.size() > 4096) out_maps.clear();        // bounded: shapes repeat in steady state
-    return &(out_maps[k] = tm);
+    if (it != out_maps.end()) { *out = it->second; return true; }
+    std::string e = make_out_map(out, base, esize, rows, cols, ld_bytes, box_c, box_r);
+    if (!e.empty()) { err = e; return false; }
+    if (out_maps.size() >= 4096) out_maps.clear();
+    out_maps[k] = *out;
+    return true;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -114,10 +116,10 @@ engine::~engine() {
     if (stream && own_stream) cudaStreamSynchronize(stream);
     auto F = [](void * p) { if (p) cudaFree(p); };
     F(x768); F(qkv_hi); F(qkv_lo); F(x512); F(y512); F(x256); F(y256); F(x128); F(y128); F(spec); F(mod); F(peak);
-    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_stats); F(gn_mr); F(voice_silu); F(attn_b1); F(attn_b2); F(err_flag);
-    F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_out_off); F(d_voice_table); F(d_wave);
+    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_part); F(gn_mr); F(voice_silu); F(attn_b1); F(attn_b2); F(err_flag);
+    F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_seg_cu); F(d_out_off); F(d_voice_table); F(d_wave);
     for (void * p : w_allocs) F(p);
-    F(d_emit); F(d_emit_jobs); F(d_pcm);
+    F(d_emit); F(d_emit_jobs); F(d_pcm); F(w.rope_pre); F(w.rope_t);
     if (h_emit) cudaFreeHost(h_emit);
     if (h_stage) cudaFreeHost(h_stage);
     if (stream && own_stream) cudaStreamDestroy(stream);
@@ -129,6 +131,8 @@ engine::~engine() {
 // ---------------------------------------------------------------------------------------------
 // load: GGUF -> HBM.  KV keys and defaults follow miocodec_load (src/miocodec.cpp:447-481).
 // ---------------------------------------------------------------------------------------------
+static std::string make_view(a_view & v, __half * hi, __half * lo, int rows, int K);
+
 namespace {
 struct loader {
     engine & E;
@@ -193,10 +197,7 @@ struct loader {
         cudaError_t ce = cudaDeviceSynchronize();
         cudaFree(tmp);
         if (ce != cudaSuccess) { err = std::string("split_weights_kernel: ") + cudaGetErrorString(ce); return false; }
-        W.box_n = (N % 256 == 0) ? 256 : 128;
-        std::string e = make_map(&W.tm_hi, W.hi, N, K * taps, W.box_n);
-        if (e.empty() && W.lo) e = make_map(&W.tm_lo, W.lo, N, K * taps, W.box_n);
-        if (e.empty() && !W.lo) W.tm_lo = W.tm_hi;
+        std::string e;
         // 256-wide tiles whenever they pad N no further than 128-wide ones would (e.g. the head, N = 394 -> 512 either
         // way): half as many passes over the A operand
         W.bn2 = ((N + 255) / 256 * 256 == (N + 127) / 128 * 128) ? 256 : 128;
@@ -466,44 +467,64 @@ std::string engine::load(const std::string & path, int dev) {
         if (!L.pack(w.head, B, 2 * NF, P, 1, 3)) return L.err;
         w.head_b = L.vec_host(bb);
     }
-    // RoPE table: theta_i = pos * s^i built by repeated multiplication in f32, cosf/sinf of libm — exactly the
-    // reference's cache (ggml_rope_cache_init, ggml-cpu/ops.cpp:5612-5626; theta_scale = powf(base, -2/n_dims))
-    {
-        w.rope_max_pos = 8192;
-        std::vector<float> r((size_t) w.rope_max_pos * 64);
-        const float theta_scale = powf(hp.rope_theta, -2.0f / 64.0f);
-        for (int pos = 0; pos < w.rope_max_pos; pos++) {
-            float theta = (float) pos;
-            for (int i = 0; i < 32; i++) {
-                r[((size_t) pos * 32 + i) * 2] = cosf(theta);
-                r[((size_t) pos * 32 + i) * 2 + 1] = sinf(theta);
-                theta *= theta_scale;
-            }
-        }
-        w.rope_pre = L.vec_host(r);
-        // the same values position-minor for the generation-3 epilogue, where lane = row = consecutive positions:
-        // rope_t[half h][i][pos] = the four floats (cos, sin, cos, sin) of pairs h*16 + 2i, 2i+1 -> a warp's float4 load
-        // covers 512 contiguous bytes instead of 32 separate lines
-        std::vector<float> rt(r.size());
-        for (int h = 0; h < 2; h++)
-            for (int i = 0; i < 8; i++)
-                for (int pos = 0; pos < w.rope_max_pos; pos++)
-                    for (int j = 0; j < 4; j++)
-                        rt[((size_t) (h * 8 + i) * w.rope_max_pos + pos) * 4 + j] = r[((size_t) pos * 32 + h * 16 + 2 * i) * 2 + j];
-        w.rope_t = L.vec_host(rt);
-    }
     {   // periodic Hann window (istft_cache, src/istft.cpp:29-31)
         std::vector<float> hn(hp.n_fft);
         for (int i = 0; i < hp.n_fft; i++) hn[i] = 0.5f * (1.0f - cosf(2.0f * (float) M_PI * i / hp.n_fft));
         w.hann = L.vec_host(hn);
+        std::vector<float> tw(784);
+        istft_twiddles(tw.data());
+        w.istft_tw = L.vec_host(tw);
     }
     if (!L.err.empty()) return L.err;
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     own_stream = true;
+    if (!(e = ensure_rope(8192)).empty()) return e;
+    // > 48 KB dynamic shared memory opt-ins are per device: set for THIS context's device
+    CK(gemm_tc3_init_device());
     CK(attention_init());
+    CK(istft_init_device());
     { const char * ev = getenv("MIO_ATTN"); attn_simt = ev && !strcmp(ev, "simt"); }
     { const char * ev = getenv("MIO_SERPENTINE"); if (ev && ev[0] == '0') serpentine = false; }
     CK(cudaDeviceSynchronize());
+    return {};
+}
+
+// RoPE table for positions [0, max_pos): theta_i = pos * s^i built by repeated multiplication in f32, cosf/sinf of libm —
+// exactly the reference's cache (ggml_rope_cache_init, ggml-cpu/ops.cpp:5612-5626; theta_scale = powf(base, -2/n_dims)).
+// Grown on demand (the reference computes the phases for any position): upload() asks for 2 * (longest utterance).
+std::string engine::ensure_rope(int max_pos) {
+    if (max_pos <= w.rope_max_pos) return {};
+    int n = std::max(8192, w.rope_max_pos);
+    while (n < max_pos) n *= 2;
+    std::vector<float> r((size_t) n * 64);
+    const float theta_scale = powf(hp.rope_theta, -2.0f / 64.0f);
+    for (int pos = 0; pos < n; pos++) {
+        float theta = (float) pos;
+        for (int i = 0; i < 32; i++) {
+            r[((size_t) pos * 32 + i) * 2] = cosf(theta);
+            r[((size_t) pos * 32 + i) * 2 + 1] = sinf(theta);
+            theta *= theta_scale;
+        }
+    }
+    // the same values position-minor for the tcgen05 epilogue, where lane = row = consecutive positions:
+    // rope_t[half h][i][pos] = the four floats (cos, sin, cos, sin) of pairs h*16 + 2i, 2i+1 -> a warp's float4 load
+    // covers 512 contiguous bytes instead of 32 separate lines
+    std::vector<float> rt(r.size());
+    for (int h = 0; h < 2; h++)
+        for (int i = 0; i < 8; i++)
+            for (int pos = 0; pos < n; pos++)
+                for (int j = 0; j < 4; j++)
+                    rt[((size_t) (h * 8 + i) * n + pos) * 4 + j] = r[((size_t) pos * 32 + h * 16 + 2 * i) * 2 + j];
+    CK(cudaSetDevice(device));
+    if (stream) CK(cudaStreamSynchronize(stream));     // kernels of the previous batch may still read the old tables
+    if (w.rope_pre) cudaFree(w.rope_pre);
+    if (w.rope_t) cudaFree(w.rope_t);
+    w.rope_pre = w.rope_t = nullptr;
+    w.rope_max_pos = 0;
+    std::string e = upload_f32(r, &w.rope_pre);
+    if (e.empty()) e = upload_f32(rt, &w.rope_t);
+    if (!e.empty()) return e;
+    w.rope_max_pos = n;
     return {};
 }
 
@@ -524,6 +545,14 @@ std::string engine::init_istft_only(int dev) {
     std::string e = upload_f32(hn, &w.hann);
     if (!e.empty()) return e;
     w_allocs.push_back(w.hann);
+    {
+        std::vector<float> tw(784);
+        istft_twiddles(tw.data());
+        e = upload_f32(tw, &w.istft_tw);
+        if (!e.empty()) return e;
+        w_allocs.push_back(w.istft_tw);
+    }
+    CK(istft_init_device());
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     own_stream = true;
     return {};
@@ -557,7 +586,7 @@ std::string engine::ensure_workspace() {
     A(spec, R18 * SPEC_LD);
     A(aA_hi, R1 * 1024); A(aA_lo, R1 * 1024); A(aFF_hi, R1 * 3072); A(aFF_lo, R1 * 3072);
     A(c16, R1 * 2304); A(h512_hi, R18 * 512); A(h512_lo, R18 * 512);
-    A(gn_stats, (size_t) GN_SLOTS * max_utts * 64);
+    A(gn_part, (size_t) (max_rows1 / GN_SEG_CODES + max_utts + 1) * 32);
     A(gn_mr, (size_t) max_utts * 32);
     A(attn_b1, R1); A(attn_b2, R2);
     A(mod, (size_t) max_voices * w.cond_rows);
@@ -612,20 +641,28 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
     const int fpc = hp.frames_per_code;
     int64_t rows_total = 0;
     std::vector<int32_t> chunk_cu_all;   // per chunk: local prefix of istft chunk counts (n+1 entries each)
+    std::vector<int32_t> seg_cu_all;     // per chunk: local prefix of GroupNorm segment counts (n+1 entries each)
+    // Every utterance starts on a multiple of ROW_ALIGN rows (code resolution) of its chunk and is followed by at least
+    // one zero row: the 16-row groups of the attention kernel and the GroupNorm segments then sit at utterance-relative
+    // positions, which makes an utterance's result bit-identical wherever it lies in a batch (the reference is
+    // batch-invariant by construction: it decodes one utterance per call).
+    auto slot_rows = [](int T) { return (T + 1 + ROW_ALIGN - 1) / ROW_ALIGN * ROW_ALIGN; };
     // Pipelined delivery: chunk i's D2H copy runs while chunk i+1 computes, so only the LAST copy is exposed.  Every
     // extra chunk costs ~1 ms of launch tails (160 kernels), so the batch is cut as rarely as the workspace allows and
     // the final chunk is split once more into (100 - p) % and p %: with p = fetch_tail_percent ~ D2H time / (compute +
     // D2H time) the small tail computes exactly while the big piece is copied, and only the tail's own copy is exposed.
     int64_t rows_left = 0;
-    for (int i = 0; i < n_utts; i++) rows_left += (int64_t) std::max(0, cu[i + 1] - cu[i]) + 1;
+    for (int i = 0; i < n_utts; i++) rows_left += (int64_t) slot_rows(std::max(0, cu[i + 1] - cu[i]));
     bool tail_split_done = false;
     big_piece_chunk = -1;
+    int t_max = 0;
     int u = 0;
     while (u < n_utts) {
         chunk_info c;
-        c.utt0 = u; c.row0 = (int) rows_total; c.cu0 = (int) chunk_cu_all.size();
-        int rows = 0, blocks = 0;
+        c.utt0 = u; c.row0 = (int) rows_total; c.cu0 = (int) chunk_cu_all.size(); c.scu0 = (int) seg_cu_all.size();
+        int rows = 0, blocks = 0, segs = 0;
         chunk_cu_all.push_back(0);
+        seg_cu_all.push_back(0);
         int row_cap_c = row_cap;
         const int tail_pct = fetch_tail_percent >= 0 ? fetch_tail_percent : (int) (tail_auto_pct + 0.5f);
         if (chunk_rows_limit > 0 && tail_pct > 0 && !tail_split_done && rows_left <= row_cap && rows_left >= 4096) {
@@ -636,9 +673,11 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
         while (u < n_utts) {
             const int T = cu[u + 1] - cu[u];
             if (T < 0) return "cu_seqlens must be non-decreasing";
-            if (T + 1 > max_rows1) return "utterance of " + std::to_string(T) + " codes exceeds max_chunk_codes";
+            const int slot = slot_rows(T);
+            if (slot > max_rows1) return "utterance of " + std::to_string(T) + " codes exceeds max_chunk_codes";
+            t_max = std::max(t_max, T);
             if (voice_ids[u] < 0 || voice_ids[u] >= nv) return "voice id out of range";
-            if ((rows + T + 1 > row_cap_c && rows > 0) || rows + T + 1 > max_rows1 || (u - c.utt0) >= max_utts) break;
+            if ((rows + slot > row_cap_c && rows > 0) || rows + slot > max_rows1 || (u - c.utt0) >= max_utts) break;
             lay.start.push_back(rows); lay.len.push_back(T); lay.voice.push_back(voice_ids[u]);
             lay.out_off.push_back((int64_t) cu[u] * hp.samples_per_token);
             for (int i = 0; i < T; i++) {
@@ -648,16 +687,19 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
                            std::to_string(u) + " is outside [0, " + std::to_string(hp.vocab) + ")";
                 lay.codes_padded.push_back(code); lay.row_utt.push_back(u - c.utt0);
             }
-            lay.codes_padded.push_back(-1); lay.row_utt.push_back(-1);
-            rows += T + 1;
+            for (int i = T; i < slot; i++) { lay.codes_padded.push_back(-1); lay.row_utt.push_back(-1); }
+            rows += slot;
             blocks += (T * fpc + ISTFT_SEG_PER_BLOCK - 1) / ISTFT_SEG_PER_BLOCK;
             chunk_cu_all.push_back(blocks);
+            segs += (T + GN_SEG_CODES - 1) / GN_SEG_CODES;
+            seg_cu_all.push_back(segs);
             u++;
         }
-        c.n_utts = u - c.utt0; c.rows1 = rows; c.istft_blocks = blocks;
+        c.n_utts = u - c.utt0; c.rows1 = rows; c.istft_blocks = blocks; c.n_segs = segs;
         rows_total += rows; rows_left -= rows;
         chunks.push_back(c);
     }
+    if (!(e = ensure_rope(2 * t_max)).empty()) return e;    // decoder positions run to 2 T - 1
     lay.rows1 = (int) rows_total;
     lay.total_codes = n_utts ? cu[n_utts] : 0;
     wave_samples = lay.total_codes * hp.samples_per_token;
@@ -679,6 +721,7 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
             !(e = dev_alloc(&d_voice, cap_utts)).empty() || !(e = dev_alloc(&d_out_off, cap_utts)).empty()) return e;
     }
     if (!(e = grow(&d_chunk_cu, cap_ccu, chunk_cu_all.size())).empty()) return e;
+    if (!(e = grow(&d_seg_cu, cap_scu, seg_cu_all.size())).empty()) return e;
     if (!(e = grow(&d_voice_table, cap_vt, (size_t) nv * hp.adaln_dim)).empty()) return e;
     if ((int64_t) wave_cap < wave_samples) {
         if (d_wave) cudaFree(d_wave);
@@ -689,7 +732,7 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
     // one pinned staging buffer, async copies on the context stream
     const size_t b_codes = (size_t) rows_total * 4, b_utts = (size_t) n_utts * 4, b_off = (size_t) n_utts * 8,
                  b_ccu = chunk_cu_all.size() * 4, b_vt = (size_t) nv * hp.adaln_dim * 4;
-    const size_t need = 2 * b_codes + 3 * b_utts + b_off + b_ccu + b_vt + 256;
+    const size_t need = 2 * b_codes + 3 * b_utts + b_off + 2 * b_ccu + b_vt + 256;
     if (need > h_stage_bytes) {
         if (h_stage) cudaFreeHost(h_stage);
         h_stage = nullptr;
@@ -713,9 +756,10 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
     CK(put(d_voice, lay.voice.data(), b_utts));
     CK(put(d_out_off, lay.out_off.data(), b_off));
     CK(put(d_chunk_cu, chunk_cu_all.data(), b_ccu));
+    CK(put(d_seg_cu, seg_cu_all.data(), b_ccu));
     CK(put(d_voice_table, voice_table, b_vt));
     n_voices = nv;
-    h2d_bytes = 2 * b_codes + 3 * b_utts + b_off + b_ccu + b_vt;
+    h2d_bytes = 2 * b_codes + 3 * b_utts + b_off + 2 * b_ccu + b_vt;
     batch_uploaded = true;
     return {};
 }
@@ -723,22 +767,39 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
 // ---------------------------------------------------------------------------------------------
 // debug snapshots
 // ---------------------------------------------------------------------------------------------
-void engine::snap_f32(const char * name, const float * d, size_t n) {
-    if (!debug_snap) return;
-    cudaStreamSynchronize(stream);
-    std::vector<float> & v = snaps[name];
-    v.resize(n);
-    cudaMemcpy(v.data(), d, n * sizeof(float), cudaMemcpyDeviceToHost);
-}
-void engine::snap_f32_2d(const char * name, const float * d, size_t rows, size_t cols, size_t ld) {
-    if (!debug_snap) return;
+// A tap is a named point of the kernel sequence.  With option "debug_snapshots" the buffer is copied to the host
+// (mio_debug_read); a pending mio_debug_write of the same name REPLACES the buffer's leading rows first, so the
+// kernels behind the tap run on the injected values (teacher-forced per-stage parity tests: every stage is fed the
+// oracle's input for that stage and compared with the oracle's output at fp32 accuracy).
+void engine::tap_f32(const std::string & name, float * d, size_t rows, size_t cols, size_t ld) {
+    if (ld == 0) ld = cols;
+    auto ov = overrides.find(name);
+    if (ov != overrides.end() && !ov->second.empty()) {
+        const size_t r = std::min(rows, ov->second.size() / cols);
+        cudaMemcpy2DAsync(d, ld * sizeof(float), ov->second.data(), cols * sizeof(float), cols * sizeof(float), r, cudaMemcpyHostToDevice, stream);
+        cudaStreamSynchronize(stream);
+    }
+    if (!snap_wanted(name)) return;
     cudaStreamSynchronize(stream);
     std::vector<float> & v = snaps[name];
     v.resize(rows * cols);
     cudaMemcpy2D(v.data(), cols * sizeof(float), d, ld * sizeof(float), cols * sizeof(float), rows, cudaMemcpyDeviceToHost);
 }
-void engine::snap_f16(const char * name, const __half * hi, const __half * lo, size_t n) {
-    if (!debug_snap) return;
+void engine::tap_f16(const std::string & name, __half * hi, __half * lo, size_t n) {
+    auto ov = overrides.find(name);
+    if (ov != overrides.end() && !ov->second.empty()) {
+        const size_t m = std::min(n, ov->second.size());
+        std::vector<__half> h(m), l(m);
+        for (size_t i = 0; i < m; i++) {
+            const float x = ov->second[i];
+            h[i] = __float2half_rn(x);
+            l[i] = __float2half_rn(x - __half2float(h[i]));
+        }
+        cudaMemcpyAsync(hi, h.data(), m * 2, cudaMemcpyHostToDevice, stream);
+        if (lo) cudaMemcpyAsync(lo, l.data(), m * 2, cudaMemcpyHostToDevice, stream);
+        cudaStreamSynchronize(stream);
+    }
+    if (!snap_wanted(name)) return;
     cudaStreamSynchronize(stream);
     std::vector<uint16_t> a(n), b(n);
     cudaMemcpy(a.data(), hi, n * 2, cudaMemcpyDeviceToHost);
@@ -763,17 +824,18 @@ cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_pa
     prof_begin(W.npass == 3 ? CAT_GEMM_SPLIT : CAT_GEMM_F16, 2.0 * M * (double) W.N * W.K * W.taps, 0.0);
     cudaError_t ce;
     if (use_simt) ce = launch_gemm_simt(p, stream);
-    else if (gemm_gen == 3) {
+    else {
         const bool f16 = (p.epi == EPI_SWIGLU || p.epi == EPI_SPLIT || p.epi == EPI_QKV);
         const int ncols = (p.epi == EPI_SWIGLU) ? W.N / 2 : W.N;
-        const CUtensorMap *o0, *o1;
+        CUtensorMap o0, o1;
+        bool ok;
         if (f16) {
-            o0 = out_map(p.out_hi, 2, M, ncols, (size_t) p.ld_h * 2);
-            o1 = out_map(p.out_lo, 2, M, ncols, (size_t) p.ld_h * 2);
+            ok = out_map(&o0, p.out_hi, 2, M, ncols, (size_t) p.ld_h * 2) && out_map(&o1, p.out_lo, 2, M, ncols, (size_t) p.ld_h * 2);
         } else {
-            o0 = o1 = out_map(p.out_f32, 4, M, ncols, (size_t) p.ld_out * 4);
+            ok = out_map(&o0, p.out_f32, 4, M, ncols, (size_t) p.ld_out * 4);
+            o1 = o0;
         }
-        if (!o0 || !o1) { prof_end(); return cudaErrorInvalidValue; }
+        if (!ok) { prof_end(); return cudaErrorInvalidValue; }
         // tile width: of {bn2, 128, 64} the one with the least (waves of tiles over the CTA pairs) x (tile width), with
         // an 8 % handicap per halving (narrower tiles re-read A and pay the epilogue more often).  Large M keeps bn2;
         // small M (a short utterance, the tail piece of the delivery pipeline) gets tiles that fill the machine.
@@ -791,11 +853,50 @@ cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_pa
         }
         const CUtensorMap & bh = bn == W.bn2 ? W.tm2_hi : (bn == 128 ? W.tm128_hi : W.tm64_hi);
         const CUtensorMap & bl = bn == W.bn2 ? W.tm2_lo : (bn == 128 ? W.tm128_lo : W.tm64_lo);
-        ce = launch_gemm_tc3(p, A.tm_hi, A.tm_lo, bh, bl, *o0, *o1, bn, stream);
-    } else if (gemm_gen == 2) ce = launch_gemm_tc2(p, A.tm_hi, A.tm_lo, W.tm2_hi, W.tm2_lo, W.bn2, stream);
-    else ce = launch_gemm_tc(p, A.tm_hi, A.tm_lo, W.tm_hi, W.tm_lo, W.box_n, stream);
+        ce = launch_gemm_tc3(p, A.tm_hi, A.tm_lo, bh, bl, o0, o1, bn, num_sms, stream);
+    }
     prof_end();
     return ce;
+}
+
+// One bare GEMM through the product kernel (mio_debug_gemm): out[M][N] = A[M][K] * B[N][K]^T with the operands split /
+// rounded exactly as the decoder does (npass 3: fp16 hi/lo pairs, npass 1: fp16).  Per-op parity tests and the
+// accumulation study (tools/accuracy_study.py) compare it with an fp64 product of the same operands.
+std::string engine::debug_gemm(int M, int N, int K, const float * A, const float * B, int npass, float * out) {
+    if (M <= 0 || N <= 0 || K <= 0 || K % 64 != 0 || !A || !B || !out || (npass != 1 && npass != 3)) return "bad argument";
+    if (istft_only) return "bad argument: this context has no decoder";
+    CK(cudaSetDevice(device));
+    gguf_file none;
+    loader L(*this, none);
+    gemm_weight W;
+    const size_t n_before = w_allocs.size();
+    std::vector<float> Bv(B, B + (size_t) N * K);
+    if (!L.pack(W, Bv, N, K, 1, npass)) return L.err;
+    float *dA = nullptr, *dO = nullptr;
+    __half *ah = nullptr, *al = nullptr;
+    std::string e;
+    auto cleanup = [&]() {
+        cudaStreamSynchronize(stream);
+        for (void * p : {(void *) dA, (void *) dO, (void *) ah, (void *) al}) if (p) cudaFree(p);
+        while (w_allocs.size() > n_before) { cudaFree(w_allocs.back()); w_allocs.pop_back(); }
+        out_maps.clear();                                // the freed buffers' addresses may be reused
+    };
+    const size_t na = (size_t) M * K;
+    if (!(e = dev_alloc(&dA, na)).empty() || !(e = dev_alloc(&dO, (size_t) M * N)).empty() || !(e = dev_alloc(&ah, na)).empty() ||
+        !(e = dev_alloc(&al, na)).empty()) { cleanup(); return e; }
+    cudaMemcpy(dA, A, na * sizeof(float), cudaMemcpyHostToDevice);
+    split_weights_kernel<<<296, 256>>>(dA, na, 1.0f, ah, npass == 3 ? al : nullptr);
+    if (cudaDeviceSynchronize() != cudaSuccess) { cleanup(); return "split kernel failed"; }
+    a_view v;
+    if (!(e = make_view(v, ah, npass == 3 ? al : nullptr, M, K)).empty()) { cleanup(); return e; }
+    gemm_params p;
+    p.epi = EPI_STORE; p.out_f32 = dO; p.ld_out = N;
+    cudaError_t ce = gemm(W, v, M, p);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(stream);
+    if (ce == cudaSuccess) ce = cudaMemcpy(out, dO, (size_t) M * N * sizeof(float), cudaMemcpyDeviceToHost);
+    cleanup();
+    if (ce != cudaSuccess) return std::string("debug_gemm: ") + cudaGetErrorString(ce);
+    return {};
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -846,23 +947,25 @@ void engine::prof_collect() {
     } while (0)
 
 std::string engine::run_resblock(const resblock_w & R, float * x, float * y, const a_view & vc, int rows, int row_div,
-                                 int & gn_slot) {
+                                 const std::string & tag) {
     const row_map rm = rmap();
     const int C = R.C;
-    double * st1 = gn_stats + (size_t) (gn_slot++) * max_utts * 64;
-    double * st2 = gn_stats + (size_t) (gn_slot++) * max_utts * 64;
-    if (gn_slot > GN_SLOTS) return "internal: GroupNorm slot overflow";
+    const int32_t * scu = d_seg_cu + cur_scu0;
     gemm_params p;
     // GN -> SiLU -> conv1 + bias
-    CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(x, rows, C, rm, row_div, st1, stream, next_dir()));
-    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(x, rows, C, rm, row_div, st1, hp.gn_eps, R.n1w, R.n1b, gn_mr, vc.hi, stream, next_dir())); launches++;
+    CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(x, C, rm, row_div, scu, cur_n_segs, gn_part, stream, next_dir()));
+    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(x, rows, C, rm, row_div, gn_part, scu, hp.gn_eps, R.n1w, R.n1b, gn_mr, vc.hi, stream, next_dir())); launches++;
+    if (taps_on()) tap_f16(tag + "_h1", vc.hi, nullptr, (size_t) rows * C);
     p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = y; p.ld_out = C; p.bias = R.c1b;
     CKG(gemm(R.c1, vc, rows, p));
+    if (taps_on()) tap_f32(tag + "_c1", y, rows, C);
     // GN -> SiLU -> conv2 + bias + residual
-    CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(y, rows, C, rm, row_div, st2, stream, next_dir()));
-    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(y, rows, C, rm, row_div, st2, hp.gn_eps, R.n2w, R.n2b, gn_mr, vc.hi, stream, next_dir())); launches++;
+    CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(y, C, rm, row_div, scu, cur_n_segs, gn_part, stream, next_dir()));
+    CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(y, rows, C, rm, row_div, gn_part, scu, hp.gn_eps, R.n2w, R.n2b, gn_mr, vc.hi, stream, next_dir())); launches++;
+    if (taps_on()) tap_f16(tag + "_h2", vc.hi, nullptr, (size_t) rows * C);
     p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x; p.ld_out = C; p.bias = R.c2b;
     CKG(gemm(R.c2, vc, rows, p));
+    if (taps_on()) tap_f32(tag + "_out", x, rows, C);
     return {};
 }
 
@@ -882,24 +985,20 @@ std::string engine::run_attention(int rows, int D, int n_head, int window, int r
         CKR(CAT_ATTN, (double) rows * 16.0 * D, launch_attention_simt(qkv_hi, qkv_lo, rows, D, n_head, window, rm, row_div, out.hi, out.lo, stream));
         return {};
     }
-    const CUtensorMap * ih = out_map(qkv_hi, 2, rows, 3 * D, (size_t) 3 * D * 2, 64, 64);
-    const CUtensorMap * il = out_map(qkv_lo, 2, rows, 3 * D, (size_t) 3 * D * 2, 64, 64);
-    const CUtensorMap * oh = out_map(out.hi, 2, rows, D, (size_t) D * 2, 64, 16);
-    const CUtensorMap * ol = out_map(out.lo, 2, rows, D, (size_t) D * 2, 64, 16);
-    if (!ih || !il || !oh || !ol) return err;
-    CKR(CAT_ATTN, (double) rows * 16.0 * D, launch_attention_tc(*ih, *il, *oh, *ol, rows, D, n_head, window, bounds, stream, next_dir()));
+    CUtensorMap ih, il, oh, ol;
+    if (!out_map(&ih, qkv_hi, 2, rows, 3 * D, (size_t) 3 * D * 2, 64, 64) || !out_map(&il, qkv_lo, 2, rows, 3 * D, (size_t) 3 * D * 2, 64, 64) ||
+        !out_map(&oh, out.hi, 2, rows, D, (size_t) D * 2, 64, 16) || !out_map(&ol, out.lo, 2, rows, D, (size_t) D * 2, 64, 16)) return err;
+    CKR(CAT_ATTN, (double) rows * 16.0 * D, launch_attention_tc(ih, il, oh, ol, rows, D, n_head, window, bounds, stream, next_dir()));
     return {};
 }
 
 std::string engine::run_chunk(const chunk_info & c) {
-    cur_row0 = c.row0; cur_utt0 = c.utt0; cur_rows1 = c.rows1; cur_n_utts = c.n_utts;
+    cur_row0 = c.row0; cur_utt0 = c.utt0; cur_rows1 = c.rows1; cur_n_utts = c.n_utts; cur_scu0 = c.scu0; cur_n_segs = c.n_segs;
     const row_map rm = rmap();
     const int R1 = c.rows1, R2 = 2 * R1, R6 = 6 * R1, R18 = 18 * R1;
     const int D = hp.prenet_dim, C = hp.dec_dim;
     gemm_params p;
     std::string e;
-    CKG(cudaMemsetAsync(gn_stats, 0, (size_t) GN_SLOTS * max_utts * 64 * sizeof(double), stream));
-    int gn_slot = 0;
 
     // valid key ranges of the banded attention, once per chunk and resolution (all layers reuse them)
     if (!attn_simt) {
@@ -908,27 +1007,27 @@ std::string engine::run_chunk(const chunk_info & c) {
     }
     // 1. token gather
     CKR(CAT_GATHER, (double) (R1) * (4.0 + 8.0 * (D)), launch_gather(w.token_embd, d_codes + c.row0, x768, R1, D, hp.vocab, err_flag, stream));
-    snap_f32("embed", x768, (size_t) R1 * D);
+    if (taps_on()) tap_f32("embed", x768, R1, D);
     // 2. prenet
     for (int i = 0; i < hp.prenet_layers; i++) {
         const prenet_layer_w & l = w.prenet[i];
         CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.an_w, l.an_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream, next_dir()));
         p = qkv_params(rm, D, 1);
         CKG(gemm(l.qkv, vA768, R1, p));
-        if (i == 0) snap_f16("pre0_qkv_rope", qkv_hi, qkv_lo, (size_t) R1 * 3 * D);
+        if (i == 0 && taps_on()) tap_f16("pre0_qkv_rope", qkv_hi, qkv_lo, (size_t) R1 * 3 * D);
         if (!(e = run_attention(R1, D, hp.prenet_heads, hp.prenet_window, 1, vA768, attn_b1)).empty()) return e;
-        if (i == 0) snap_f16("pre0_attn", vA768.hi, vA768.lo, (size_t) R1 * D);
+        if (i == 0 && taps_on()) tap_f16("pre0_attn", vA768.hi, vA768.lo, (size_t) R1 * D);
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
         CKG(gemm(l.wo, vA768, R1, p));
-        if (i == 0) snap_f32("pre0_x_attn", x768, (size_t) R1 * D);
+        if (i == 0 && taps_on()) tap_f32("pre0_x_attn", x768, R1, D);
         CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.fn_w, l.fn_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream, next_dir()));
         p = gemm_params(); p.epi = EPI_SWIGLU; p.out_hi = vFF2048.hi; p.out_lo = vFF2048.lo; p.ld_h = hp.prenet_ff;
         CKG(gemm(l.gu, vA768, R1, p));
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
         CKG(gemm(l.down, vFF2048, R1, p));
-        if (i == 0) snap_f32("pre0_out", x768, (size_t) R1 * D);
+        if (taps_on()) tap_f32("pre" + std::to_string(i) + "_out", x768, R1, D);
     }
-    snap_f32("prenet_x", x768, (size_t) R1 * D);
+    if (taps_on()) tap_f32("prenet_x", x768, R1, D);
     CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, w.pre_norm_w, w.pre_norm_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream, next_dir()));
     // 2b. 768 -> 512 (+bias) written straight as the split operand of the ConvTranspose GEMM
     p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = vA512.hi; p.out_lo = vA512.lo; p.ld_h = C; p.bias = w.pre_out_b;
@@ -936,7 +1035,7 @@ std::string engine::run_chunk(const chunk_info & c) {
     // CTAs still read it -> stage through aFF
     p.out_hi = aFF_hi; p.out_lo = aFF_lo;
     CKG(gemm(w.pre_out, vA768, R1, p));
-    snap_f16("prenet_out", aFF_hi, aFF_lo, (size_t) R1 * C);
+    if (taps_on()) tap_f16("prenet_out", aFF_hi, aFF_lo, (size_t) R1 * C);
     // 3. wave_upsample ConvTranspose1d(k=2, s=2): [R1][2*512] == [R2][512]
     {
         a_view v = vFF1536;   // aFF viewed as [.][512]
@@ -944,11 +1043,11 @@ std::string engine::run_chunk(const chunk_info & c) {
         p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = x512; p.ld_out = 2 * C; p.bias = w.up0_b; p.bias_mod = C;
         CKG(gemm(w.up0, v, R1, p));
     }
-    snap_f32("upsample", x512, (size_t) R2 * C);
+    if (taps_on()) tap_f32("upsample", x512, R2, C);
     // 4. prior resnet blocks
     for (int b = 0; b < hp.resnet_blocks; b++)
-        if (!(e = run_resblock(w.prior[b], x512, y512, vC512, R2, 2, gn_slot)).empty()) return e;
-    snap_f32("prior", x512, (size_t) R2 * C);
+        if (!(e = run_resblock(w.prior[b], x512, y512, vC512, R2, 2, "prior" + std::to_string(b))).empty()) return e;
+    if (taps_on()) tap_f32("prior", x512, R2, C);
     // 5. decoder: 8 AdaLN-Zero layers (conditioning vectors per voice were computed once in run())
     for (int i = 0; i < hp.dec_layers; i++) {
         const dec_layer_w & l = w.dec[i];
@@ -956,6 +1055,7 @@ std::string engine::run_chunk(const chunk_info & c) {
         CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, oa, oa + C, rm, 2, vA512.hi, vA512.lo, nullptr, stream, next_dir()));
         p = qkv_params(rm, C, 2);
         CKG(gemm(l.qkv, vA512, R2, p));
+        if (i == 0 && taps_on()) tap_f16("dec0_qkv_rope", qkv_hi, qkv_lo, (size_t) R2 * 3 * C);
         if (!(e = run_attention(R2, C, hp.dec_heads, hp.dec_window, 2, vA512, attn_b2)).empty()) return e;
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x512; p.ld_out = C;
         p.gate = mod + oa + 2 * C; p.gate_ld = w.cond_rows; p.row_utt = rm.row_utt; p.row_div = 2; p.gate_voice = rm.voice;
@@ -966,43 +1066,45 @@ std::string engine::run_chunk(const chunk_info & c) {
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x512; p.ld_out = C;
         p.gate = mod + of + 2 * C; p.gate_ld = w.cond_rows; p.row_utt = rm.row_utt; p.row_div = 2; p.gate_voice = rm.voice;
         CKG(gemm(l.down, vFF1536, R2, p));
-        if (i == 0) snap_f32("dec0_out", x512, (size_t) R2 * C);
+        if (taps_on()) tap_f32("dec" + std::to_string(i) + "_out", x512, R2, C);
     }
-    snap_f32("decoder_x", x512, (size_t) R2 * C);
+    if (taps_on()) tap_f32("decoder_x", x512, R2, C);
     // 6. final AdaLN (shift, scale only) -> fp32 in place
     {
         const int on = hp.dec_layers * 2 * 3 * C;
         CKR(CAT_LN, (double) (R2) * 8.0 * (C), launch_layernorm(x512, R2, C, hp.norm_eps, nullptr, nullptr, mod, w.cond_rows, on, on + C, rm, 2, nullptr, nullptr, x512, stream, next_dir()));
     }
-    snap_f32("final_norm", x512, (size_t) R2 * C);
+    if (taps_on()) tap_f32("final_norm", x512, R2, C);
     // 7. post resnet blocks
     for (int b = 0; b < hp.resnet_blocks; b++)
-        if (!(e = run_resblock(w.post[b], x512, y512, vC512, R2, 2, gn_slot)).empty()) return e;
-    snap_f32("post", x512, (size_t) R2 * C);
+        if (!(e = run_resblock(w.post[b], x512, y512, vC512, R2, 2, "post" + std::to_string(b))).empty()) return e;
+    if (taps_on()) tap_f32("post", x512, R2, C);
     // 8. upsampler stage 0: ConvT(512->256, k9 s3) + bias + trim + Snake, then resblock
     CKR(CAT_SPLIT, (double) (R2) * 8.0 * (C), launch_split(x512, R2, C, rm, 2, vA512.hi, vA512.lo, stream));
     p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = x256; p.ld_out = 3 * 256; p.bias = w.upT_b[0]; p.bias_mod = 256;
     p.snake_ea = w.snake_ea[0]; p.snake_eb = w.snake_eb[0];
     CKG(gemm(w.upT[0], vA512, R2, p));
-    snap_f32("up0_snake", x256, (size_t) R6 * 256);
-    if (!(e = run_resblock(w.up_res[0], x256, y256, vC256, R6, 6, gn_slot)).empty()) return e;
-    snap_f32("up0", x256, (size_t) R6 * 256);
+    if (taps_on()) tap_f32("up0_snake", x256, R6, 256);
+    if (!(e = run_resblock(w.up_res[0], x256, y256, vC256, R6, 6, "upres0")).empty()) return e;
+    if (taps_on()) tap_f32("up0", x256, R6, 256);
     //    stage 1: ConvT(256->128, k9 s3)
     CKR(CAT_SPLIT, (double) (R6) * 8.0 * (256), launch_split(x256, R6, 256, rm, 6, vFF256.hi, vFF256.lo, stream));
     p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = x128; p.ld_out = 3 * 128; p.bias = w.upT_b[1]; p.bias_mod = 128;
     p.snake_ea = w.snake_ea[1]; p.snake_eb = w.snake_eb[1];
     CKG(gemm(w.upT[1], vFF256, R6, p));
-    if (!(e = run_resblock(w.up_res[1], x128, y128, vC128, R18, 18, gn_slot)).empty()) return e;
-    snap_f32("up1", x128, (size_t) R18 * 128);
+    if (taps_on()) tap_f32("up1_snake", x128, R18, 128);
+    if (!(e = run_resblock(w.up_res[1], x128, y128, vC128, R18, 18, "upres1")).empty()) return e;
+    if (taps_on()) tap_f32("up1", x128, R18, 128);
     // 8b. out_proj 128 -> 512 + bias + Snake -> split operand of the head
     CKR(CAT_SPLIT, (double) (R18) * 8.0 * (128), launch_split(x128, R18, 128, rm, 18, vFF128.hi, vFF128.lo, stream));
     p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = vH512.hi; p.out_lo = vH512.lo; p.ld_h = 512; p.bias = w.out_proj_b;
     p.snake_ea = w.out_snake_ea; p.snake_eb = w.out_snake_eb;
     CKG(gemm(w.out_proj, vFF128, R18, p));
+    if (taps_on()) tap_f16("out_snake", vH512.hi, vH512.lo, (size_t) R18 * 512);
     // 9. head: 512 -> 394, exp/clamp/cos/sin -> interleaved (re, im)
     p = gemm_params(); p.epi = EPI_HEAD; p.out_f32 = spec; p.ld_out = SPEC_LD; p.bias = w.head_b;
     CKG(gemm(w.head, vH512, R18, p));
-    snap_f32_2d("spec", spec, (size_t) R18, 2 * hp.n_freq, SPEC_LD);
+    if (taps_on()) tap_f32("spec", spec, R18, 2 * hp.n_freq, SPEC_LD);
     // ISTFT
     if (!(e = run_istft(c, spec)).empty()) return e;
     return {};
@@ -1012,7 +1114,7 @@ std::string engine::run_istft(const chunk_info & c, const float * spec_dev) {
     istft_params ip;
     ip.spec = spec_dev; ip.spec_ld = SPEC_LD; ip.wave = d_wave;
     ip.start = d_start + c.utt0; ip.len = d_len + c.utt0; ip.out_off = d_out_off + c.utt0;
-    ip.chunk_cu = d_chunk_cu + c.cu0; ip.hann = w.hann;
+    ip.chunk_cu = d_chunk_cu + c.cu0; ip.hann = w.hann; ip.tw = w.istft_tw;
     ip.n_utts = c.n_utts; ip.frames_per_code = hp.frames_per_code; ip.total_chunks = c.istft_blocks;
     double istft_bytes = 0.0;   // 394*4 read + 98*4 written per frame
     for (int u = 0; u < c.n_utts; u++) istft_bytes += (double) lay.len[c.utt0 + u] * hp.frames_per_code * 1968.0;
@@ -1187,7 +1289,7 @@ std::string engine::run_istft_only(const float * spec_host, int n_frames) {
     CK(cudaStreamSynchronize(stream));   // the small host sources above are locals
     istft_params ip;
     ip.spec = spec; ip.spec_ld = SPEC_LD; ip.wave = d_wave; ip.start = d_start; ip.len = d_len; ip.out_off = d_out_off; ip.chunk_cu = d_chunk_cu;
-    ip.hann = w.hann; ip.n_utts = 1; ip.frames_per_code = 1; ip.total_chunks = blocks;
+    ip.hann = w.hann; ip.tw = w.istft_tw; ip.n_utts = 1; ip.frames_per_code = 1; ip.total_chunks = blocks;
     const double istft_bytes = (double) n_frames * 1968.0;
     launches = 0;
     CKR(CAT_ISTFT, istft_bytes, launch_istft(ip, stream));

@@ -27,6 +27,7 @@ struct chunk_info {              // a run of whole utterances that fits the work
     int row0 = 0, rows1 = 0;     // rows (code resolution) in the concatenated device arrays
     int cu0 = 0;                 // offset of this chunk's ISTFT block prefix in d_chunk_cu
     int istft_blocks = 0;
+    int scu0 = 0, n_segs = 0;    // offset of this chunk's GroupNorm segment prefix in d_seg_cu, segments in the chunk
 };
 
 struct out_map_key {
@@ -54,7 +55,6 @@ struct engine {
     bool serpentine = true, dir_flip = false;
     bool next_dir() { if (!serpentine) return false; dir_flip = !dir_flip; return dir_flip; }
     int num_sms = 148;               // multiProcessorCount of the device (tile-width choice of the GEMM dispatch)
-    int gemm_gen = 3;                // 1: one CTA per tile; 2: persistent CTA pairs (cta_group::2); 3: + TMA-store epilogue (default)
     int max_rows1 = 65536 + 4096;    // workspace rows at code resolution (codes + one pad row per utterance), ~8.5 GB
     bool ws_ready = false;
     bool istft_only = false;         // created by mio_istft_ctx_create: no decoder weights, ISTFT workspace only
@@ -69,7 +69,7 @@ struct engine {
     __half *aA_hi = nullptr, *aA_lo = nullptr, *aFF_hi = nullptr, *aFF_lo = nullptr, *c16 = nullptr,
            *h512_hi = nullptr, *h512_lo = nullptr, *qkv_hi = nullptr, *qkv_lo = nullptr;
     bool attn_simt = false;           // MIO_ATTN=simt: CUDA-core validation kernel
-    double * gn_stats = nullptr;      // [GN_SLOTS][max_utts][32][2]
+    double2 * gn_part = nullptr;      // [segments][32] (sum, sum of squares) of the GroupNorm being computed
     float * voice_silu = nullptr;     // [max_voices][128] silu(voice embedding), input of cond_kernel
     float2 * gn_mr = nullptr;         // [max_utts][32] (mean, rstd) of the GroupNorm being applied
     int2 * attn_b1 = nullptr;         // [max_rows1]   valid key range per prenet row (attn_bounds_kernel)
@@ -84,11 +84,11 @@ struct engine {
     // ---- current batch (device copies of the layout)
     batch_layout lay;
     std::vector<chunk_info> chunks;
-    int cur_row0 = 0, cur_utt0 = 0, cur_rows1 = 0, cur_n_utts = 0;
-    size_t cap_rows = 0, cap_rows_ru = 0, cap_utts = 0, cap_ccu = 0, cap_vt = 0;
+    int cur_row0 = 0, cur_utt0 = 0, cur_rows1 = 0, cur_n_utts = 0, cur_scu0 = 0, cur_n_segs = 0;
+    size_t cap_rows = 0, cap_rows_ru = 0, cap_utts = 0, cap_ccu = 0, cap_scu = 0, cap_vt = 0;
     size_t h2d_bytes = 0;
     int32_t *d_codes = nullptr, *d_row_utt = nullptr, *d_start = nullptr, *d_len = nullptr, *d_voice = nullptr,
-            *d_chunk_cu = nullptr;
+            *d_chunk_cu = nullptr, *d_seg_cu = nullptr;
     int64_t * d_out_off = nullptr;
     float * d_voice_table = nullptr;
     int n_voices = 0;
@@ -107,6 +107,7 @@ struct engine {
     std::string load(const std::string & gguf_path, int device);
     std::string init_istft_only(int device);
     std::string ensure_workspace();
+    std::string ensure_rope(int max_pos);                 // grows the RoPE tables to cover positions [0, max_pos)
     // layout + H2D. codes_concat/cu_seqlens in the caller's (unpadded) indexing.
     std::string upload(const int32_t * codes, const int32_t * cu, int n_utts, const float * voice_table, int n_voices,
                        const int32_t * voice_ids, int chunk_rows_limit = 0);
@@ -131,13 +132,15 @@ struct engine {
     std::string fetch_spec(int utt, float * out, int64_t cap);
     row_map rmap() const;
     std::string run_chunk(const chunk_info & c);
-    std::string run_resblock(const resblock_w & R, float * x, float * y, const a_view & vc, int rows, int row_div, int & gn_slot);
+    std::string run_resblock(const resblock_w & R, float * x, float * y, const a_view & vc, int rows, int row_div,
+                             const std::string & tag);
     std::string run_istft(const chunk_info & c, const float * spec_dev);
     std::string view512_ff(a_view & v);
     cudaError_t gemm(const gemm_weight & W, const a_view & A, int M, gemm_params p);
+    std::string debug_gemm(int M, int N, int K, const float * A, const float * B, int npass, float * out);
     std::map<out_map_key, CUtensorMap> out_maps;          // TMA maps of GEMM outputs, keyed by (buffer, shape)
     // box {box_c, box_r}; swizzle = box_c * esize (128-byte or 64-byte box rows)
-    const CUtensorMap * out_map(const void * base, int esize, int rows, int cols, size_t ld_bytes, int box_c = 32, int box_r = 32);
+    bool out_map(CUtensorMap * out, const void * base, int esize, int rows, int cols, size_t ld_bytes, int box_c = 32, int box_r = 32);
     gemm_params qkv_params(const row_map & rm, int D, int row_div);
     std::string run_attention(int rows, int D, int n_head, int window, int row_div, const a_view & out, const int2 * bounds);
     // profiling
@@ -148,9 +151,15 @@ struct engine {
     void prof_begin(int cat, double flops, double bytes);
     void prof_end();
     void prof_collect();
-    void snap_f32(const char * name, const float * d, size_t n);
-    void snap_f32_2d(const char * name, const float * d, size_t rows, size_t cols, size_t ld);
-    void snap_f16(const char * name, const __half * hi, const __half * lo, size_t n);
+    // named taps of the kernel sequence: snapshot (debug_snapshots) and teacher-forced overrides (mio_debug_write)
+    std::map<std::string, std::vector<float>> overrides;
+    std::string snap_filter;          // option "debug_snapshot_filter": ",name1,name2," — empty = every tap
+    bool taps_on() const { return debug_snap || !overrides.empty(); }
+    bool snap_wanted(const std::string & name) const {
+        return debug_snap && (snap_filter.empty() || snap_filter.find("," + name + ",") != std::string::npos);
+    }
+    void tap_f32(const std::string & name, float * d, size_t rows, size_t cols, size_t ld = 0);
+    void tap_f16(const std::string & name, __half * hi, __half * lo, size_t n);
 };
 
 }  // namespace mio

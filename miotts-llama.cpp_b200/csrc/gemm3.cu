@@ -1,9 +1,20 @@
-// Generation-3 tap-GEMM: the persistent CTA-pair tcgen05 main loop of gemm.cu (generation 2) with a rebuilt epilogue.
+// Dense contractions of the decoder (linear layers, conv1d k=3 and ConvTranspose1d as tap-GEMMs) on the sm_100a
+// tensor cores: TMA (cp.async.bulk.tensor, SWIZZLE_128B) -> shared memory ring -> tcgen05.mma.cta_group::2.kind::f16
+// (FP32 accumulators in TMEM, double buffered) -> tcgen05.ld -> fused epilogue -> TMA store.
 //
-// Why: the layers of this decoder have short K (128..2048), so a 256 x 256 tile spends only ~6 us in MMAs and the
-// epilogue sets the tile time (profiles/r1b_summary.md: tensor pipe 31-74 % busy, tracking K).  Generation 2 used 4
-// epilogue warps with per-thread row-strided 16-byte global stores and an exposed read-modify-write for residuals.
-// Here:
+// Numerics.  The reference computes these layers in FP32 (ggml_mul_mat on F32 weights, src/miocodec.cpp:205-209)
+// except conv1d, whose operands it rounds to FP16 itself (ggml.c:4416, ops.cpp:6232-6256).  A single 16-bit pass
+// costs 48 dB SNR, so FP32-class layers run as split precision: a = a_hi + a_lo, b = b_hi + b_lo
+// (fp16 pairs, ~22 significant bits) and D = a_hi*b_hi + a_hi*b_lo + a_lo*b_hi with FP32 accumulation (npass = 3);
+// conv1d layers run one exact-in-kind pass (npass = 1).
+//
+// Tap-GEMM: D[m][n] = sum_{tap} sum_k A[m + tap - (taps==3)][k] * B[n][tap*K + k].  Row shifts are plain TMA
+// coordinates; out-of-range rows are zero-filled by TMA and utterances are separated by zero rows, which is the
+// zero padding of conv1d / the missing taps of ConvTranspose1d.
+//
+// Layout of the kernel: one cluster of 2 CTAs per SM pair, static round-robin over 256 x BN output tiles; each CTA
+// loads its 128 rows of A and HALF of the B tile; the leader CTA issues the MMAs (M = 256).  The layers have short K
+// (128..2048), so a 256 x 256 tile spends only ~6 us in MMAs and the epilogue sets the tile time, hence:
 //   * 8 epilogue warps per CTA (two per TMEM lane quadrant, each owning half of the tile's columns)
 //   * each warp moves 32 rows x 32 accumulator columns at a time: tcgen05.ld -> registers -> fused math -> swizzled
 //     shared-memory staging tile (4 KB per warp, bank-conflict free) -> one TMA store (full 128-byte lines, clipped
@@ -381,52 +392,65 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     }
 }
 
-static int g3_num_sms = 0;
-
 template <int BN, int NPASS, int EPI>
 static cudaError_t launch_tc3_inst(const gemm_params & p, const CUtensorMap & a_hi, const CUtensorMap & a_lo,
                                    const CUtensorMap & b_hi, const CUtensorMap & b_lo, const CUtensorMap & o0,
-                                   const CUtensorMap & o1, cudaStream_t st) {
+                                   const CUtensorMap & o1, int num_sms, cudaStream_t st) {
     using cfg = gemm3_cfg<BN, NPASS>;
     static_assert(cfg::SMEM_BYTES <= 232448, "shared memory budget");
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc3_kernel<BN, NPASS, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             cfg::SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        attr_done = true;
-    }
-    if (g3_num_sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g3_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    }
     const int tiles = ((p.N + BN - 1) / BN) * ((p.M + 255) / 256);
-    int clusters = g3_num_sms / 2;
+    int clusters = num_sms / 2;
     if (tiles < clusters) clusters = tiles;
     gemm_tc3_kernel<BN, NPASS, EPI><<<2 * clusters, G3_THREADS, cfg::SMEM_BYTES, st>>>(a_hi, a_lo, b_hi, b_lo, o0, o1, p);
     return cudaGetLastError();
 }
 
+template <int BN, int NPASS, int EPI>
+static cudaError_t set_attr_inst() {
+    return cudaFuncSetAttribute(gemm_tc3_kernel<BN, NPASS, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                gemm3_cfg<BN, NPASS>::SMEM_BYTES);
+}
+template <int BN>
+static cudaError_t set_attr_bn() {
+    cudaError_t e;
+    if ((e = set_attr_inst<BN, 1, EPI_STORE>()) != cudaSuccess) return e;
+    if ((e = set_attr_inst<BN, 1, EPI_RESID>()) != cudaSuccess) return e;
+    if ((e = set_attr_inst<BN, 3, EPI_STORE>()) != cudaSuccess) return e;
+    if ((e = set_attr_inst<BN, 3, EPI_RESID>()) != cudaSuccess) return e;
+    if constexpr (BN >= 128) { if ((e = set_attr_inst<BN, 3, EPI_SWIGLU>()) != cudaSuccess) return e; }
+    if ((e = set_attr_inst<BN, 3, EPI_SPLIT>()) != cudaSuccess) return e;
+    if ((e = set_attr_inst<BN, 3, EPI_SNAKE>()) != cudaSuccess) return e;
+    if ((e = set_attr_inst<BN, 3, EPI_HEAD>()) != cudaSuccess) return e;
+    return set_attr_inst<BN, 3, EPI_QKV>();
+}
+// The opt-in to > 48 KB of dynamic shared memory is stored per device, so every context sets it for ITS device
+// (a process-wide "done" flag would leave the second GPU of a multi-device process without it).
+cudaError_t gemm_tc3_init_device() {
+    cudaError_t e;
+    if ((e = set_attr_bn<256>()) != cudaSuccess) return e;
+    if ((e = set_attr_bn<128>()) != cudaSuccess) return e;
+    return set_attr_bn<64>();
+}
+
 template <int BN, int NPASS>
 static cudaError_t launch_tc3_epi(const gemm_params & p, const CUtensorMap & a_hi, const CUtensorMap & a_lo,
                                   const CUtensorMap & b_hi, const CUtensorMap & b_lo, const CUtensorMap & o0,
-                                  const CUtensorMap & o1, cudaStream_t st) {
+                                  const CUtensorMap & o1, int num_sms, cudaStream_t st) {
     switch (p.epi) {
-        case EPI_STORE: return launch_tc3_inst<BN, NPASS, EPI_STORE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
-        case EPI_RESID: return launch_tc3_inst<BN, NPASS, EPI_RESID>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+        case EPI_STORE: return launch_tc3_inst<BN, NPASS, EPI_STORE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+        case EPI_RESID: return launch_tc3_inst<BN, NPASS, EPI_RESID>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
         default: break;
     }
     if constexpr (NPASS == 3) {
         switch (p.epi) {
             case EPI_SWIGLU:
                 if (p.N % 64 != 0) return cudaErrorInvalidValue;
-                if constexpr (BN >= 128) return launch_tc3_inst<BN, 3, EPI_SWIGLU>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+                if constexpr (BN >= 128) return launch_tc3_inst<BN, 3, EPI_SWIGLU>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
                 else return cudaErrorInvalidValue;   // a (gate, up) pair row needs 64 accumulator columns per warp
-            case EPI_SPLIT: return launch_tc3_inst<BN, 3, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
-            case EPI_SNAKE: return launch_tc3_inst<BN, 3, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
-            case EPI_HEAD: return launch_tc3_inst<BN, 3, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
-            case EPI_QKV: return launch_tc3_inst<BN, 3, EPI_QKV>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, st);
+            case EPI_SPLIT: return launch_tc3_inst<BN, 3, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+            case EPI_SNAKE: return launch_tc3_inst<BN, 3, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+            case EPI_HEAD: return launch_tc3_inst<BN, 3, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+            case EPI_QKV: return launch_tc3_inst<BN, 3, EPI_QKV>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
             default: break;
         }
     }
@@ -435,20 +459,20 @@ static cudaError_t launch_tc3_epi(const gemm_params & p, const CUtensorMap & a_h
 
 cudaError_t launch_gemm_tc3(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
                             const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, const CUtensorMap & tmO0,
-                            const CUtensorMap & tmO1, int bn, cudaStream_t st) {
+                            const CUtensorMap & tmO1, int bn, int num_sms, cudaStream_t st) {
     if (p.M <= 0) return cudaSuccess;
     if (p.K % G3_BK != 0 || (p.taps != 1 && p.taps != 3)) return cudaErrorInvalidValue;
     if (bn == 256) {
-        if (p.npass == 3) return launch_tc3_epi<256, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
-        return launch_tc3_epi<256, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
+        if (p.npass == 3) return launch_tc3_epi<256, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, num_sms, st);
+        return launch_tc3_epi<256, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, num_sms, st);
     }
     if (bn == 128) {
-        if (p.npass == 3) return launch_tc3_epi<128, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
-        return launch_tc3_epi<128, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
+        if (p.npass == 3) return launch_tc3_epi<128, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, num_sms, st);
+        return launch_tc3_epi<128, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, num_sms, st);
     }
     if (bn == 64) {   // latency mode: small M, more (narrower) tiles
-        if (p.npass == 3) return launch_tc3_epi<64, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
-        return launch_tc3_epi<64, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, st);
+        if (p.npass == 3) return launch_tc3_epi<64, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, num_sms, st);
+        return launch_tc3_epi<64, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, num_sms, st);
     }
     return cudaErrorInvalidValue;
 }

@@ -137,35 +137,26 @@ __global__ void __launch_bounds__(IST_THREADS, 2) istft_kernel(istft_params p, c
     }
 }
 
-static float * g_tw = nullptr;   // device: tw392 (392 floats) followed by tw196 (392 floats)
-static int g_tw_dev = -1;
-
-static cudaError_t ensure_tables() {
-    int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return e;
-    if (g_tw && g_tw_dev == dev) return cudaSuccess;
-    float h[4 * 196];
+// twiddles of the two DFT-14 passes: tw392 (196 complex) followed by tw196 (196 complex); built by the engine once per
+// context (engine::load / init_istft_only) so that contexts on different devices never share device pointers
+void istft_twiddles(float * h /*[784]*/) {
     for (int k = 0; k < 196; k++) {
         h[2 * k] = (float) cos(2.0 * M_PI * k / 392.0);
         h[2 * k + 1] = (float) sin(2.0 * M_PI * k / 392.0);
         h[392 + 2 * k] = (float) cos(2.0 * M_PI * k / 196.0);
         h[392 + 2 * k + 1] = (float) sin(2.0 * M_PI * k / 196.0);
     }
-    e = cudaMalloc(&g_tw, sizeof(h));
-    if (e != cudaSuccess) return e;
-    e = cudaMemcpy(g_tw, h, sizeof(h), cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) return e;
-    g_tw_dev = dev;
+}
+
+cudaError_t istft_init_device() {
     return cudaFuncSetAttribute(istft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) IST_SMEM);
 }
 
 cudaError_t launch_istft(const istft_params & p, cudaStream_t st) {
     if (p.total_chunks <= 0) return cudaSuccess;
     if (p.spec_ld % 4 != 0 || p.spec_ld < 2 * IST_NFREQ) return cudaErrorInvalidValue;   // 16-byte rows for the bulk copies
-    cudaError_t e = ensure_tables();
-    if (e != cudaSuccess) return e;
-    istft_kernel<<<p.total_chunks, IST_THREADS, IST_SMEM, st>>>(p, g_tw, g_tw + 392);
+    if (!p.tw) return cudaErrorInvalidValue;
+    istft_kernel<<<p.total_chunks, IST_THREADS, IST_SMEM, st>>>(p, p.tw, p.tw + 392);
     return cudaGetLastError();
 }
 

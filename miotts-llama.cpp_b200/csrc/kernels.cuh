@@ -46,20 +46,18 @@ struct gemm_params {
     const __half * b_hi = nullptr; const __half * b_lo = nullptr;
 };
 
-// tcgen05 path. tmA_* : 2-D maps over [a_rows][K] fp16, box {64, 128}; tmB_*: over [N][taps*K], box {64, bn}.
-cudaError_t launch_gemm_tc(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
-                           const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, int bn, cudaStream_t st);
-// generation 2: persistent CTA-pair kernel (cta_group::2, 256 x bn tiles). tmB_*: box {64, bn/2}
-cudaError_t launch_gemm_tc2(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
-                            const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, int bn, cudaStream_t st);
-// generation 3 (default): generation 2's main loop + 8 epilogue warps that stage results in swizzled shared memory and
-// write them with TMA stores (reduce-add for EPI_RESID).  tmO0: fp32 output or fp16 hi, tmO1: fp16 lo; box {32, 32},
-// SWIZZLE_128B (fp32) / SWIZZLE_64B (fp16), row extent == M so the TMA unit clips the last tile.
+// tcgen05 path (gemm3.cu): persistent CTA-pair kernel (cta_group::2, 256 x bn tiles, double-buffered TMEM accumulators),
+// 8 epilogue warps that stage results in swizzled shared memory and write them with TMA stores (reduce-add for
+// EPI_RESID).  tmA_*: 2-D maps over [a_rows][K] fp16, box {64, 128}; tmB_*: over [N][taps*K], box {64, bn/2};
+// tmO0: fp32 output or fp16 hi, tmO1: fp16 lo; box {32, 32}, SWIZZLE_128B (fp32) / SWIZZLE_64B (fp16), row extent == M
+// so the TMA unit clips the last tile.  num_sms: multiProcessorCount of the device the stream belongs to.
 cudaError_t launch_gemm_tc3(const gemm_params & p, const CUtensorMap & tmA_hi, const CUtensorMap & tmA_lo,
                             const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, const CUtensorMap & tmO0,
-                            const CUtensorMap & tmO1, int bn, cudaStream_t st);
+                            const CUtensorMap & tmO1, int bn, int num_sms, cudaStream_t st);
+// CUDA-core validation kernel (gemm_simt.cu): fp32 FMAs on the same operands, libdevice transcendentals
 cudaError_t launch_gemm_simt(const gemm_params & p, cudaStream_t st);
-cudaError_t gemm_tc_init();   // sets the dynamic shared memory attributes once
+// > 48 KB dynamic shared memory is a per-DEVICE function attribute: every context calls these once for its device
+cudaError_t gemm_tc3_init_device();
 
 // ------------------------------------------------------------------------------------------ elementwise
 struct row_map {                 // device pointers describing the padded row space of the current batch
@@ -87,16 +85,20 @@ cudaError_t launch_attention_tc(const CUtensorMap & tm_in_hi, const CUtensorMap 
                                 cudaStream_t st, bool rev = false);
 cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, int rows, int D, int n_head, int window,
                                   const row_map & rm, int row_div, __half * out_hi, __half * out_lo, cudaStream_t st);
-cudaError_t attention_init();
+cudaError_t attention_init();      // per device (dynamic shared memory attributes), called by every context
 cudaError_t attention_tc_init();
-// GroupNorm statistics: stats[utt][32][2] (sum, sum of squares; double), rows at resolution row_div
-cudaError_t launch_gn_stats(const float * x, int rows, int C, const row_map & rm, int row_div, double * stats,
-                            cudaStream_t st, bool rev = false);
+cudaError_t istft_init_device();   // per device
+// GroupNorm statistics, deterministic two-stage reduction: part[segment][32] = (sum, sum of squares) of one segment of
+// GN_SEG_CODES codes of one utterance; seg_cu[n_utts+1] = prefix of the per-utterance segment counts
+constexpr int GN_SEG_CODES = 16;        // codes per statistics segment (counted from the utterance start)
+constexpr int ROW_ALIGN = 16;           // utterances start on multiples of 16 rows (code resolution), see engine::upload
+cudaError_t launch_gn_stats(const float * x, int C, const row_map & rm, int row_div, const int32_t * seg_cu, int total_segs,
+                            double2 * part, cudaStream_t st, bool rev = false);
 // y = fp16( silu( (x-mean)*rstd*w + b ) ), zeros on pad rows
-// (two launches: per-(utterance, group) mean / rstd into mr_scratch[n_utts*32], then the per-element pass)
-cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double * stats,
-                                 float eps, const float * w, const float * b, float2 * mr_scratch, __half * out, cudaStream_t st,
-                                 bool rev = false);
+// (two launches: segments -> per-(utterance, group) mean / rstd into mr_scratch[n_utts*32], then the per-element pass)
+cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double2 * part,
+                                 const int32_t * seg_cu, float eps, const float * w, const float * b, float2 * mr_scratch,
+                                 __half * out, cudaStream_t st, bool rev = false);
 cudaError_t launch_split(const float * x, int rows, int C, const row_map & rm, int row_div, __half * hi, __half * lo,
                          cudaStream_t st);
 // mod[voice][cond_rows] = W[cond_rows][128] * silu(emb[voice]) + b
@@ -113,11 +115,13 @@ struct istft_params {
     const int64_t * out_off;     // [n_utts] sample offset in wave
     const int32_t * chunk_cu;    // [n_utts+1] prefix sum of per-utterance chunk counts
     const float * hann;          // [392]
+    const float * tw;            // [784] twiddles (istft_twiddles), device
     int n_utts;
     int frames_per_code;         // 18
     int total_chunks;
 };
 constexpr int ISTFT_SEG_PER_BLOCK = 44;   // output hops (98 samples) per block; +4 halo frames
+void istft_twiddles(float * host784);
 cudaError_t launch_istft(const istft_params & p, cudaStream_t st);
 // per-utterance peak normalisation 0.95/max|s| (src/test-to-speech.cpp:289-300)
 cudaError_t launch_peak_normalize(float * wave, const int32_t * len, const int64_t * out_off, int n_utts,

@@ -34,9 +34,7 @@ struct gemm_weight {
     float out_scale = 1.f;            // epilogue multiplier (inverse of the power-of-two weight pre-scale)
     __half * hi = nullptr;
     __half * lo = nullptr;
-    CUtensorMap tm_hi, tm_lo;         // box {64, box_n}       (generation-1 kernel, one CTA per 128 x box_n tile)
-    int box_n = 0;
-    CUtensorMap tm2_hi, tm2_lo;       // box {64, bn2 / 2}     (generation-2 kernel, CTA pair per 256 x bn2 tile)
+    CUtensorMap tm2_hi, tm2_lo;       // box {64, bn2 / 2}     (CTA pair per 256 x bn2 tile: each CTA loads half of B)
     int bn2 = 0;
     // narrower tiles for small M (a single short utterance has too few 256 x bn2 tiles to fill 74 CTA pairs):
     // box {64, 64} and {64, 32} for 256 x 128 and 256 x 64 tiles
@@ -75,6 +73,7 @@ struct weights {
     float * rope_t = nullptr;         // the same table position-minor: [2][8][rope_max_pos][4] (generation-3 QKV epilogue)
     int rope_max_pos = 0;
     float * hann = nullptr;                       // [n_fft]
+    float * istft_tw = nullptr;                   // [784] ISTFT twiddles (istft_twiddles)
 };
 
 // Padded row space (DESIGN.md "row space"): utterance u owns rows [start[u], start[u]+len[u]) at code

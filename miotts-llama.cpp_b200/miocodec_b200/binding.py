@@ -28,6 +28,7 @@ EXPORTS = [
     "mio_stream_stats", "mio_debug_read", "mio_last_error", "mio_version", "mio_host_alloc", "mio_host_free",
     "mio_profile_enable", "mio_profile_categories", "mio_profile_name", "mio_profile_read", "mio_batch_h2d_bytes",
     "mio_ctx_stream_seconds", "mio_parse_speech_tokens", "mio_decode_pcm16_batch", "mio_batch_fetch_pcm16", "mio_wav_header", "mio_wav_write_pcm16",
+    "mio_debug_write", "mio_debug_clear", "mio_debug_gemm",
 ]
 
 
@@ -109,6 +110,9 @@ def lib() -> C.CDLL:
     L.mio_wav_write_pcm16.argtypes = [C.c_char_p, vp, i64, C.c_int]
     L.mio_debug_read.argtypes = [vp, C.c_char_p, f32p, i64]
     L.mio_debug_read.restype = i64
+    L.mio_debug_write.argtypes = [vp, C.c_char_p, f32p, i64]
+    L.mio_debug_clear.argtypes = [vp]
+    L.mio_debug_gemm.argtypes = [vp, C.c_int, C.c_int, C.c_int, f32p, f32p, C.c_int, f32p]
     _lib = L
     return L
 
@@ -296,6 +300,24 @@ class MioCodec:
         _check(n)
         out = np.empty(n, dtype=np.float32)
         _check(lib().mio_debug_read(self._h, name.encode(), out.ctypes.data, out.size))
+        return out
+
+    def debug_write(self, name: str, data):
+        """Teacher forcing: replace the leading floats of the named tap on the next decodes (mio_debug_write)."""
+        d = _f32(data).reshape(-1)
+        _check(lib().mio_debug_write(self._h, name.encode(), d.ctypes.data, d.size))
+
+    def debug_clear(self):
+        _check(lib().mio_debug_clear(self._h))
+
+    def debug_gemm(self, A, B, npass: int = 3) -> np.ndarray:
+        """out[M][N] = A[M][K] @ B[N][K].T through the product tcgen05 kernel (mio_debug_gemm)."""
+        A, B = _f32(A), _f32(B)
+        M, K = A.shape
+        N = B.shape[0]
+        assert B.shape[1] == K
+        out = np.empty((M, N), dtype=np.float32)
+        _check(lib().mio_debug_gemm(self._h, M, N, K, A.ctypes.data, B.ctypes.data, npass, out.ctypes.data))
         return out
 
     # ---- streaming -------------------------------------------------------------------------------

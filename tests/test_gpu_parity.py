@@ -36,7 +36,7 @@ def test_wave_and_spec_match_reference_golden(codec, weights, case):
     assert wave.shape == g["wave"].shape == (1764 * len(codes),)
     fused = codec.decode_wave(codes, emb)                             # decode_codes_to_audio
     assert fused.shape == wave.shape
-    assert snr_db(fused, wave) > 55.0                                 # same kernels, only GN atomics order differs
+    assert np.array_equal(fused, wave)                                # same kernels, deterministic: same bits
     hp, W = weights
     floor = snr_db(port.istft(port.decode(W, hp, codes, emb)), g["wave"])
     s = snr_db(wave, g["wave"])
@@ -72,7 +72,7 @@ def test_istft_is_linear_at_full_size(codec):
     assert d.min() >= 98 * 6000 - 147 and d.max() < 98 * 6000 + 245
 
 
-@pytest.mark.parametrize("mode", ["tc3", "tc2", "tc1", "simt"])
+@pytest.mark.parametrize("mode", ["tc3", "simt"])
 def test_stages_before_first_conv_are_fp32_accurate(assets, weights, mode):
     from miocodec_b200 import binding, synth
     from oracle import port
@@ -83,7 +83,7 @@ def test_stages_before_first_conv_are_fp32_accurate(assets, weights, mode):
     c.set_option("debug_snapshots", "1")
     c.decode_wave(codes, emb)
     T = len(codes)
-    lim = {"tc3": 90.0, "tc2": 90.0, "tc1": 90.0, "simt": 105.0}[mode]
+    lim = {"tc3": 90.0, "simt": 105.0}[mode]
     for name, r in [("embed", 1), ("pre0_qkv_rope", 1), ("pre0_attn", 1), ("pre0_out", 1), ("prenet_out", 1), ("upsample", 2)]:
         got = c.debug_read(name).reshape(-1, inter[name].shape[1])[: T * r]
         s = snr_db(got, inter[name])
@@ -111,14 +111,14 @@ def test_batch_ragged_equals_single(codec):
         single = codec.decode_wave(codes[cu[b]:cu[b + 1]], vt[vids[b]])
         got = out[1764 * cu[b]: 1764 * cu[b + 1]]
         assert got.shape == single.shape
-        assert snr_db(got, single) > 55.0, (b, n, snr_db(got, single))
+        assert np.array_equal(got, single), (b, n, snr_db(got, single))   # batch-invariant like the reference
     # permutation invariance: utterances are independent
     perm = [3, 0, 6, 2, 5, 1, 4]
     cu2 = np.concatenate([[0], np.cumsum([lens[p] for p in perm])]).astype(np.int32)
     codes2 = np.concatenate([codes[cu[p]:cu[p + 1]] for p in perm])
     out2 = codec.decode_wave_batch(codes2, cu2, vt, vids[perm])
     for j, p in enumerate(perm):
-        assert snr_db(out2[1764 * cu2[j]: 1764 * cu2[j + 1]], out[1764 * cu[p]: 1764 * cu[p + 1]]) > 55.0
+        assert np.array_equal(out2[1764 * cu2[j]: 1764 * cu2[j + 1]], out[1764 * cu[p]: 1764 * cu[p + 1]])
 
 
 def test_multi_chunk_batches(assets, codec):
@@ -132,7 +132,7 @@ def test_multi_chunk_batches(assets, codec):
     vids = np.array([0, 1, 0, 1, 0, 1], dtype=np.int32)
     a = small.decode_wave_batch(codes, cu, vt, vids)
     b = codec.decode_wave_batch(codes, cu, vt, vids)
-    assert snr_db(a, b) > 55.0
+    assert np.array_equal(a, b)                                       # chunking never changes an utterance's bits
     with pytest.raises(binding.MioError) as ei:
         small.decode_wave(synth.synth_codes(400, 1), vt[0])          # one utterance larger than the workspace
     assert ei.value.code == binding.MIO_ERR_ARG
@@ -261,7 +261,7 @@ def test_c3_and_c5_full_batches_sampled_against_live_reference(assets, codec):
         for b in picks:
             got = wave[1764 * int(cu[b]): 1764 * int(cu[b + 1])]
             alone = codec.decode_wave(codes[cu[b]:cu[b + 1]], vt[vids[b]])
-            assert got.shape == alone.shape and snr_db(got, alone) > 55.0, (name, b)
+            assert got.shape == alone.shape and np.array_equal(got, alone), (name, b)
             if R is not None:
                 w_ref = R.decode_wave(codes[cu[b]:cu[b + 1]], vt[vids[b]])
                 s = snr_db(got, w_ref)
@@ -289,8 +289,4 @@ def test_delivery_pipeline_splits_do_not_change_the_result(codec):
     finally:
         codec.set_option("fetch_tail_percent", "-1")
     for pct in (12, 30, -1):
-        # not bit-identical: the chunk size regroups the fp32 partial sums of the GroupNorm statistics
-        for b in (0, 40, 79):
-            a0 = outs[0][1764 * cu[b]: 1764 * cu[b + 1]]
-            a1 = outs[pct][1764 * cu[b]: 1764 * cu[b + 1]]
-            assert snr_db(a1, a0) > 55.0, (pct, b, snr_db(a1, a0))
+        assert np.array_equal(outs[pct], outs[0]), pct               # bit-identical under any split
