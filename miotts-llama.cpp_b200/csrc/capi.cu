@@ -94,6 +94,13 @@ int mio_ctx_set_option(mio_ctx * c, const char * key, const char * value) {
         else return fail(MIO_ERR_ARG, "bad argument: gemm must be tc or simt");
         return MIO_OK;
     }
+    if (!strcmp(key, "chunk_acc")) {
+        if (!strcmp(value, "off")) c->E.chunk_mode = 0;
+        else if (!strcmp(value, "prenet")) c->E.chunk_mode = 1;
+        else if (!strcmp(value, "all")) c->E.chunk_mode = 2;
+        else return fail(MIO_ERR_ARG, "bad argument: chunk_acc must be off, prenet or all");
+        return MIO_OK;
+    }
     if (!strcmp(key, "max_chunk_codes")) {
         if (c->E.ws_ready) return fail(MIO_ERR_STATE, "max_chunk_codes must be set before the first decode");
         const long v = strtol(value, nullptr, 10);

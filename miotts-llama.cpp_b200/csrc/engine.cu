@@ -485,6 +485,8 @@ std::string engine::load(const std::string & path, int dev) {
     CK(istft_init_device());
     { const char * ev = getenv("MIO_ATTN"); attn_simt = ev && !strcmp(ev, "simt"); }
     { const char * ev = getenv("MIO_SERPENTINE"); if (ev && ev[0] == '0') serpentine = false; }
+    { const char * ev = getenv("MIO_CHUNK_ACC"); if (ev) chunk_mode = !strcmp(ev, "off") ? 0 : (!strcmp(ev, "all") ? 2 : 1); }
+    { const char * ev = getenv("MIO_CHUNK_KB"); if (ev && atoi(ev) >= 1 && atoi(ev) <= 64) chunk_kb = atoi(ev); }
     CK(cudaDeviceSynchronize());
     return {};
 }
@@ -815,6 +817,8 @@ void engine::tap_f16(const std::string & name, __half * hi, __half * lo, size_t 
 cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_params p) {
     p.M = M; p.N = W.N; p.K = W.K; p.taps = W.taps; p.npass = W.npass; p.out_scale = W.out_scale;
     p.reverse = next_dir() ? 1 : 0;
+    // chunked accumulation (gemm3.cu): callers request it (p.chunk = 1) for the layers in front of the first conv1d
+    p.chunk = (W.npass == 3 && (chunk_mode == 2 || (chunk_mode == 1 && p.chunk > 0))) ? chunk_kb : 0;
     { static const int order = getenv("MIO_MMA_ORDER") ? atoi(getenv("MIO_MMA_ORDER")) : 2; p.mma_order = order; }
     if (p.bias_mod <= 1) p.bias_mod = W.N;
     p.a_hi = A.hi; p.a_lo = A.lo; p.lda = A.K; p.a_rows = A.rows;
@@ -882,7 +886,8 @@ std::string engine::debug_gemm(int M, int N, int K, const float * A, const float
         out_maps.clear();                                // the freed buffers' addresses may be reused
     };
     const size_t na = (size_t) M * K;
-    if (!(e = dev_alloc(&dA, na)).empty() || !(e = dev_alloc(&dO, (size_t) M * N)).empty() || !(e = dev_alloc(&ah, na)).empty() ||
+    const int ldo = (N + 3) / 4 * 4;                     // TMA store pitch: a multiple of 16 bytes
+    if (!(e = dev_alloc(&dA, na)).empty() || !(e = dev_alloc(&dO, (size_t) M * ldo)).empty() || !(e = dev_alloc(&ah, na)).empty() ||
         !(e = dev_alloc(&al, na)).empty()) { cleanup(); return e; }
     cudaMemcpy(dA, A, na * sizeof(float), cudaMemcpyHostToDevice);
     split_weights_kernel<<<296, 256>>>(dA, na, 1.0f, ah, npass == 3 ? al : nullptr);
@@ -890,10 +895,10 @@ std::string engine::debug_gemm(int M, int N, int K, const float * A, const float
     a_view v;
     if (!(e = make_view(v, ah, npass == 3 ? al : nullptr, M, K)).empty()) { cleanup(); return e; }
     gemm_params p;
-    p.epi = EPI_STORE; p.out_f32 = dO; p.ld_out = N;
+    p.epi = EPI_STORE; p.out_f32 = dO; p.ld_out = ldo; p.chunk = 1;     // chunked unless option chunk_acc = off
     cudaError_t ce = gemm(W, v, M, p);
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(stream);
-    if (ce == cudaSuccess) ce = cudaMemcpy(out, dO, (size_t) M * N * sizeof(float), cudaMemcpyDeviceToHost);
+    if (ce == cudaSuccess) ce = cudaMemcpy2D(out, (size_t) N * sizeof(float), dO, (size_t) ldo * sizeof(float), (size_t) N * sizeof(float), M, cudaMemcpyDeviceToHost);
     cleanup();
     if (ce != cudaSuccess) return std::string("debug_gemm: ") + cudaGetErrorString(ce);
     return {};
@@ -1013,17 +1018,21 @@ std::string engine::run_chunk(const chunk_info & c) {
         const prenet_layer_w & l = w.prenet[i];
         CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.an_w, l.an_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream, next_dir()));
         p = qkv_params(rm, D, 1);
+        p.chunk = 1;
         CKG(gemm(l.qkv, vA768, R1, p));
         if (i == 0 && taps_on()) tap_f16("pre0_qkv_rope", qkv_hi, qkv_lo, (size_t) R1 * 3 * D);
         if (!(e = run_attention(R1, D, hp.prenet_heads, hp.prenet_window, 1, vA768, attn_b1)).empty()) return e;
         if (i == 0 && taps_on()) tap_f16("pre0_attn", vA768.hi, vA768.lo, (size_t) R1 * D);
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
+        p.chunk = 1;
         CKG(gemm(l.wo, vA768, R1, p));
         if (i == 0 && taps_on()) tap_f32("pre0_x_attn", x768, R1, D);
         CKR(CAT_LN, (double) (R1) * 8.0 * (D), launch_layernorm(x768, R1, D, hp.norm_eps, l.fn_w, l.fn_b, nullptr, 0, 0, 0, rm, 1, vA768.hi, vA768.lo, nullptr, stream, next_dir()));
         p = gemm_params(); p.epi = EPI_SWIGLU; p.out_hi = vFF2048.hi; p.out_lo = vFF2048.lo; p.ld_h = hp.prenet_ff;
+        p.chunk = 1;
         CKG(gemm(l.gu, vA768, R1, p));
         p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x768; p.ld_out = D;
+        p.chunk = 1;
         CKG(gemm(l.down, vFF2048, R1, p));
         if (taps_on()) tap_f32("pre" + std::to_string(i) + "_out", x768, R1, D);
     }
@@ -1034,6 +1043,7 @@ std::string engine::run_chunk(const chunk_info & c) {
     // the prenet LN output lives in aA viewed as [R1][768]; the 512-wide result must not overwrite it while other
     // CTAs still read it -> stage through aFF
     p.out_hi = aFF_hi; p.out_lo = aFF_lo;
+    p.chunk = 1;
     CKG(gemm(w.pre_out, vA768, R1, p));
     if (taps_on()) tap_f16("prenet_out", aFF_hi, aFF_lo, (size_t) R1 * C);
     // 3. wave_upsample ConvTranspose1d(k=2, s=2): [R1][2*512] == [R2][512]
@@ -1041,6 +1051,7 @@ std::string engine::run_chunk(const chunk_info & c) {
         a_view v = vFF1536;   // aFF viewed as [.][512]
         if (!(e = view512_ff(v)).empty()) return e;
         p = gemm_params(); p.epi = EPI_STORE; p.out_f32 = x512; p.ld_out = 2 * C; p.bias = w.up0_b; p.bias_mod = C;
+        p.chunk = 1;
         CKG(gemm(w.up0, v, R1, p));
     }
     if (taps_on()) tap_f32("upsample", x512, R2, C);

@@ -29,6 +29,10 @@ namespace mio {
 constexpr int G3_BK = 64;
 constexpr int G3_THREADS = 320;     // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-9: epilogue
 constexpr int G3_EPI_WARPS = 8;
+// Chunked accumulation (template parameter CHUNK > 0, see the kernel): 384 threads = 3 warpgroups so that setmaxnreg
+// can move registers from the producer / MMA warpgroup (warps 0-3, two of them idle) to the epilogue warpgroups
+// (warps 4-11), which keep a 256 x BN tile's fp32 running sum in registers: 40 / 232 registers per thread.
+constexpr int G3_THREADS_CHUNKED = 384;
 constexpr int G3_STAGE_TILE = 4096; // staging bytes per epilogue warp
 
 template <int BN, int NPASS>
@@ -192,8 +196,17 @@ template <int EPI> struct epi3_out {
     static constexpr int ACC_PER_OUT = (EPI == EPI_SWIGLU) ? 2 : 1;   // accumulator columns per output column
 };
 
-template <int BN, int NPASS, int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G3_THREADS, 1)
+// CHUNK = 0: the whole K extent accumulates in one TMEM accumulator (double buffered across tiles).
+// CHUNK = 1: "chunked accumulation" (chunk length p.chunk k-blocks, a run-time value).  The tensor core adds into its fp32 accumulator with TRUNCATION toward zero, once
+// per MMA instruction (profiles/r2a_parity_attribution.md: probes + a signed bias of -2e-6 of the output rms at K = 768,
+// -5e-6 at K = 2048, against 5e-7 unbiased for fp32 FMAs).  That bias is what kept the decoder ~0.8 dB under the
+// reference's own cross-build parity floor: the layers in front of the first conv1d need fp32-grade sums.  Here every
+// p.chunk k-blocks (p.chunk * 64 of K) go to a FRESH TMEM accumulator (the two buffers alternate per chunk instead of per
+// tile), the small cross terms (hi*lo, lo*hi) of a k-block are issued before its hi*hi, and the epilogue warps add the
+// finished chunk to a running sum in registers with round-to-nearest.  The truncations then act on partial sums of
+// short runs whose signs are independent, so the error stops growing with K: ~4e-7 of the output rms for any K.
+template <int BN, int NPASS, int EPI, int CHUNK>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(CHUNK > 0 ? G3_THREADS_CHUNKED : G3_THREADS, 1)
 gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                 const __grid_constant__ CUtensorMap tmB_hi, const __grid_constant__ CUtensorMap tmB_lo,
                 const __grid_constant__ CUtensorMap tmO0, const __grid_constant__ CUtensorMap tmO1,
@@ -212,6 +225,7 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     uint32_t * tmem_slot = (uint32_t *) (bars + 2 * cfg::STAGES + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr int EPI_WARP0 = (CHUNK > 0) ? 4 : 2;            // first epilogue warp
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
     const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
@@ -241,6 +255,9 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
 
+    if (warp < EPI_WARP0) {
+    // chunked variant: this warpgroup (producer, MMA issuer, two idle warps) hands its registers to the epilogue warpgroups
+    if constexpr (CHUNK > 0) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
     if (warp == 0) {
         // ===== TMA producer (both CTAs) =====
         if (lane == 0) {
@@ -269,6 +286,43 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     } else if (warp == 1) {
         // ===== MMA issuer (leader CTA only) =====
         if (leader && lane == 0) {
+            if constexpr (CHUNK > 0) {
+                int it = 0, ci = 0;                               // ci: running chunk counter = accumulator hand-offs
+                for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                    for (int kb0 = 0; kb0 < num_kb; kb0 += p.chunk, ci++) {
+                        const int b = ci & 1;
+                        const uint32_t aph = (uint32_t) (ci >> 1) & 1u;
+                        mbar_wait(&tmem_empty[b], aph ^ 1u);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        const uint32_t d_tmem = tmem_base + (uint32_t) (b * BN);
+                        const int nk = (num_kb - kb0 < p.chunk) ? num_kb - kb0 : p.chunk;
+                        for (int j = 0; j < nk; j++, it++) {
+                            const int s = it % cfg::STAGES;
+                            const uint32_t ph = (uint32_t) (it / cfg::STAGES) & 1u;
+                            mbar_wait(&full[s], ph);
+                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                            const uint32_t sa = smem_u32(smem + s * cfg::STAGE_BYTES);
+                            const uint32_t sb = sa + cfg::NOPS * cfg::A_BYTES;
+                            const uint64_t da_hi = umma_desc(sa), db_hi = umma_desc(sb);
+                            if constexpr (NPASS == 3) {
+                                const uint64_t da_lo = umma_desc(sa + cfg::A_BYTES), db_lo = umma_desc(sb + cfg::B_BYTES);
+                                // cross terms first: they are 2^-11 of the hi*hi terms, so their truncations are free
+#pragma unroll
+                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_lo + (uint64_t) (k * 2), cfg::IDESC, (j > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_lo + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), cfg::IDESC, 1u);
+#pragma unroll
+                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), cfg::IDESC, 1u);
+                            } else {
+#pragma unroll
+                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), cfg::IDESC, (j > 0 || k > 0) ? 1u : 0u);
+                            }
+                            umma_commit_pair(&empty[s]);
+                        }
+                        umma_commit_pair(&tmem_full[b]);
+                    }
+                }
+            } else {
             int it = 0, tile_iter = 0;
             for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, tile_iter++) {
                 const int b = tile_iter & 1;
@@ -312,16 +366,20 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                 }
                 umma_commit_pair(&tmem_full[b]);
             }
+            }
         }
+    }
     } else {
-        // ===== epilogue warps (both CTAs): TMEM lane quadrant = warp % 4, column half = (warp - 2) / 4 =====
+        // ===== epilogue warps (both CTAs): TMEM lane quadrant = warp % 4, column half = (warp - EPI_WARP0) / 4 =====
+        if constexpr (CHUNK > 0) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
         const int lg = warp & 3;
-        const int half = (warp - 2) >> 2;
+        const int half = (warp - EPI_WARP0) >> 2;
         constexpr int CH = BN / 2 / 32;                          // 32-column chunks per warp per tile
-        uint8_t * stage = epi_smem + (warp - 2) * G3_STAGE_TILE;
+        uint8_t * stage = epi_smem + (warp - EPI_WARP0) * G3_STAGE_TILE;
         const uint32_t tmem_empty_leader0 = mapa_u32(smem_u32(&tmem_empty[0]), 0);
         const uint32_t tmem_empty_leader1 = mapa_u32(smem_u32(&tmem_empty[1]), 0);
         int tile_iter = 0;
+        [[maybe_unused]] int ci = 0;                             // CHUNK > 0: running chunk counter (accumulator hand-offs)
         for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, tile_iter++) {
             const int t2 = p.reverse ? num_tiles - 1 - tile : tile;
             const int tm = t2 / tiles_n, tn = t2 - tm * tiles_n;
@@ -343,6 +401,64 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                     const int u = (row < p.M) ? p.row_utt[row / p.row_div] : -1;
                     if (u >= 0) aux = p.gate_voice[u];
                 }
+            }
+            if constexpr (CHUNK > 0) {
+                // running sum of this thread's row: CH pieces of 32 columns, in registers
+                float acc[CH][32];
+#pragma unroll
+                for (int j = 0; j < CH; j++) {
+#pragma unroll
+                    for (int i = 0; i < 32; i++) acc[j][i] = 0.f;
+                }
+                const int nchunks = (num_kb + p.chunk - 1) / p.chunk;
+                for (int cc = 0; cc < nchunks; cc++, ci++) {
+                    const int bb = ci & 1;
+                    mbar_wait(&tmem_full[bb], (uint32_t) (ci >> 1) & 1u);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t t_addr = tmem_base + ((uint32_t) (lg * 32) << 16) + (uint32_t) (bb * BN + half * (BN / 2));
+#pragma unroll
+                    for (int j = 0; j < CH; j++) {
+                        if (j < nch) {                                   // warp-uniform
+                            float t[32];
+                            tmem_ld32(t_addr + (uint32_t) (j * 32), t);
+#pragma unroll
+                            for (int i = 0; i < 32; i++) acc[j][i] += t[i];       // round-to-nearest, unlike the MMA's adder
+                        }
+                    }
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_remote(bb ? tmem_empty_leader1 : tmem_empty_leader0);
+                }
+#pragma unroll 1
+                for (int c = 0; c < nch; c++) {
+                    float v[32];
+#pragma unroll
+                    for (int i = 0; i < 32; i++) v[i] = acc[0][i];
+#pragma unroll
+                    for (int j = 0; j + 1 < CH; j++) {                   // rotate: the piece index stays static for the compiler
+#pragma unroll
+                        for (int i = 0; i < 32; i++) acc[j][i] = acc[j + 1][i];
+                    }
+                    const int part = (eo::ACC_PER_OUT == 2) ? (c & 1) : 0;
+                    if (part == 0) {
+                        if (lane == 0) tma_store_wait_read0();
+                        __syncwarp();
+                    }
+                    epi3_chunk<EPI>(p, row, colw + c * 32, v, stage, lane, part, aux);
+                    const bool flush = (eo::ACC_PER_OUT == 1) || part == 1 || c == nch - 1;
+                    if (flush) {
+                        fence_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            const int oc = (eo::ACC_PER_OUT == 2) ? (colw + (c & ~1) * 32) / 2 : colw + c * 32;
+                            if (eo::REDUCE) tma_reduce_add_2d(&tmO0, stage, oc, row0);
+                            else tma_store_2d(&tmO0, stage, oc, row0);
+                            if (eo::F16) tma_store_2d(&tmO1, stage + 2048, oc, row0);
+                            tma_store_commit();
+                        }
+                    }
+                }
+                continue;
             }
             mbar_wait(&tmem_full[b], aph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -392,7 +508,9 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     }
 }
 
-template <int BN, int NPASS, int EPI>
+constexpr int G3_CHUNK = 1;   // template flag of the chunked kernels; the chunk length (k-blocks) is the run-time p.chunk
+
+template <int BN, int NPASS, int EPI, int CHUNK>
 static cudaError_t launch_tc3_inst(const gemm_params & p, const CUtensorMap & a_hi, const CUtensorMap & a_lo,
                                    const CUtensorMap & b_hi, const CUtensorMap & b_lo, const CUtensorMap & o0,
                                    const CUtensorMap & o1, int num_sms, cudaStream_t st) {
@@ -401,14 +519,36 @@ static cudaError_t launch_tc3_inst(const gemm_params & p, const CUtensorMap & a_
     const int tiles = ((p.N + BN - 1) / BN) * ((p.M + 255) / 256);
     int clusters = num_sms / 2;
     if (tiles < clusters) clusters = tiles;
-    gemm_tc3_kernel<BN, NPASS, EPI><<<2 * clusters, G3_THREADS, cfg::SMEM_BYTES, st>>>(a_hi, a_lo, b_hi, b_lo, o0, o1, p);
+    gemm_tc3_kernel<BN, NPASS, EPI, CHUNK><<<2 * clusters, CHUNK > 0 ? G3_THREADS_CHUNKED : G3_THREADS, cfg::SMEM_BYTES, st>>>(
+        a_hi, a_lo, b_hi, b_lo, o0, o1, p);
     return cudaGetLastError();
+}
+
+// chunked accumulation exists for the fp32-class layers in front of the first conv1d (engine::run_chunk sets p.chunk there)
+template <int EPI> struct epi3_chunkable {
+    static constexpr bool value = (EPI == EPI_STORE || EPI == EPI_RESID || EPI == EPI_SWIGLU || EPI == EPI_SPLIT || EPI == EPI_QKV);
+};
+
+template <int BN, int NPASS, int EPI>
+static cudaError_t launch_tc3_pick(const gemm_params & p, const CUtensorMap & a_hi, const CUtensorMap & a_lo,
+                                   const CUtensorMap & b_hi, const CUtensorMap & b_lo, const CUtensorMap & o0,
+                                   const CUtensorMap & o1, int num_sms, cudaStream_t st) {
+    if constexpr (NPASS == 3 && epi3_chunkable<EPI>::value) {
+        if (p.chunk > 0) return launch_tc3_inst<BN, NPASS, EPI, G3_CHUNK>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+    }
+    return launch_tc3_inst<BN, NPASS, EPI, 0>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
 }
 
 template <int BN, int NPASS, int EPI>
 static cudaError_t set_attr_inst() {
-    return cudaFuncSetAttribute(gemm_tc3_kernel<BN, NPASS, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                gemm3_cfg<BN, NPASS>::SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc3_kernel<BN, NPASS, EPI, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         gemm3_cfg<BN, NPASS>::SMEM_BYTES);
+    if constexpr (NPASS == 3 && epi3_chunkable<EPI>::value) {
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(gemm_tc3_kernel<BN, NPASS, EPI, G3_CHUNK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     gemm3_cfg<BN, NPASS>::SMEM_BYTES);
+    }
+    return e;
 }
 template <int BN>
 static cudaError_t set_attr_bn() {
@@ -437,20 +577,20 @@ static cudaError_t launch_tc3_epi(const gemm_params & p, const CUtensorMap & a_h
                                   const CUtensorMap & b_hi, const CUtensorMap & b_lo, const CUtensorMap & o0,
                                   const CUtensorMap & o1, int num_sms, cudaStream_t st) {
     switch (p.epi) {
-        case EPI_STORE: return launch_tc3_inst<BN, NPASS, EPI_STORE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
-        case EPI_RESID: return launch_tc3_inst<BN, NPASS, EPI_RESID>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+        case EPI_STORE: return launch_tc3_pick<BN, NPASS, EPI_STORE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+        case EPI_RESID: return launch_tc3_pick<BN, NPASS, EPI_RESID>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
         default: break;
     }
     if constexpr (NPASS == 3) {
         switch (p.epi) {
             case EPI_SWIGLU:
                 if (p.N % 64 != 0) return cudaErrorInvalidValue;
-                if constexpr (BN >= 128) return launch_tc3_inst<BN, 3, EPI_SWIGLU>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+                if constexpr (BN >= 128) return launch_tc3_pick<BN, 3, EPI_SWIGLU>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
                 else return cudaErrorInvalidValue;   // a (gate, up) pair row needs 64 accumulator columns per warp
-            case EPI_SPLIT: return launch_tc3_inst<BN, 3, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
-            case EPI_SNAKE: return launch_tc3_inst<BN, 3, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
-            case EPI_HEAD: return launch_tc3_inst<BN, 3, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
-            case EPI_QKV: return launch_tc3_inst<BN, 3, EPI_QKV>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+            case EPI_SPLIT: return launch_tc3_pick<BN, 3, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+            case EPI_SNAKE: return launch_tc3_pick<BN, 3, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+            case EPI_HEAD: return launch_tc3_pick<BN, 3, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+            case EPI_QKV: return launch_tc3_pick<BN, 3, EPI_QKV>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
             default: break;
         }
     }

@@ -25,6 +25,9 @@ struct gemm_params {
     int npass = 3;                         // 3: (a_hi + a_lo)(b_hi + b_lo) without lo*lo; 1: a_hi * b_hi
     int mma_order = 2;                     // MIO_MMA_ORDER: 2 (default) = pass-major inside a 64-wide k-block (4 x hi*hi, 4 x
                                            // hi*lo, 4 x lo*hi), 0 / 1 = the three passes interleaved per 16-wide k step
+    int chunk = 0;                         // > 0: chunked accumulation (gemm3.cu): a fresh tensor-core accumulator every chunk * 64 of K,
+                                           // chunks added in fp32 registers with round-to-nearest; the layers in front of
+                                           // the first conv1d use it (npass 3 only)
     int reverse = 0;                       // walk the M tiles from the last row down (generation 3): consecutive kernels
                                            // alternate, so each starts on the rows its predecessor left in L2
     float out_scale = 1.f;

@@ -42,13 +42,24 @@ build_variant() {
     g++ -std=gnu++17 -O3 -fPIC "${arch[@]}" "${DEFS[@]}" "${INCS[@]}" -c "$GG/src/$s" -o "$o" &
     pids+=($!)
   done
-  # the reference hot path itself + our C wrapper
-  g++ -std=gnu++17 -O2 -fPIC "${arch[@]}" "${INCS[@]}" -I"$REF/src" -c "$REF/src/miocodec.cpp" -o "$obj/ref_miocodec.o" & pids+=($!)
-  g++ -std=gnu++17 -O2 -fPIC "${arch[@]}" -I"$REF/src" -c "$REF/src/istft.cpp" -o "$obj/ref_istft.o" & pids+=($!)
+  # the reference hot path itself + our C wrapper.  The reference's CMakeLists.txt gives its first-party sources NO
+  # -march flag (only ggml is built "native", GGML_NATIVE): they are compiled for baseline x86-64, i.e. without FMA
+  # contraction.  That is visible in the bits of irfft's accumulation (src/istft.cpp:57-62) and of the crossfade
+  # (src/test-to-speech.cpp:388-395), so the first-party files are compiled the same way here (Release: -O3 -DNDEBUG).
+  FP=(-std=gnu++17 -O3 -DNDEBUG -fPIC)
+  g++ "${FP[@]}" "${INCS[@]}" -I"$REF/src" -c "$REF/src/miocodec.cpp" -o "$obj/ref_miocodec.o" & pids+=($!)
+  g++ "${FP[@]}" -I"$REF/src" -c "$REF/src/istft.cpp" -o "$obj/ref_istft.o" & pids+=($!)
   # the steps either side of the path: token parser and WAV writer, also unmodified
-  g++ -std=gnu++17 -O2 -fPIC "${arch[@]}" -I"$REF/src" -c "$REF/src/token-parser.cpp" -o "$obj/ref_token_parser.o" & pids+=($!)
-  g++ -std=gnu++17 -O2 -fPIC "${arch[@]}" -I"$REF/src" -c "$REF/src/wav-writer.cpp" -o "$obj/ref_wav_writer.o" & pids+=($!)
-  g++ -std=gnu++17 -O2 -fPIC "${arch[@]}" -I"$REF/src" -c "$HERE/ref_capi.cpp" -o "$obj/ref_capi.o" & pids+=($!)
+  g++ "${FP[@]}" -I"$REF/src" -c "$REF/src/token-parser.cpp" -o "$obj/ref_token_parser.o" & pids+=($!)
+  g++ "${FP[@]}" -I"$REF/src" -c "$REF/src/wav-writer.cpp" -o "$obj/ref_wav_writer.o" & pids+=($!)
+  # the streaming policy (emit_range / maybe_emit live inside TestToSpeech::synthesize_stream_profiled): the reference's
+  # orchestrator, unmodified, against a scripted stand-in for libllama (oracle/stub_llama.cpp; token generation is out
+  # of scope, the stub only feeds the codes the "LLM" would emit)
+  LL="$REF/third_party/llama.cpp/include"
+  g++ "${FP[@]}" "${INCS[@]}" -I"$LL" -I"$REF/src" -c "$REF/src/test-to-speech.cpp" -o "$obj/ref_test_to_speech.o" & pids+=($!)
+  g++ "${FP[@]}" -I"$REF/src" -c "$REF/src/text-normalize.cpp" -o "$obj/ref_text_normalize.o" & pids+=($!)
+  g++ "${FP[@]}" "${INCS[@]}" -I"$LL" -c "$HERE/stub_llama.cpp" -o "$obj/stub_llama.o" & pids+=($!)
+  g++ "${FP[@]}" -I"$REF/src" -c "$HERE/ref_capi.cpp" -o "$obj/ref_capi.o" & pids+=($!)
   for p in "${pids[@]}"; do wait "$p"; done
   g++ -shared -o "$OUT/libmio_ref_$tag.so" "$obj"/*.o -lpthread -lm -ldl
   rm -rf "$obj"

@@ -133,6 +133,29 @@ class Reference:
         return out[:n].copy()
 
 
+def ref_stream_session(gguf_path: str, voice_path: str, codes, skip_llm: bool = False, chunk_samples: int = 4096):
+    """The reference's OWN streaming code: TestToSpeech::synthesize_stream_profiled (src/test-to-speech.cpp:348-626,
+    unmodified) with oracle/stub_llama.cpp emitting `codes` one per generated token (LLM branch: maybe_emit cadence /
+    holdback / llround indexing, emit_range chunking + crossfade) or, with skip_llm, the single-decode branch.
+    Returns (emitted audio, chunk sizes, stats dict with the StreamProfile counters)."""
+    L = C.CDLL(lib_path())
+    L.mio_ref_stream_session.restype = C.c_long
+    L.mio_ref_stream_session.argtypes = [C.c_char_p, C.c_char_p, C.c_void_p, C.c_int, C.c_int, C.c_long, C.c_void_p, C.c_long,
+                                         C.c_void_p, C.c_long, C.POINTER(C.c_long), C.c_void_p]
+    codes = np.ascontiguousarray(codes, dtype=np.int32)
+    out = np.empty(len(codes) * 1764 + 8192, dtype=np.float32)
+    chunks = np.zeros(len(out) // max(1, chunk_samples) + 64 + 2 * len(codes), dtype=np.int64)
+    nch = C.c_long(0)
+    prof = np.zeros(5, dtype=np.int64)
+    n = L.mio_ref_stream_session(gguf_path.encode(), voice_path.encode(), codes.ctypes.data, len(codes), int(skip_llm), chunk_samples,
+                                 out.ctypes.data, out.size, chunks.ctypes.data, chunks.size, C.byref(nch), prof.ctypes.data)
+    if n < 0:
+        raise RuntimeError("reference stream session failed (%d)" % n)
+    stats = dict(decode_calls=int(prof[0]), decoded_codes=int(prof[1]), emitted_samples=int(prof[2]), llm_tokens=int(prof[3]),
+                 last_flags=int(prof[4]))
+    return out[:n].copy(), chunks[: nch.value].copy(), stats
+
+
 def ref_istft_only(spec: np.ndarray, n_fft: int = 392, hop: int = 98) -> np.ndarray:
     """istft() of the reference without a codec context."""
     p = lib_path()

@@ -12,6 +12,7 @@
 #include "istft.h"      // reference header
 #include "token-parser.h"   // reference header (pre-path ingest)
 #include "wav-writer.h"     // reference header (post-path epilogue)
+#include "test-to-speech.h" // reference header: TestToSpeech (streaming policy)
 
 #include <chrono>
 #include <cstdio>
@@ -120,6 +121,67 @@ long mio_ref_parse_speech_tokens(const char * text, long text_len, int * out, lo
     std::vector<int> codes = parse_speech_tokens(std::string(text, (size_t) text_len));
     for (long i = 0; i < (long) codes.size() && i < cap; i++) out[i] = codes[i];
     return (long) codes.size();
+}
+
+// The reference's own streaming session: TestToSpeech::synthesize_stream_profiled, LLM branch
+// (/root/reference/src/test-to-speech.cpp:430-625: maybe_emit :507-571, emit_range :367-417), with oracle/stub_llama.cpp
+// emitting `codes` one per generated token.  skip_llm != 0 runs the skip_llm branch (:419-428) on "<|s_N|>" text instead.
+// Writes the concatenated emitted audio to out, the size of every callback chunk to chunk_sizes, and
+// profile[0..4] = decode_calls, decoded_codes, emitted_samples, llm_tokens, number of callbacks with is_last_chunk.
+// Returns the number of emitted samples or < 0.
+long mio_ref_stream_session(const char * codec_gguf, const char * voice_path, const int * codes, int n_codes, int skip_llm,
+                            long chunk_samples, float * out, long out_cap, long * chunk_sizes, long chunk_cap, long * n_chunks,
+                            long long * profile) {
+    stderr_mute m;
+    char script[] = "/tmp/mio_ref_scriptXXXXXX";
+    std::string text;
+    TestToSpeech::Config cfg;
+    cfg.codec_path = codec_gguf;
+    if (!skip_llm) {
+        int fd = mkstemp(script);
+        if (fd < 0) return -1;
+        FILE * f = fdopen(fd, "w");
+        for (int i = 0; i < n_codes; i++) fprintf(f, "%d\n", codes[i]);
+        fclose(f);
+        cfg.model_path = script;
+        text = "scripted";
+    } else {
+        for (int i = 0; i < n_codes; i++) text += "<|s_" + std::to_string(codes[i]) + "|>";
+    }
+    long total = 0, nchunks = 0, lasts = 0;
+    bool overflow = false;
+    long rc = -2;
+    {
+        TestToSpeech tts(cfg);
+        VoiceModel voice;
+        if (tts.is_ready() && voice.load_from_file(voice_path)) {
+            TestToSpeech::Options opt;
+            opt.skip_llm = skip_llm != 0;
+            opt.max_tokens = n_codes + 8 > 700 ? n_codes + 8 : 700;
+            opt.apply_peak_normalization = false;
+            TestToSpeech::StreamProfile prof;
+            const bool ok = tts.synthesize_stream_profiled(
+                voice, text,
+                [&](const float * s, size_t n, int, bool is_last) -> bool {
+                    if (total + (long) n > out_cap) overflow = true;
+                    else if (n > 0) memcpy(out + total, s, n * sizeof(float));
+                    total += (long) n;
+                    if (nchunks < chunk_cap) chunk_sizes[nchunks] = (long) n;
+                    nchunks++;
+                    if (is_last) lasts++;
+                    return true;
+                },
+                (size_t) chunk_samples, opt, prof);
+            if (ok && !overflow) {
+                profile[0] = prof.decode_calls; profile[1] = (long long) prof.decoded_codes;
+                profile[2] = (long long) prof.emitted_samples; profile[3] = prof.llm_tokens; profile[4] = lasts;
+                rc = total;
+            } else rc = overflow ? -3 : -4;
+        }
+    }
+    if (!skip_llm) unlink(script);
+    if (n_chunks) *n_chunks = nchunks;
+    return rc;
 }
 
 // wav_write (/root/reference/src/wav-writer.cpp:24-45): 44-byte RIFF header + PCM16 (clamp(s*32767) truncated).

@@ -46,3 +46,46 @@ def codec(assets):
     c = binding.MioCodec(assets[0], 0)
     yield c
     c.close()
+
+
+# ---- the parity floor: the reference against its own other-ISA build (tests/test_parity_floor.py) ----------------------
+FLOOR_SNR_DB = 59.3          # lowest per-utterance v3-vs-v4 SNR measured (T = 20 .. 250; mean over 32 utterances 59.85 +- 0.24)
+FLOOR_MAXABS = 2.9e-3        # largest per-utterance v3-vs-v4 max-abs measured over the same set (signal peak ~2)
+_floor_refs = {}
+
+
+def reference_floor(gguf, codes, emb):
+    """(SNR dB, max-abs) between the two builds of the reference (oracle/_ref v3 = AVX2, v4 = AVX-512) for this utterance,
+    or the recorded constants when this host cannot run both."""
+    from oracle import ref
+    flags = ref._cpu_flags()
+    here = os.path.dirname(os.path.abspath(ref.__file__))
+    both = all(os.path.exists(os.path.join(here, "_ref", f"libmio_ref_{t}.so")) for t in ("v3", "v4")) and \
+        {"avx512f", "avx512bw", "avx512dq", "avx512vl", "avx512cd"} <= flags
+    if not both:
+        return FLOOR_SNR_DB, FLOOR_MAXABS
+    waves = []
+    for tag in ("v3", "v4"):
+        if tag not in _floor_refs:
+            old = os.environ.get("MIO_REF_VARIANT")
+            os.environ["MIO_REF_VARIANT"] = tag
+            try:
+                _floor_refs[tag] = ref.Reference(gguf)
+            finally:
+                if old is None:
+                    os.environ.pop("MIO_REF_VARIANT", None)
+                else:
+                    os.environ["MIO_REF_VARIANT"] = old
+        waves.append(_floor_refs[tag].decode_wave(codes, emb))
+    return snr_db(waves[0], waves[1]), float(np.abs(waves[0] - waves[1]).max())
+
+
+def assert_at_parity_floor(wave, w_ref, gguf, codes, emb, what=""):
+    """The GPU waveform must be as close to the reference as the reference's other build is: SNR >= floor - 0.5 dB (and
+    never below 58.5), max-abs <= 1.25 x the larger of this utterance's floor max-abs and the recorded one."""
+    f_snr, f_max = reference_floor(gguf, codes, emb)
+    s, m = snr_db(wave, w_ref), float(np.abs(wave - w_ref).max())
+    print(f"{what}: SNR {s:.2f} dB (floor {f_snr:.2f}), max-abs {m:.2e} (floor {f_max:.2e}), peak {np.abs(w_ref).max():.2f}")
+    assert s > max(58.5, min(f_snr, 60.0) - 0.5), (what, s, f_snr)
+    assert m < 1.25 * max(f_max, FLOOR_MAXABS), (what, m, f_max)
+    return s

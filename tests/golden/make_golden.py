@@ -53,6 +53,20 @@ def main():
     spec = rng.standard_normal((50, 394)).astype(np.float32)
     wave = ref.ref_istft_only(spec)
     np.savez_compressed(os.path.join(HERE, "istft50.npz"), spec=spec, wave=wave)
+    # streaming sessions of the reference's OWN orchestrator (TestToSpeech::synthesize_stream_profiled, LLM branch, with
+    # oracle/stub_llama.cpp emitting the codes): chunk sizes + StreamProfile counters for every N, the emitted audio for
+    # the short ones (the long ones are compared live on the GPU box, where oracle/_ref is present)
+    import hashlib as _h
+    for N, vid in ((7, 0), (47, 1), (100, 2), (230, 4), (700, 5)):
+        codes = synth.synth_codes(N, 70 + N)
+        audio, chunks, st = ref.ref_stream_session(g, voices[vid], codes)
+        assert len(audio) == 1764 * N == st["emitted_samples"]
+        keep = audio if N <= 100 else np.empty(0, dtype=np.float32)
+        np.savez_compressed(os.path.join(HERE, f"stream{N}.npz"), codes=codes.astype(np.int32), voice=np.int32(vid), chunks=chunks.astype(np.int64),
+                            decode_calls=np.int64(st["decode_calls"]), decoded_codes=np.int64(st["decoded_codes"]),
+                            emitted_samples=np.int64(st["emitted_samples"]), llm_tokens=np.int64(st["llm_tokens"]), audio=keep,
+                            audio_sha256=np.frombuffer(_h.sha256(audio.tobytes()).digest(), dtype=np.uint8))
+        print("stream", N, st, len(chunks))
     with open(os.path.join(HERE, "meta.txt"), "w") as f:
         for k, v in meta.items():
             f.write(f"{k}={v}\n")

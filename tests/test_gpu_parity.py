@@ -2,22 +2,24 @@
 compared with the oracle: golden vectors produced by the unmodified reference, the compiled reference itself when
 oracle/_ref loads on this host, and the torch restatement (oracle/port.py) for per-stage checks.
 
-Tolerances (DESIGN.md "parity floor"): the reference rounds conv1d operands to FP16 (ggml.c:4416), which makes its
-output discontinuous in fp32 round-off; an exact (fp64) evaluation of the same graph only reaches ~59-60 dB SNR /
-~2e-3 max-abs against it.  Stages before the first conv1d and the ISTFT are continuous and are held to
->= 90 dB; the end-to-end waveform is held to >= 55 dB and to within 3 dB of what the fp32 port reaches.
-Frame counts, sample counts and indexing are exact."""
+Tolerances (DESIGN.md "parity floor", tests/test_parity_floor.py): the reference rounds conv1d operands to FP16
+(ggml.c:4416), which makes its output discontinuous in fp32 round-off; the reference built for another ISA, and an exact
+(fp64) evaluation of the same graph, only reach 59.3-59.9 dB SNR / 1.9-2.9e-3 max-abs against it.  That measured floor is
+the bar: the end-to-end waveform must be within 0.5 dB of the floor of the SAME utterance (conftest.assert_at_parity_floor:
+both builds of the reference are run live when the host has AVX-512) and within 1.25 x its max-abs.  Stages in front of the
+first conv1d are continuous and are held to >= 105 dB (tcgen05 with chunked accumulation) and the ISTFT to >= 88 dB; every
+later stage is held to fp32 accuracy by the teacher-forced tests (tests/test_gpu_stages.py).  Frame counts, sample counts
+and indexing are exact; results are bit-identical across batching, chunking and delivery splits."""
 import os
 
 import numpy as np
 import pytest
 
-from conftest import load_golden, snr_db
+from conftest import assert_at_parity_floor, load_golden, snr_db
 
 pytestmark = pytest.mark.gpu
 
-WAVE_SNR_MIN = 55.0
-WAVE_MAXABS_REL = 5e-3
+VALIDATOR_SNR_MIN = 58.5     # product path vs a CUDA-core validation path: two independent evaluations, i.e. the floor again
 
 
 def _voice(v):
@@ -26,7 +28,7 @@ def _voice(v):
 
 
 @pytest.mark.parametrize("case", ["ref20", "rand33", "one"])
-def test_wave_and_spec_match_reference_golden(codec, weights, case):
+def test_wave_and_spec_match_reference_golden(codec, weights, assets, case):
     from oracle import port
     g = load_golden(case)
     codes, emb = g["codes"], _voice(int(g["voice"]))
@@ -38,12 +40,13 @@ def test_wave_and_spec_match_reference_golden(codec, weights, case):
     assert fused.shape == wave.shape
     assert np.array_equal(fused, wave)                                # same kernels, deterministic: same bits
     hp, W = weights
-    floor = snr_db(port.istft(port.decode(W, hp, codes, emb)), g["wave"])
-    s = snr_db(wave, g["wave"])
-    print(f"{case}: wave SNR {s:.1f} dB (fp32 port reaches {floor:.1f} dB), spec SNR {snr_db(spec, g['spec']):.1f} dB")
-    assert s > WAVE_SNR_MIN and s > floor - 3.0
-    assert np.abs(wave - g["wave"]).max() < WAVE_MAXABS_REL * max(1.0, np.abs(g["wave"]).max())
-    assert snr_db(spec, g["spec"]) > WAVE_SNR_MIN
+    port_snr = snr_db(port.istft(port.decode(W, hp, codes, emb)), g["wave"])
+    print(f"{case}: the fp32 port reaches {port_snr:.2f} dB, spec SNR {snr_db(spec, g['spec']):.2f} dB")
+    if case == "one":      # a single code: 1764 samples, the statistic is too noisy for a 0.5 dB band
+        assert snr_db(wave, g["wave"]) > 58.5 and np.abs(wave - g["wave"]).max() < 3.6e-3
+    else:
+        assert_at_parity_floor(wave, g["wave"], assets[0], codes, emb, case)
+    assert snr_db(spec, g["spec"]) > 58.3
 
 
 def test_istft_matches_reference_golden(codec):
@@ -83,7 +86,7 @@ def test_stages_before_first_conv_are_fp32_accurate(assets, weights, mode):
     c.set_option("debug_snapshots", "1")
     c.decode_wave(codes, emb)
     T = len(codes)
-    lim = {"tc3": 90.0, "simt": 105.0}[mode]
+    lim = {"tc3": 105.0, "simt": 105.0}[mode]       # tcgen05 with chunked accumulation is as accurate as fp32 FMAs
     for name, r in [("embed", 1), ("pre0_qkv_rope", 1), ("pre0_attn", 1), ("pre0_out", 1), ("prenet_out", 1), ("upsample", 2)]:
         got = c.debug_read(name).reshape(-1, inter[name].shape[1])[: T * r]
         s = snr_db(got, inter[name])
@@ -166,7 +169,7 @@ def test_simt_and_tensor_core_paths_agree(assets, codec):
     codes, emb = synth.synth_codes(50, 8), _voice(2)
     simt = binding.MioCodec(assets[0], 0, gemm="simt")
     a, b = simt.decode_wave(codes, emb), codec.decode_wave(codes, emb)
-    assert snr_db(b, a) > WAVE_SNR_MIN
+    assert snr_db(b, a) > VALIDATOR_SNR_MIN
     simt.close()
 
 
@@ -181,7 +184,7 @@ def test_attention_validation_kernel_agrees(assets, codec):
     finally:
         del os.environ["MIO_ATTN"]
     a, b = simt.decode_wave(codes, emb), codec.decode_wave(codes, emb)
-    assert snr_db(b, a) > WAVE_SNR_MIN
+    assert snr_db(b, a) > VALIDATOR_SNR_MIN
     simt.close()
 
 
@@ -198,10 +201,7 @@ def test_c2_full_size_against_live_reference(assets, codec):
     w_ref = R.decode_wave(codes, emb)
     R.close()
     assert w_ref.shape == wave.shape
-    s = snr_db(wave, w_ref)
-    print(f"C2 T=700: SNR {s:.1f} dB, max-abs {np.abs(wave - w_ref).max():.2e}, peak {np.abs(w_ref).max():.2f}")
-    assert s > WAVE_SNR_MIN
-    assert np.abs(wave - w_ref).max() < WAVE_MAXABS_REL * max(1.0, np.abs(w_ref).max()) * 2
+    assert_at_parity_floor(wave, w_ref, assets[0], codes, emb, "C2 T=700")
 
 
 def test_streaming_matches_reference_policy(codec):
@@ -233,7 +233,7 @@ def test_streaming_matches_reference_policy(codec):
         mine = s.stats()
         assert mine == st, (mine, st)                                  # decode_calls / decoded_codes / emitted_samples exact
         assert out.shape == ref_out.shape == (N[i] * 1764,)            # sample_diff == 0 (stream-compare.cpp:258-262)
-        assert snr_db(out, ref_out) > 58.0, snr_db(out, ref_out)
+        assert np.array_equal(out, ref_out)                            # same decoder under both policies: same bits
         s.close()
     # StreamProfile's codec_sec + istft_sec: one timed device pass per round in which a cadence fired
     sec1, passes1 = codec.stream_seconds()
@@ -264,9 +264,8 @@ def test_c3_and_c5_full_batches_sampled_against_live_reference(assets, codec):
             assert got.shape == alone.shape and np.array_equal(got, alone), (name, b)
             if R is not None:
                 w_ref = R.decode_wave(codes[cu[b]:cu[b + 1]], vt[vids[b]])
-                s = snr_db(got, w_ref)
-                print(f"{name} utterance {b} ({int(cu[b + 1] - cu[b])} codes): SNR {s:.1f} dB, max-abs {np.abs(got - w_ref).max():.2e}")
-                assert w_ref.shape == got.shape and s > WAVE_SNR_MIN, (name, b, s)
+                assert w_ref.shape == got.shape
+                assert_at_parity_floor(got, w_ref, assets[0], codes[cu[b]:cu[b + 1]], vt[vids[b]], f"{name} utterance {b} ({int(cu[b + 1] - cu[b])} codes)")
         if R is not None:
             R.close()
 

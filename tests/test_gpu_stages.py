@@ -84,11 +84,13 @@ def test_stage_teacher_forced(tf_codec, oracle_taps, case, inputs, output, rows_
 
 
 def test_teacher_forcing_is_transparent(tf_codec, oracle_taps):
-    """Injecting a tap's own snapshot must not change anything downstream (the override lands where the kernels read)."""
+    """Injecting a tap's own snapshot must not change anything downstream (the override lands where the kernels read).
+    fp32 and fp16-operand taps only: a split (hi, lo) tap is re-split on the host, and when lo is an fp16 subnormal the same
+    VALUE hi + lo can come back as a different (hi, lo) pair — the same number to the GEMM's three passes, not the same bits."""
     codes, emb, _ = oracle_taps
     tf_codec.debug_clear()
     base = tf_codec.decode_wave(codes, emb)
-    snap = {n: tf_codec.debug_read(n) for n in ("upsample", "prior0_h2", "dec3_out", "out_snake")}
+    snap = {n: tf_codec.debug_read(n) for n in ("pre2_out", "upsample", "prior0_h2", "dec3_out", "upres1_h1", "spec")}
     for n, v in snap.items():
         tf_codec.debug_write(n, v)
     try:

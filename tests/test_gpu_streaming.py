@@ -4,12 +4,17 @@ full-prefix re-decode, llround indexing, 1323-sample crossfade; src/test-to-spee
 
 Checked for every stream: emitted sample count == 1764 * codes (stream-compare's sample_diff == 0,
 examples/stream-compare.cpp:258-262) and the StreamProfile counters (decode_calls, decoded_codes, emitted_samples,
-src/test-to-speech.h:28-38) equal the restated policy's.  Checked for a sample of streams: the emitted waveform against
-the policy port driven by single-utterance decodes (MAE / max-abs like stream-compare.cpp:100-124)."""
+src/test-to-speech.h:28-38) equal the reference's own (golden of the UNMODIFIED TestToSpeech::synthesize_stream_profiled
+run with the scripted LLM stub, tests/golden/stream700.npz).  Checked for a sample of streams: the emitted waveform is
+BIT-IDENTICAL to the policy port (oracle/port.stream_policy, itself pinned bit for bit against the reference's
+orchestrator in tests/test_oracle.py) driven by single-utterance decodes of the same decoder.
+
+test_streams_against_the_reference_orchestrator runs the reference's own streaming code live on the host (its CPU codec)
+next to GPU streams fed the same codes: counters exact, waveform at the parity floor."""
 import numpy as np
 import pytest
 
-from conftest import snr_db
+from conftest import load_golden, snr_db
 
 pytestmark = pytest.mark.gpu
 
@@ -54,6 +59,8 @@ def test_c4_1024_streams_700_codes(codec):
                         got[i].append(a)
                     done[i] = last
     calls, dcodes = _policy_counters(N)
+    g = load_golden("stream700")                 # the reference's own orchestrator on a 700-code stream
+    assert (calls, dcodes) == (int(g["decode_calls"]), int(g["decoded_codes"])) == (18, 7160)
     for i, s in enumerate(streams):
         assert done[i], i
         st = s.stats()
@@ -67,6 +74,43 @@ def test_c4_1024_streams_700_codes(codec):
         assert st["decode_calls"] == calls
         err = np.abs(out - ref_out)
         print(f"stream {i}: SNR {snr_db(out, ref_out):.1f} dB, MAE {err.mean():.2e}, max-abs {err.max():.2e}")
-        assert snr_db(out, ref_out) > 55.0
+        assert np.array_equal(out, ref_out)      # batched streaming == the policy over single decodes, bit for bit
     for s in streams:
         s.close()
+
+
+@pytest.mark.parametrize("N", [7, 47, 100, 230])
+def test_streams_against_the_reference_orchestrator(codec, assets, N):
+    """GPU stream vs the reference's OWN streaming session (oracle/_ref: unmodified src/test-to-speech.cpp + stub LLM +
+    the reference's CPU codec) on the same codes: StreamProfile counters exact, sample count exact, waveform at the
+    parity floor (the two codecs differ, the policy must not)."""
+    from miocodec_b200 import synth
+    from oracle import ref
+    g = load_golden(f"stream{N}")
+    codes, vid = g["codes"], int(g["voice"])
+    s = codec.open_stream(synth.synth_voice(vid))
+    got = []
+    for k in range(N):
+        s.push(codes[k])
+        if k == N - 1:
+            s.finish()
+        codec.step_streams([s])
+        a, last = s.read()
+        got.append(a)
+    assert last
+    out = np.concatenate(got)
+    st = s.stats()
+    s.close()
+    assert st == dict(decode_calls=int(g["decode_calls"]), decoded_codes=int(g["decoded_codes"]), emitted_samples=int(g["emitted_samples"]))
+    assert out.shape == (1764 * N,)
+    if ref.available():
+        want, chunks, rst = ref.ref_stream_session(assets[0], assets[1][vid], codes)
+        assert rst["decode_calls"] == st["decode_calls"] and rst["decoded_codes"] == st["decoded_codes"]
+    else:
+        if N > 100:
+            pytest.skip("golden audio is stored for N <= 100 only")
+        want = g["audio"]
+    err = np.abs(out - want)
+    sn = snr_db(out, want)
+    print(f"stream N={N}: vs the reference orchestrator SNR {sn:.2f} dB, MAE {err.mean():.2e}, max-abs {err.max():.2e}")
+    assert sn > 58.0 and err.max() < 4.5e-3

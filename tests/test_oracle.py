@@ -98,3 +98,62 @@ def test_stream_policy_cadence():
     calls.clear()
     out, st = port.stream_policy(fake_decode, np.zeros(7, dtype=np.int32))
     assert calls == [7] and len(out) == 7 * 1764
+
+
+# ---- streaming policy: the port against the reference's OWN orchestrator ---------------------------------------------
+@pytest.mark.parametrize("N", [7, 47, 100, 230, 700])
+def test_stream_policy_matches_reference_golden_counters(N):
+    """Goldens were produced by the UNMODIFIED TestToSpeech::synthesize_stream_profiled (LLM branch, src/test-to-speech.cpp
+    :430-625) with oracle/stub_llama.cpp emitting the codes (tests/golden/make_golden.py).  The port must make the same
+    decisions: decode calls, decoded codes, emitted samples, and the size of every callback chunk."""
+    from oracle import port
+    g = load_golden(f"stream{N}")
+    sizes = []
+
+    def fake_decode(c):
+        return np.zeros(len(c) * 1764, dtype=np.float32)
+
+    out, st = port.stream_policy(fake_decode, g["codes"], chunk_log=sizes)
+    assert st["decode_calls"] == int(g["decode_calls"]) and st["decoded_codes"] == int(g["decoded_codes"])
+    assert st["emitted_samples"] == int(g["emitted_samples"]) == 1764 * N == len(out)
+    assert int(g["llm_tokens"]) == N
+    assert sizes == [int(v) for v in g["chunks"]]
+
+
+@pytest.mark.parametrize("N", [7, 47, 100])
+def test_stream_policy_is_bit_exact_against_the_reference_orchestrator(assets, N):
+    """Same codec (the compiled reference) under both policies: the port's emitted audio must equal the reference
+    orchestrator's bit for bit — cadence, llround indexing, chunking and the crossfade arithmetic (:388-395)."""
+    from miocodec_b200 import synth
+    from oracle import port, ref
+    if not ref.available():
+        pytest.skip("oracle/_ref not built")
+    g = load_golden(f"stream{N}")
+    R = ref.Reference(assets[0])
+    emb = synth.synth_voice(int(g["voice"]))
+    out, st = port.stream_policy(lambda c: R.decode_wave(c, emb), g["codes"])
+    meta = dict(l.strip().split("=", 1) for l in open(os.path.join(GOLDEN, "meta.txt")))
+    if R.variant == meta["variant"]:
+        assert np.array_equal(out, g["audio"])
+        assert hashlib.sha256(out.tobytes()).digest() == bytes(g["audio_sha256"])
+    else:
+        assert out.shape == g["audio"].shape and snr_db(out, g["audio"]) > 57.0
+    R.close()
+
+
+def test_reference_orchestrator_live_session(assets):
+    """The reference's own streaming code runs here (stub LLM): a live session reproduces its golden, and its skip_llm
+    branch (:419-428) equals the offline decode bit for bit."""
+    from miocodec_b200 import synth
+    from oracle import ref
+    if not ref.available():
+        pytest.skip("oracle/_ref not built")
+    g = load_golden("stream100")
+    vid = int(g["voice"])
+    audio, chunks, st = ref.ref_stream_session(assets[0], assets[1][vid], g["codes"])
+    assert [int(v) for v in chunks] == [int(v) for v in g["chunks"]]
+    assert (st["decode_calls"], st["decoded_codes"], st["emitted_samples"], st["llm_tokens"], st["last_flags"]) == (3, 260, 176400, 100, 1)
+    R = ref.Reference(assets[0])
+    a2, ch2, st2 = ref.ref_stream_session(assets[0], assets[1][vid], g["codes"][:30], skip_llm=True)
+    assert np.array_equal(a2, R.decode_wave(g["codes"][:30], synth.synth_voice(vid))) and st2["decode_calls"] == 0
+    R.close()

@@ -41,8 +41,9 @@ def part_gemm():
     gguf, _ = synth.ensure_assets()
     rng = np.random.default_rng(0)
     print("== gemm: product kernel vs fp64 on the same operands (M=512, N=256; rel = rms(err)/rms(out); bias = mean(err*sign(out))/rms(out))")
-    for mode in ("tc", "simt"):
-        c = binding.MioCodec(gguf, 0, gemm=mode)
+    for mode in ("tc", "tc_chunked", "simt"):
+        c = binding.MioCodec(gguf, 0, gemm=mode.split("_")[0])
+        c.set_option("chunk_acc", "all" if mode == "tc_chunked" else "off")
         for K in (128, 512, 768, 2048):
             A = rng.standard_normal((512, K)).astype(np.float32)
             B = (rng.standard_normal((256, K)) / np.sqrt(K)).astype(np.float32)
@@ -57,7 +58,7 @@ def part_gemm():
                     kept = full = true = ah @ bh.T
                 rms = np.sqrt(np.mean(true ** 2))
                 e_k, e_t = out - kept, out - true
-                print(f"  {mode:4s} K={K:5d} npass={npass}: vs kept terms rel {np.sqrt(np.mean(e_k ** 2)) / rms:.3e} bias {np.mean(e_k * np.sign(kept)) / rms:+.3e}"
+                print(f"  {mode:10s} K={K:5d} npass={npass}: vs kept terms rel {np.sqrt(np.mean(e_k ** 2)) / rms:.3e} bias {np.mean(e_k * np.sign(kept)) / rms:+.3e}"
                       f" | vs fp32 operands rel {np.sqrt(np.mean(e_t ** 2)) / rms:.3e} | dropped lo*lo rel {np.sqrt(np.mean((kept - full) ** 2)) / rms:.3e}"
                       f" | operand split rel {np.sqrt(np.mean((full - true) ** 2)) / rms:.3e}", flush=True)
         if mode == "tc":
@@ -101,25 +102,29 @@ def part_stages(T=100):
     s32, i32 = port.decode(W, hp, codes, emb, want_inter=True)
     i32["spec"] = s32
     got = {}
-    for mode in ("tc", "simt"):
-        c = binding.MioCodec(gguf, 0, gemm=mode)
+    for mode in ("tc", "tc_nochunk", "simt"):
+        c = binding.MioCodec(gguf, 0, gemm=mode.split("_")[0])
+        if mode == "tc_nochunk":
+            c.set_option("chunk_acc", "off")
         c.set_option("debug_snapshots", "1")
         c.decode_wave(codes, emb)
         got[mode] = {n: c.debug_read(n) for n, _ in STAGE_TAPS}
         c.close()
     print(f"== stages: SNR (dB) against the fp64 evaluation of the graph, T={T}")
-    print(f"  {'tap':14s} {'tcgen05':>9s} {'simt':>9s} {'fp32 port':>10s}")
+    print(f"  {'tap':14s} {'tcgen05':>9s} {'unchunked':>9s} {'simt':>9s} {'fp32 port':>10s}")
     for name, r in STAGE_TAPS:
         ref = i64[name]
         row = []
-        for mode in ("tc", "simt"):
+        for mode in ("tc", "tc_nochunk", "simt"):
             g = got[mode][name].reshape(-1, ref.shape[1])[: T * r]
             row.append(snr(g, ref))
-        print(f"  {name:14s} {row[0]:9.1f} {row[1]:9.1f} {snr(i32[name], ref):10.1f}", flush=True)
+        print(f"  {name:14s} {row[0]:9.1f} {row[1]:9.1f} {row[2]:9.1f} {snr(i32[name], ref):10.1f}", flush=True)
 
 
 VARIANTS = {
     "tc": {},
+    "tc_unchunked": {"MIO_CHUNK_ACC": "off"},
+    "tc_chunk_all": {"MIO_CHUNK_ACC": "all"},
     "simt": {"MIO_GEMM": "simt"},
     "attn_simt": {"MIO_ATTN": "simt"},
     "gn_precise": {"MIO_GN_PRECISE": "1"},
