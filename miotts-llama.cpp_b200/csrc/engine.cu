@@ -119,7 +119,7 @@ engine::~engine() {
     F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_part); F(gn_mr); F(voice_silu); F(attn_b1); F(attn_b2); F(err_flag);
     F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_seg_cu); F(d_out_off); F(d_voice_table); F(d_wave);
     for (void * p : w_allocs) F(p);
-    F(d_emit); F(d_emit_jobs); F(d_pcm); F(w.rope_pre); F(w.rope_t);
+    F(d_emit); F(d_emit_jobs); F(d_pcm); F(w.rope_pre); F(w.rope_t); F(istft_spec);
     if (h_emit) cudaFreeHost(h_emit);
     if (h_stage) cudaFreeHost(h_stage);
     if (stream && own_stream) cudaStreamDestroy(stream);
@@ -577,8 +577,8 @@ std::string engine::ensure_workspace() {
     const size_t R1 = (size_t) max_rows1, R2 = 2 * R1, R6 = 6 * R1, R18 = 18 * R1;
     std::string e;
 #define A(ptr, n) if (!(e = dev_alloc(&ptr, (size_t) (n))).empty()) return e;
-    if (istft_only) {   // mio_istft_ctx_create: only the spectrogram staging buffer is needed
-        A(spec, R18 * SPEC_LD); A(err_flag, 1);
+    if (istft_only) {   // mio_istft_ctx_create: no decoder workspace (run_istft_only grows its own staging buffer)
+        A(err_flag, 1);
         CK(cudaMemset(err_flag, 0, sizeof(int)));
         ws_ready = true;
         return {};
@@ -1264,12 +1264,20 @@ std::string engine::fetch_spec(int utt, float * out, int64_t cap) {
 
 // standalone ISTFT of a host spectrogram (mio_istft): one utterance of n_frames frames
 std::string engine::run_istft_only(const float * spec_host, int n_frames) {
-    std::string e = ensure_workspace();
-    if (!e.empty()) return e;
+    std::string e;
     CK(cudaSetDevice(device));
-    const int fpc = hp.frames_per_code;
     if (n_frames <= 0) return "bad argument";
-    if ((int64_t) n_frames > (int64_t) max_rows1 * fpc) return "too many frames for the workspace";
+    if (!err_flag) { if (!(e = dev_alloc(&err_flag, 1)).empty()) return e; CK(cudaMemset(err_flag, 0, sizeof(int))); }
+    // own staging buffer, grown with the call: never the decoder's workspace (mio_istft on a codec context must not
+    // need 8 GB of activations, and an ISTFT-only context stays a few MB)
+    if ((int64_t) istft_spec_rows < (int64_t) n_frames) {
+        if (stream) CK(cudaStreamSynchronize(stream));
+        if (istft_spec) cudaFree(istft_spec);
+        istft_spec = nullptr;
+        istft_spec_rows = (size_t) n_frames + (size_t) n_frames / 4 + 64;
+        if (!(e = dev_alloc(&istft_spec, istft_spec_rows * SPEC_LD)).empty()) { istft_spec_rows = 0; return e; }
+    }
+    float * const spec = istft_spec;                       // shadows the decoder's spectrogram buffer in this function
     batch_uploaded = false; batch_ran = false;
     // layout: a single pseudo-utterance whose length is counted in frames (frames_per_code = 1)
     const int32_t start0 = 0, len0 = n_frames;

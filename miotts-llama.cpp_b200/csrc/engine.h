@@ -132,6 +132,7 @@ struct engine {
     cudaEvent_t tune_ev[4] = {nullptr, nullptr, nullptr, nullptr};
     int fetch_chunk_codes = 1 << 20; // optional extra cap on the chunk size of the host-delivery pipeline
     std::string run_istft_only(const float * spec_host, int n_frames);   // mio_istft
+    float * istft_spec = nullptr; size_t istft_spec_rows = 0;            // its staging buffer (grown on demand)
     std::string sync();                                   // stream sync + error flag
     std::string fetch_wave(float * out, int64_t cap);
     std::string fetch_spec(int utt, float * out, int64_t cap);

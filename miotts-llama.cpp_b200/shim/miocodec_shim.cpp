@@ -8,7 +8,6 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
-#include <mutex>
 
 #include "../../include/miocodec_b200.h"
 
@@ -17,14 +16,21 @@ struct miocodec_context {
 };
 
 namespace {
-std::mutex g_mu;
-std::vector<miocodec_context *> g_live;      // contexts created by miocodec_load, most recent last
-mio_ctx * g_istft_ctx = nullptr;             // lazily created when istft() is called with no codec loaded
-
 int device_ordinal() {
     const char * e = getenv("MIO_DEVICE");
     return e ? atoi(e) : 0;
 }
+
+// istft() of the reference is a pure, thread-safe free function of (spec, cache) (src/istft.h:38-42).  It therefore gets
+// its OWN ISTFT-only device context per calling thread (a few MB: tables + a spectrogram staging buffer that grows with
+// the call), never a codec context: a concurrent miocodec_decode / streaming session / miocodec_free on another thread
+// cannot be disturbed by it, and it works before any codec is loaded.
+struct istft_thread_ctx {
+    mio_ctx * c = nullptr;
+    int device = -1;
+    ~istft_thread_ctx() { if (c) mio_ctx_destroy(c); }
+};
+thread_local istft_thread_ctx t_istft;
 }  // namespace
 
 miocodec_context * miocodec_load(const std::string & model_path) {
@@ -35,17 +41,11 @@ miocodec_context * miocodec_load(const std::string & model_path) {
     }
     miocodec_context * ctx = new miocodec_context();
     ctx->c = c;
-    std::lock_guard<std::mutex> lk(g_mu);
-    g_live.push_back(ctx);
     return ctx;
 }
 
 void miocodec_free(miocodec_context * ctx) {
     if (!ctx) return;
-    {
-        std::lock_guard<std::mutex> lk(g_mu);
-        g_live.erase(std::remove(g_live.begin(), g_live.end(), ctx), g_live.end());
-    }
     mio_ctx_destroy(ctx->c);
     delete ctx;
 }
@@ -157,18 +157,17 @@ std::vector<float> istft(const float * spec, int n_frames, int hop_length, const
                 cache.n_fft(), cache.win_length(), hop_length);
         return {};
     }
-    mio_ctx * c = nullptr;
-    {
-        std::lock_guard<std::mutex> lk(g_mu);
-        if (!g_live.empty()) c = g_live.back()->c;
-        else {
-            if (!g_istft_ctx && mio_istft_ctx_create(device_ordinal(), &g_istft_ctx) != MIO_OK) {
-                fprintf(stderr, "istft: %s\n", mio_last_error());
-                return {};
-            }
-            c = g_istft_ctx;
+    const int dev = device_ordinal();
+    if (t_istft.c && t_istft.device != dev) { mio_ctx_destroy(t_istft.c); t_istft.c = nullptr; }
+    if (!t_istft.c) {
+        if (mio_istft_ctx_create(dev, &t_istft.c) != MIO_OK) {
+            fprintf(stderr, "istft: %s\n", mio_last_error());
+            t_istft.c = nullptr;
+            return {};
         }
+        t_istft.device = dev;
     }
+    mio_ctx * c = t_istft.c;
     std::vector<float> wave((size_t) n_frames * (size_t) hop_length);
     int64_t n = 0;
     if (mio_istft(c, spec, n_frames, wave.data(), (int64_t) wave.size(), &n) != MIO_OK) {

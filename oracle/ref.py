@@ -156,6 +156,20 @@ def ref_stream_session(gguf_path: str, voice_path: str, codes, skip_llm: bool = 
     return out[:n].copy(), chunks[: nch.value].copy(), stats
 
 
+def ref_istft_tables(n_fft: int = 392, win_length: int = 392) -> dict:
+    """The tables of the reference's istft_cache (src/istft.cpp:7-41), through its own getters."""
+    L = C.CDLL(lib_path())
+    L.mio_ref_istft_tables.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    dims = np.zeros(4, dtype=np.int32)
+    n_mid = max(0, n_fft // 2 + 1 - 2)
+    cos_t = np.empty(n_fft * n_mid, dtype=np.float32)
+    sin_t = np.empty_like(cos_t)
+    nyq = np.empty(n_fft, dtype=np.float32)
+    hann = np.empty(win_length, dtype=np.float32)
+    L.mio_ref_istft_tables(n_fft, win_length, cos_t.ctypes.data, sin_t.ctypes.data, nyq.ctypes.data, hann.ctypes.data, dims.ctypes.data)
+    return dict(dims=tuple(int(v) for v in dims), cos=cos_t, sin=sin_t, nyq=nyq, hann=hann)
+
+
 def ref_istft_only(spec: np.ndarray, n_fft: int = 392, hop: int = 98) -> np.ndarray:
     """istft() of the reference without a codec context."""
     p = lib_path()

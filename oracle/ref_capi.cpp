@@ -89,6 +89,18 @@ long mio_ref_istft(const float * spec, int n_frames, int n_fft, int hop, float *
     return (long) a.size();
 }
 
+// the tables of the reference's istft_cache (src/istft.cpp:7-41), copied out through its own getters.
+// Returns n_mid; cos/sin need n_fft * n_mid floats, nyq n_fft, hann win_length.
+int mio_ref_istft_tables(int n_fft, int win_length, float * cos_t, float * sin_t, float * nyq, float * hann, int * dims /*[4]*/) {
+    istft_cache c(n_fft, win_length);
+    if (dims) { dims[0] = c.n_fft(); dims[1] = c.win_length(); dims[2] = c.n_freq(); dims[3] = c.n_mid(); }
+    if (cos_t) memcpy(cos_t, c.cos_table().data(), c.cos_table().size() * sizeof(float));
+    if (sin_t) memcpy(sin_t, c.sin_table().data(), c.sin_table().size() * sizeof(float));
+    if (nyq) memcpy(nyq, c.nyquist_sign().data(), c.nyquist_sign().size() * sizeof(float));
+    if (hann) memcpy(hann, c.hann_window().data(), c.hann_window().size() * sizeof(float));
+    return c.n_mid();
+}
+
 // codes -> waveform, exactly what decode_codes_to_audio times
 // (src/test-to-speech.cpp:264-287), peak normalisation off.
 long mio_ref_decode_wave(void * ctx, const int * codes, int n_codes, const float * emb,

@@ -81,11 +81,13 @@ def reference_floor(gguf, codes, emb):
 
 
 def assert_at_parity_floor(wave, w_ref, gguf, codes, emb, what=""):
-    """The GPU waveform must be as close to the reference as the reference's other build is: SNR >= floor - 0.5 dB (and
-    never below 58.5), max-abs <= 1.25 x the larger of this utterance's floor max-abs and the recorded one."""
+    """The GPU waveform must be as close to the reference as the reference's other build is.  One utterance is a noisy
+    statistic (sd 0.25 dB for the floor AND for any second implementation, profiles/r2d/e2e.log), so a single utterance is
+    held to floor - 1.0 dB (never below 58.5) and 1.25 x the larger of its own floor max-abs and the recorded one; the
+    MEAN over 32 utterances is held to 0.6 dB in tests/test_gpu_parity.py::test_mean_parity_over_32_utterances."""
     f_snr, f_max = reference_floor(gguf, codes, emb)
     s, m = snr_db(wave, w_ref), float(np.abs(wave - w_ref).max())
     print(f"{what}: SNR {s:.2f} dB (floor {f_snr:.2f}), max-abs {m:.2e} (floor {f_max:.2e}), peak {np.abs(w_ref).max():.2f}")
-    assert s > max(58.5, min(f_snr, 60.0) - 0.5), (what, s, f_snr)
+    assert s > max(58.5, min(f_snr, 60.0) - 1.0), (what, s, f_snr)
     assert m < 1.25 * max(f_max, FLOOR_MAXABS), (what, m, f_max)
     return s

@@ -20,6 +20,15 @@ static bool write_f32(const std::string & path, const std::vector<float> & v) {
 }
 
 int main(int argc, char ** argv) {
+    // shim_demo --dump-tables <n_fft> <win_length> <out_prefix>: the istft_cache tables (host-side, needs no GPU), for the
+    // value-by-value comparison with the reference's istft_cache (tests/test_shim.py)
+    if (argc == 5 && std::string(argv[1]) == "--dump-tables") {
+        istft_cache c(atoi(argv[2]), atoi(argv[3]));
+        const std::string pre = argv[4];
+        printf("n_fft=%d win_length=%d n_freq=%d n_mid=%d\n", c.n_fft(), c.win_length(), c.n_freq(), c.n_mid());
+        return (write_f32(pre + ".cos.f32", c.cos_table()) && write_f32(pre + ".sin.f32", c.sin_table()) &&
+                write_f32(pre + ".nyq.f32", c.nyquist_sign()) && write_f32(pre + ".hann.f32", c.hann_window())) ? 0 : 1;
+    }
     if (argc < 5) { fprintf(stderr, "usage: %s model.gguf voice.emb.gguf codes.i32 out_prefix\n", argv[0]); return 2; }
     const std::string prefix = argv[4];
     // istft() must work before any codec is loaded (it is a free function in the reference)
