@@ -3,6 +3,7 @@
 
 #include <cstdio>
 #include <cstring>
+#include <exception>
 #include <new>
 #include <string>
 
@@ -31,6 +32,19 @@ static int classify(const std::string & e) {
     if (e.find("before") != std::string::npos) return MIO_ERR_STATE;
     return MIO_ERR_CUDA;
 }
+// No exception may cross the C ABI: host allocations (std::vector growth on a huge batch, std::string) can throw.
+template <class F>
+static int guarded(F && body) {
+    try {
+        return body();
+    } catch (const std::bad_alloc &) {
+        return fail(MIO_ERR_ARG, "out of host memory");
+    } catch (const std::exception & e) {
+        return fail(MIO_ERR_ARG, std::string("internal error: ") + e.what());
+    } catch (...) {
+        return fail(MIO_ERR_ARG, "internal error");
+    }
+}
 #define TRY(expr)                                          \
     do {                                                   \
         std::string _e = (expr);                           \
@@ -43,37 +57,41 @@ const char * mio_last_error(void) { return g_err.c_str(); }
 const char * mio_version(void) { return "miocodec_b200 0.1 (sm_100a)"; }
 
 int mio_ctx_create(const char * gguf_path, int device, mio_ctx ** out_ctx) {
-    if (!gguf_path || !out_ctx) return fail(MIO_ERR_ARG, "bad argument");
-    *out_ctx = nullptr;
-    {   // file problems are reported before any CUDA call so the error is meaningful on machines without a GPU
-        gguf_file probe;
-        std::string e = probe.open(gguf_path);
-        if (!e.empty()) return fail(classify(e), e);
-    }
-    mio_ctx * c = new (std::nothrow) mio_ctx();
-    if (!c) return fail(MIO_ERR_ARG, "out of host memory");
-    std::string e = c->E.load(gguf_path, device);
-    if (!e.empty()) {
-        delete c;
-        return fail(classify(e), e);
-    }
-    if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "simt")) c->E.use_simt = true;
-    *out_ctx = c;
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!gguf_path || !out_ctx) return fail(MIO_ERR_ARG, "bad argument");
+        *out_ctx = nullptr;
+        {   // file problems are reported before any CUDA call so the error is meaningful on machines without a GPU
+            gguf_file probe;
+            std::string e = probe.open(gguf_path);
+            if (!e.empty()) return fail(classify(e), e);
+        }
+        mio_ctx * c = new (std::nothrow) mio_ctx();
+        if (!c) return fail(MIO_ERR_ARG, "out of host memory");
+        std::string e = c->E.load(gguf_path, device);
+        if (!e.empty()) {
+            delete c;
+            return fail(classify(e), e);
+        }
+        if (getenv("MIO_GEMM") && !strcmp(getenv("MIO_GEMM"), "simt")) c->E.use_simt = true;
+        *out_ctx = c;
+        return MIO_OK;
+    });
 }
 
 int mio_istft_ctx_create(int device, mio_ctx ** out_ctx) {
-    if (!out_ctx) return fail(MIO_ERR_ARG, "bad argument");
-    *out_ctx = nullptr;
-    mio_ctx * c = new (std::nothrow) mio_ctx();
-    if (!c) return fail(MIO_ERR_ARG, "out of host memory");
-    std::string e = c->E.init_istft_only(device);
-    if (!e.empty()) {
-        delete c;
-        return fail(classify(e), e);
-    }
-    *out_ctx = c;
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!out_ctx) return fail(MIO_ERR_ARG, "bad argument");
+        *out_ctx = nullptr;
+        mio_ctx * c = new (std::nothrow) mio_ctx();
+        if (!c) return fail(MIO_ERR_ARG, "out of host memory");
+        std::string e = c->E.init_istft_only(device);
+        if (!e.empty()) {
+            delete c;
+            return fail(classify(e), e);
+        }
+        *out_ctx = c;
+        return MIO_OK;
+    });
 }
 
 void mio_ctx_destroy(mio_ctx * ctx) { delete ctx; }
@@ -144,29 +162,33 @@ int mio_ctx_set_stream(mio_ctx * c, void * cuda_stream) {
 }
 
 int mio_voice_load(const char * path, float * out, int cap) {
-    if (!path || !out) return fail(MIO_ERR_ARG, "bad argument");
-    gguf_file g;
-    std::string e = g.open(path);
-    if (!e.empty()) return fail(classify(e), e);
-    if (g.tensors.empty()) return fail(MIO_ERR_FORMAT, std::string("no tensors in ") + path);
-    const gguf_tensor & t = g.tensors[0];               // "the first tensor", src/miocodec.cpp:825
-    if (t.dtype != GT_F32) return fail(MIO_ERR_FORMAT, "unsupported voice embedding type (F32 only)");   // :840-847
-    const int64_t n = t.nelements();
-    if (n > cap) return fail(MIO_ERR_ARG, "capacity too small");
-    if (!g.read_raw(t, out, (size_t) n * sizeof(float))) return fail(MIO_ERR_IO, "short read");
-    return (int) n;
+    return guarded([&]() -> int {
+        if (!path || !out) return fail(MIO_ERR_ARG, "bad argument");
+        gguf_file g;
+        std::string e = g.open(path);
+        if (!e.empty()) return fail(classify(e), e);
+        if (g.tensors.empty()) return fail(MIO_ERR_FORMAT, std::string("no tensors in ") + path);
+        const gguf_tensor & t = g.tensors[0];               // "the first tensor", src/miocodec.cpp:825
+        if (t.dtype != GT_F32) return fail(MIO_ERR_FORMAT, "unsupported voice embedding type (F32 only)");   // :840-847
+        const int64_t n = t.nelements();
+        if (n > cap) return fail(MIO_ERR_ARG, "capacity too small");
+        if (!g.read_raw(t, out, (size_t) n * sizeof(float))) return fail(MIO_ERR_IO, "short read");
+        return (int) n;
+    });
 }
 
 int mio_print_tensors(const char * path) {
-    if (!path) return fail(MIO_ERR_ARG, "bad argument");
-    gguf_file g;
-    std::string e = g.open(path);
-    if (!e.empty()) return fail(classify(e), e);
-    printf("Tensors in %s: %lld\n", path, (long long) g.tensors.size());
-    for (const gguf_tensor & t : g.tensors)
-        printf("  %-60s [%5lld, %5lld, %5lld, %5lld] type=%d\n", t.name.c_str(), (long long) t.ne[0], (long long) t.ne[1],
-               (long long) t.ne[2], (long long) t.ne[3], (int) t.dtype);
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!path) return fail(MIO_ERR_ARG, "bad argument");
+        gguf_file g;
+        std::string e = g.open(path);
+        if (!e.empty()) return fail(classify(e), e);
+        printf("Tensors in %s: %lld\n", path, (long long) g.tensors.size());
+        for (const gguf_tensor & t : g.tensors)
+            printf("  %-60s [%5lld, %5lld, %5lld, %5lld] type=%d\n", t.name.c_str(), (long long) t.ne[0], (long long) t.ne[1],
+                   (long long) t.ne[2], (long long) t.ne[3], (int) t.dtype);
+        return MIO_OK;
+    });
 }
 
 static int upload_one(mio_ctx * c, const int32_t * codes, int n_codes, const float * emb) {
@@ -179,52 +201,62 @@ static int upload_one(mio_ctx * c, const int32_t * codes, int n_codes, const flo
 
 int mio_decode_spec(mio_ctx * c, const int32_t * codes, int n_codes, const float * emb, float * spec_out, int64_t cap,
                     int * out_n_frames) {
-    if (!c) return fail(MIO_ERR_ARG, "bad argument");
-    const int nf = n_codes * c->E.hp.frames_per_code;
-    if (out_n_frames) *out_n_frames = nf;
-    if (!spec_out) return MIO_OK;
-    if (cap < (int64_t) nf * 2 * c->E.hp.n_freq) return fail(MIO_ERR_ARG, "capacity too small");
-    int r = upload_one(c, codes, n_codes, emb);
-    if (r != MIO_OK) return r;
-    TRY(c->E.run(false));
-    TRY(c->E.fetch_spec(0, spec_out, cap));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c) return fail(MIO_ERR_ARG, "bad argument");
+        const int nf = n_codes * c->E.hp.frames_per_code;
+        if (out_n_frames) *out_n_frames = nf;
+        if (!spec_out) return MIO_OK;
+        if (cap < (int64_t) nf * 2 * c->E.hp.n_freq) return fail(MIO_ERR_ARG, "capacity too small");
+        int r = upload_one(c, codes, n_codes, emb);
+        if (r != MIO_OK) return r;
+        TRY(c->E.run(false));
+        TRY(c->E.fetch_spec(0, spec_out, cap));
+        return MIO_OK;
+    });
 }
 
 int mio_istft(mio_ctx * c, const float * spec, int n_frames, float * wave_out, int64_t cap, int64_t * out_n) {
-    if (!c || !spec || !wave_out || n_frames <= 0) return fail(MIO_ERR_ARG, "bad argument");
-    const int64_t n = (int64_t) n_frames * c->E.hp.hop;
-    if (out_n) *out_n = n;
-    if (cap < n) return fail(MIO_ERR_ARG, "capacity too small");
-    TRY(c->E.run_istft_only(spec, n_frames));
-    TRY(c->E.fetch_wave(wave_out, cap));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c || !spec || !wave_out || n_frames <= 0) return fail(MIO_ERR_ARG, "bad argument");
+        const int64_t n = (int64_t) n_frames * c->E.hp.hop;
+        if (out_n) *out_n = n;
+        if (cap < n) return fail(MIO_ERR_ARG, "capacity too small");
+        TRY(c->E.run_istft_only(spec, n_frames));
+        TRY(c->E.fetch_wave(wave_out, cap));
+        return MIO_OK;
+    });
 }
 
 int mio_decode_wave(mio_ctx * c, const int32_t * codes, int n_codes, const float * emb, int peak_normalize,
                     float * wave_out, int64_t cap, int64_t * out_n) {
-    if (!c || !wave_out) return fail(MIO_ERR_ARG, "bad argument");
-    if (n_codes == 0) { if (out_n) *out_n = 0; return MIO_OK; }     // decode_codes_to_audio: n_codes <= 0 -> empty, true
-    const int64_t n = (int64_t) n_codes * c->E.hp.samples_per_token;
-    if (out_n) *out_n = n;
-    if (cap < n) return fail(MIO_ERR_ARG, "capacity too small");
-    int r = upload_one(c, codes, n_codes, emb);
-    if (r != MIO_OK) return r;
-    TRY(c->E.run(peak_normalize != 0));
-    TRY(c->E.fetch_wave(wave_out, cap));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c || !wave_out) return fail(MIO_ERR_ARG, "bad argument");
+        if (n_codes == 0) { if (out_n) *out_n = 0; return MIO_OK; }     // decode_codes_to_audio: n_codes <= 0 -> empty, true
+        const int64_t n = (int64_t) n_codes * c->E.hp.samples_per_token;
+        if (out_n) *out_n = n;
+        if (cap < n) return fail(MIO_ERR_ARG, "capacity too small");
+        int r = upload_one(c, codes, n_codes, emb);
+        if (r != MIO_OK) return r;
+        TRY(c->E.run(peak_normalize != 0));
+        TRY(c->E.fetch_wave(wave_out, cap));
+        return MIO_OK;
+    });
 }
 
 int mio_batch_upload(mio_ctx * c, const int32_t * codes, const int32_t * cu, int n_utts, const float * vt, int nv,
                      const int32_t * vids) {
-    if (!c) return fail(MIO_ERR_ARG, "bad argument");
-    TRY(c->E.upload(codes, cu, n_utts, vt, nv, vids));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c) return fail(MIO_ERR_ARG, "bad argument");
+        TRY(c->E.upload(codes, cu, n_utts, vt, nv, vids));
+        return MIO_OK;
+    });
 }
 int mio_batch_run(mio_ctx * c, int peak_normalize) {
-    if (!c) return fail(MIO_ERR_ARG, "bad argument");
-    TRY(c->E.run(peak_normalize != 0));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c) return fail(MIO_ERR_ARG, "bad argument");
+        TRY(c->E.run(peak_normalize != 0));
+        return MIO_OK;
+    });
 }
 int mio_batch_sync(mio_ctx * c) {
     if (!c) return fail(MIO_ERR_ARG, "bad argument");
@@ -232,36 +264,44 @@ int mio_batch_sync(mio_ctx * c) {
     return MIO_OK;
 }
 int mio_batch_fetch(mio_ctx * c, float * out, int64_t cap) {
-    if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
-    TRY(c->E.fetch_wave(out, cap));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
+        TRY(c->E.fetch_wave(out, cap));
+        return MIO_OK;
+    });
 }
 int64_t mio_batch_kernel_launches(const mio_ctx * c) { return c ? c->E.launches : 0; }
 void * mio_batch_wave_device(mio_ctx * c) { return c ? (void *) c->E.d_wave : nullptr; }
 
 int mio_decode_wave_batch(mio_ctx * c, const int32_t * codes, const int32_t * cu, int n_utts, const float * vt, int nv,
                           const int32_t * vids, int peak_normalize, float * out, int64_t cap) {
-    if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
-    // pipelined delivery (engine::upload: chunks as large as the workspace allows + one tail split); chunk i's D2H copy runs on a
-    // second stream while chunk i+1 computes
-    TRY(c->E.upload(codes, cu, n_utts, vt, nv, vids, c->E.fetch_chunk_codes + c->E.fetch_chunk_codes / 16));
-    if (cap < c->E.wave_samples) return fail(MIO_ERR_ARG, "capacity too small");
-    TRY(c->E.run(peak_normalize != 0, out));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
+        // pipelined delivery (engine::upload: chunks as large as the workspace allows + one tail split); chunk i's D2H copy runs on a
+        // second stream while chunk i+1 computes
+        TRY(c->E.upload(codes, cu, n_utts, vt, nv, vids, c->E.fetch_chunk_codes + c->E.fetch_chunk_codes / 16));
+        if (cap < c->E.wave_samples) return fail(MIO_ERR_ARG, "capacity too small");
+        TRY(c->E.run(peak_normalize != 0, out));
+        return MIO_OK;
+    });
 }
 
 int mio_decode_pcm16_batch(mio_ctx * c, const int32_t * codes, const int32_t * cu, int n_utts, const float * vt, int nv,
                            const int32_t * vids, int peak_normalize, int16_t * out, int64_t cap) {
-    if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
-    TRY(c->E.upload(codes, cu, n_utts, vt, nv, vids, c->E.fetch_chunk_codes + c->E.fetch_chunk_codes / 16));
-    if (cap < c->E.wave_samples) return fail(MIO_ERR_ARG, "capacity too small");
-    TRY(c->E.run(peak_normalize != 0, nullptr, out));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
+        TRY(c->E.upload(codes, cu, n_utts, vt, nv, vids, c->E.fetch_chunk_codes + c->E.fetch_chunk_codes / 16));
+        if (cap < c->E.wave_samples) return fail(MIO_ERR_ARG, "capacity too small");
+        TRY(c->E.run(peak_normalize != 0, nullptr, out));
+        return MIO_OK;
+    });
 }
 int mio_batch_fetch_pcm16(mio_ctx * c, int16_t * out, int64_t cap) {
-    if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
-    TRY(c->E.fetch_pcm16(out, cap));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c || !out) return fail(MIO_ERR_ARG, "bad argument");
+        TRY(c->E.fetch_pcm16(out, cap));
+        return MIO_OK;
+    });
 }
 
 // ---- host-side neighbours of the path
@@ -324,15 +364,17 @@ void mio_stream_default_config(const mio_ctx * c, mio_stream_config * cfg) {
     if (c && cfg) stream_default_config(c->E, cfg);
 }
 int mio_stream_open(mio_ctx * c, const float * emb, const mio_stream_config * cfg, mio_stream ** out) {
-    if (!c || !emb || !out) return fail(MIO_ERR_ARG, "bad argument");
-    *out = nullptr;
-    stream_state * s = nullptr;
-    std::string e = stream_open(c->E, emb, cfg, &s);
-    if (!e.empty()) return fail(classify(e), e);
-    mio_stream * h = new mio_stream();
-    h->S = s;
-    *out = h;
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c || !emb || !out) return fail(MIO_ERR_ARG, "bad argument");
+        *out = nullptr;
+        stream_state * s = nullptr;
+        std::string e = stream_open(c->E, emb, cfg, &s);
+        if (!e.empty()) return fail(classify(e), e);
+        mio_stream * h = new mio_stream();
+        h->S = s;
+        *out = h;
+        return MIO_OK;
+    });
 }
 void mio_stream_close(mio_stream * s) {
     if (!s) return;
@@ -340,9 +382,11 @@ void mio_stream_close(mio_stream * s) {
     delete s;
 }
 int mio_stream_push_codes(mio_stream * s, const int32_t * codes, int n) {
-    if (!s || (!codes && n > 0) || n < 0) return fail(MIO_ERR_ARG, "bad argument");
-    TRY(stream_push(*s->S, codes, n));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!s || (!codes && n > 0) || n < 0) return fail(MIO_ERR_ARG, "bad argument");
+        TRY(stream_push(*s->S, codes, n));
+        return MIO_OK;
+    });
 }
 int mio_stream_finish(mio_stream * s) {
     if (!s) return fail(MIO_ERR_ARG, "bad argument");
@@ -350,11 +394,13 @@ int mio_stream_finish(mio_stream * s) {
     return MIO_OK;
 }
 int mio_streams_step(mio_ctx * c, mio_stream ** streams, int n) {
-    if (!c || (!streams && n > 0) || n < 0) return fail(MIO_ERR_ARG, "bad argument");
-    std::vector<stream_state *> v(n);
-    for (int i = 0; i < n; i++) v[i] = streams[i] ? streams[i]->S : nullptr;
-    TRY(streams_step(c->E, v.data(), n));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c || (!streams && n > 0) || n < 0) return fail(MIO_ERR_ARG, "bad argument");
+        std::vector<stream_state *> v(n);
+        for (int i = 0; i < n; i++) v[i] = streams[i] ? streams[i]->S : nullptr;
+        TRY(streams_step(c->E, v.data(), n));
+        return MIO_OK;
+    });
 }
 int64_t mio_stream_read(mio_stream * s, float * out, int64_t cap, int * is_last) {
     if (!s || (!out && cap > 0)) return fail(MIO_ERR_ARG, "bad argument");
@@ -401,10 +447,12 @@ int mio_profile_read(mio_ctx * c, int cat, double * ms, double * flops, double *
 int64_t mio_batch_h2d_bytes(const mio_ctx * c) { return c ? (int64_t) c->E.h2d_bytes : 0; }
 
 int mio_debug_write(mio_ctx * c, const char * name, const float * data, int64_t n) {
-    if (!c || !name || n < 0 || (!data && n > 0)) return fail(MIO_ERR_ARG, "bad argument");
-    if (n == 0) c->E.overrides.erase(name);
-    else c->E.overrides[name].assign(data, data + n);
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c || !name || n < 0 || (!data && n > 0)) return fail(MIO_ERR_ARG, "bad argument");
+        if (n == 0) c->E.overrides.erase(name);
+        else c->E.overrides[name].assign(data, data + n);
+        return MIO_OK;
+    });
 }
 int mio_debug_clear(mio_ctx * c) {
     if (!c) return fail(MIO_ERR_ARG, "bad argument");
@@ -413,9 +461,11 @@ int mio_debug_clear(mio_ctx * c) {
 }
 
 int mio_debug_gemm(mio_ctx * c, int M, int N, int K, const float * A, const float * B, int npass, float * out) {
-    if (!c) return fail(MIO_ERR_ARG, "bad argument");
-    TRY(c->E.debug_gemm(M, N, K, A, B, npass, out));
-    return MIO_OK;
+    return guarded([&]() -> int {
+        if (!c) return fail(MIO_ERR_ARG, "bad argument");
+        TRY(c->E.debug_gemm(M, N, K, A, B, npass, out));
+        return MIO_OK;
+    });
 }
 
 int64_t mio_debug_read(mio_ctx * c, const char * name, float * out, int64_t cap) {

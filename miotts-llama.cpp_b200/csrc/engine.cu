@@ -1152,6 +1152,17 @@ std::string engine::ensure_pcm() {
 }
 
 std::string engine::run(bool peak_normalize, float * host_dst, int16_t * host_pcm) {
+    std::string e = run_impl(peak_normalize, host_dst, host_pcm);
+    if (!e.empty() && (host_dst || host_pcm)) {
+        // an error in the middle of the delivery pipeline: no D2H copy into the caller's buffer may still be in flight
+        // when the call returns
+        if (copy_stream) cudaStreamSynchronize(copy_stream);
+        if (stream) cudaStreamSynchronize(stream);
+    }
+    return e;
+}
+
+std::string engine::run_impl(bool peak_normalize, float * host_dst, int16_t * host_pcm) {
     if (!batch_uploaded) return "mio_batch_run before mio_batch_upload";
     CK(cudaSetDevice(device));
     launches = 0;

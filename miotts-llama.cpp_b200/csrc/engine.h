@@ -120,6 +120,7 @@ struct engine {
     // second stream as soon as it is complete (overlaps with the next chunk) and return when everything has landed
     // host_pcm != nullptr: the same pipeline delivering PCM16 (converted on the device, half the D2H bytes)
     std::string run(bool peak_normalize, float * host_dst = nullptr, int16_t * host_pcm = nullptr);
+    std::string run_impl(bool peak_normalize, float * host_dst, int16_t * host_pcm);
     std::string fetch_pcm16(int16_t * out, int64_t cap);
     int16_t * d_pcm = nullptr; int64_t pcm_cap = 0;       // PCM16 image of d_wave (grown on demand)
     std::string ensure_pcm();

@@ -1,5 +1,6 @@
 #include "gguf_reader.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 
@@ -137,6 +138,20 @@ std::string gguf_file::open(const std::string & p) {
     if (!r.ok) return "corrupt GGUF tensor index: " + p;
     long pos = ftell(r.f);
     data_offset = ((uint64_t) pos + alignment - 1) / alignment * alignment;
+    // every tensor must lie inside the file: sizes and offsets come from the file and are used for allocations and
+    // seeks later (a negative / huge extent must fail here with an error code, not as bad_alloc across the C ABI)
+    if (fseek(r.f, 0, SEEK_END) != 0) return "corrupt GGUF file: " + p;
+    const uint64_t file_size = (uint64_t) ftell(r.f);
+    for (const gguf_tensor & t : tensors) {
+        uint64_t n = 1;
+        for (uint32_t d = 0; d < 4; d++) {
+            if (t.ne[d] < 0 || (t.ne[d] > 0 && n > (1ull << 40) / (uint64_t) t.ne[d])) return "corrupt GGUF tensor extent (" + t.name + "): " + p;
+            n *= (uint64_t) t.ne[d];
+        }
+        const uint64_t bytes = (uint64_t) t.nbytes();     // 0 for dtypes this reader does not handle (rejected when read)
+        if (t.offset > file_size || data_offset > file_size || bytes > file_size - std::min(file_size, data_offset + t.offset))
+            return "corrupt GGUF tensor data range (" + t.name + "): " + p;
+    }
     return {};
 }
 

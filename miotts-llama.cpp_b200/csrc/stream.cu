@@ -127,6 +127,8 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
             if (streams[i] && streams[i]->job_head < streams[i]->jobs.size()) act.push_back(streams[i]);
         if (act.empty()) break;
         const auto t_pass0 = std::chrono::steady_clock::now();
+        // a round holds at most max_voices streams (one conditioning row each); the rest fire in the next round of this
+        // same call (the for(;;) loop runs until no stream has a pending job), so nothing is dropped
         if ((int) act.size() > E.max_voices) act.resize(E.max_voices);
         std::vector<int32_t> codes, cu(1, 0), vid;
         std::vector<float> vt;
@@ -161,11 +163,19 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
             if (E.d_emit) cudaFree(E.d_emit);
             if (E.d_emit_jobs) cudaFree(E.d_emit_jobs);
             if (E.h_emit) cudaFreeHost(E.h_emit);
-            E.emit_cap = emit_total + emit_total / 4 + 4096;
-            E.emit_jobs_cap = (int64_t) jobs.size() + 64;
-            if (cudaMalloc(&E.d_emit, (size_t) E.emit_cap * sizeof(float)) != cudaSuccess ||
-                cudaMalloc(&E.d_emit_jobs, (size_t) E.emit_jobs_cap * sizeof(emit_job)) != cudaSuccess ||
-                cudaMallocHost(&E.h_emit, (size_t) E.emit_cap * sizeof(float)) != cudaSuccess) return "cudaMalloc failed (emit buffers)";
+            E.d_emit = E.d_emit_jobs = E.h_emit = nullptr;          // a failed allocation below must not leave freed pointers behind
+            const int64_t want_emit = emit_total + emit_total / 4 + 4096, want_jobs = (int64_t) jobs.size() + 64;
+            E.emit_cap = E.emit_jobs_cap = 0;
+            if (cudaMalloc(&E.d_emit, (size_t) want_emit * sizeof(float)) != cudaSuccess ||
+                cudaMalloc(&E.d_emit_jobs, (size_t) want_jobs * sizeof(emit_job)) != cudaSuccess ||
+                cudaMallocHost(&E.h_emit, (size_t) want_emit * sizeof(float)) != cudaSuccess) {
+                if (E.d_emit) cudaFree(E.d_emit);
+                if (E.d_emit_jobs) cudaFree(E.d_emit_jobs);
+                if (E.h_emit) cudaFreeHost(E.h_emit);
+                E.d_emit = E.d_emit_jobs = E.h_emit = nullptr;
+                return "cudaMalloc failed (emit buffers)";
+            }
+            E.emit_cap = want_emit; E.emit_jobs_cap = want_jobs;
         }
         if (cudaMemcpyAsync(E.d_emit_jobs, jobs.data(), jobs.size() * sizeof(emit_job), cudaMemcpyHostToDevice, E.stream) != cudaSuccess)
             return "cudaMemcpyAsync failed (emit jobs)";

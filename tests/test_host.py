@@ -111,3 +111,32 @@ def test_sharding_balances_and_covers():
         assert loads.max() / loads.mean() < 1.01                      # longest-first packing: <1% imbalance
     assert sharding.shard_utterances(np.array([], dtype=np.int64), 4, 2).size == 0
     assert sharding.shard_utterances(np.array([7]), 4, 3).size + sharding.shard_utterances(np.array([7]), 4, 0).size == 1
+
+
+def test_corrupt_tensor_extents_are_rejected_at_open(tmp_path):
+    """Sizes and offsets come from the file: a tensor whose extent or data range does not fit the file must be refused
+    with MIO_ERR_FORMAT when the file is opened (no bad_alloc / wild seek across the C ABI)."""
+    import struct
+    from miocodec_b200 import binding
+
+    def gguf(ne, offset, payload=64):
+        def s(b):
+            e = b.encode()
+            return struct.pack("<Q", len(e)) + e
+        head = b"GGUF" + struct.pack("<IQQ", 3, 1, 1) + s("general.architecture") + struct.pack("<I", 8) + s("miocodec")
+        head += s("token_embd") + struct.pack("<I", len(ne)) + struct.pack("<%dQ" % len(ne), *ne) + struct.pack("<IQ", 0, offset)
+        head += b"\0" * ((-len(head)) % 32)
+        return head + b"\0" * payload
+
+    L = binding.lib()
+    import ctypes as C
+    for name, blob in (("huge", gguf([1 << 40, 1 << 30], 0)), ("negative", gguf([(1 << 64) - 8, 4], 0)), ("past_end", gguf([4, 4], 1 << 20)),
+                       ("too_long", gguf([768, 12800], 0))):
+        p = tmp_path / f"{name}.gguf"
+        p.write_bytes(blob)
+        h = C.c_void_p()
+        rc = L.mio_ctx_create(str(p).encode(), 0, C.byref(h))
+        assert rc == binding.MIO_ERR_FORMAT, (name, rc, L.mio_last_error())
+        assert b"corrupt GGUF" in L.mio_last_error()
+        out = np.zeros(8, dtype=np.float32)
+        assert L.mio_voice_load(str(p).encode(), out.ctypes.data, 8) == binding.MIO_ERR_FORMAT
