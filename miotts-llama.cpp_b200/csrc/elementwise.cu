@@ -4,6 +4,8 @@
 // (formulae: SURVEY.md Appendix A).
 #include "kernels.cuh"
 
+#include <cuda_bf16.h>
+
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -333,10 +335,47 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(const float * __restrict_
     }
 }
 
+// Any channel count that is a multiple of 32 (upsampler widths other than 512 / 256 / 128): warp w of the block owns
+// groups w, w + 8, ...; its lanes walk the (row, channel-in-group) cells of the segment in a fixed strided order and a
+// shuffle tree adds the 32 partial sums, so the result is as run-to-run and batch invariant as the fast kernel's.
+__global__ void __launch_bounds__(256) gn_stats_generic_kernel(const float * __restrict__ x, int C, const int32_t * __restrict__ start,
+                                                               const int32_t * __restrict__ len, const int32_t * __restrict__ seg_cu,
+                                                               int n_utts, int row_div, double2 * __restrict__ part) {
+    const int sb = blockIdx.x;
+    int lo = 0, hi = n_utts;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (seg_cu[mid] <= sb) lo = mid; else hi = mid;
+    }
+    const int u = lo, seg = sb - seg_cu[u];
+    const int cpg = C / 32;
+    const int r0 = (start[u] + seg * GN_SEG_CODES) * row_div;
+    const int nrows = min(GN_SEG_CODES, len[u] - seg * GN_SEG_CODES) * row_div;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int g = warp; g < 32; g += 8) {
+        float s = 0.f, q = 0.f;
+        const float * xp = x + (size_t) r0 * C + g * cpg;
+        for (int i = lane; i < nrows * cpg; i += 32) {
+            const int r = i / cpg, c = i - r * cpg;
+            const float v = __ldg(xp + (size_t) r * C + c);
+            s += v; q += v * v;
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            s += __shfl_xor_sync(0xffffffffu, s, o);
+            q += __shfl_xor_sync(0xffffffffu, q, o);
+        }
+        if (lane == 0) part[(size_t) sb * 32 + g] = make_double2((double) s, (double) q);
+    }
+}
+
 cudaError_t launch_gn_stats(const float * x, int C, const row_map & rm, int row_div, const int32_t * seg_cu, int total_segs,
                             double2 * part, cudaStream_t st, bool rev) {
     if (total_segs <= 0) return cudaSuccess;
-    if (C != 512 && C != 256 && C != 128) return cudaErrorInvalidValue;
+    if (C <= 0 || C % 32 != 0) return cudaErrorInvalidValue;
+    if (C != 512 && C != 256 && C != 128) {
+        gn_stats_generic_kernel<<<total_segs, 256, 0, st>>>(x, C, rm.start, rm.len, seg_cu, rm.n_utts, row_div, part);
+        return cudaGetLastError();
+    }
     gn_stats_kernel<<<total_segs, 256, 0, st>>>(x, C, rm.start, rm.len, seg_cu, rm.n_utts, row_div, part, rev ? 1 : 0);
     return cudaGetLastError();
 }
@@ -424,16 +463,43 @@ __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
     }
 }
 
+// Any even channel count per group (C a multiple of 64): one thread per channel pair, grid-stride over (row, pair).
+template <bool PRECISE>
+__global__ void __launch_bounds__(256) gn_apply_silu_generic_kernel(
+        const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt, int row_div,
+        const float2 * __restrict__ mr, const float * __restrict__ w, const float * __restrict__ b, __half * __restrict__ out) {
+    const int C2 = C >> 1, cpg = C / 32;
+    const size_t total = (size_t) rows * C2;
+    for (size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t) gridDim.x * blockDim.x) {
+        const int r = (int) (idx / C2), c = (int) (idx - (size_t) r * C2) * 2;
+        const int u = __ldg(row_utt + r / row_div);
+        __half2 h = __floats2half2_rn(0.f, 0.f);
+        if (u >= 0) {
+            const float2 v = *(const float2 *) (x + (size_t) r * C + c);
+            const float2 m = __ldg(mr + (size_t) u * 32 + c / cpg);
+            h = __floats2half2_rn(silu_pick<PRECISE>((v.x - m.x) * m.y * __ldg(w + c) + __ldg(b + c)),
+                                  silu_pick<PRECISE>((v.y - m.x) * m.y * __ldg(w + c + 1) + __ldg(b + c + 1)));
+        }
+        *(__half2 *) (out + (size_t) r * C + c) = h;
+    }
+}
+
 cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map & rm, int row_div, const double2 * part,
                                  const int32_t * seg_cu, float eps, const float * w, const float * b, float2 * mr_scratch,
                                  __half * out, cudaStream_t st, bool rev) {
     if (rows <= 0) return cudaSuccess;
-    if (C % 128 != 0 || C > 2048) return cudaErrorInvalidValue;
+    if (C <= 0 || C % 64 != 0) return cudaErrorInvalidValue;
     gn_finalize_kernel<<<(rm.n_utts * 32 + 255) / 256, 256, 0, st>>>(part, seg_cu, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
     static int precise_set = -1;
     if (precise_set < 0) {
         const char * ev = getenv("MIO_GN_PRECISE");
         precise_set = (ev && ev[0] == '1') ? 1 : 0;
+    }
+    if (C != 128 && C != 256 && C != 512 && C != 1024 && C != 2048) {     // the fast kernel needs C / 8 to divide 256
+        const int grid = (int) min((size_t) 148 * 16, ((size_t) rows * (C / 2) + 255) / 256);
+        if (precise_set) gn_apply_silu_generic_kernel<true><<<grid, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out);
+        else gn_apply_silu_generic_kernel<false><<<grid, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out);
+        return cudaGetLastError();
     }
     const int rpb = (rows >= GNA_ROWS * 148 * 2) ? GNA_ROWS : 16;      // few rows: more, shorter blocks (latency mode)
     if (precise_set) gn_apply_silu_kernel<true><<<(rows + rpb - 1) / rpb, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb, rev ? 1 : 0);
@@ -472,6 +538,34 @@ cudaError_t launch_split(const float * x, int rows, int C, const row_map & rm, i
     return cudaGetLastError();
 }
 
+// BF16-stored matrices: the reference rounds the activations to BF16 (round to nearest even, ggml_compute_fp32_to_bf16)
+// and multiplies once.  The (hi, lo) operand pair becomes one BF16 operand IN PLACE (bit patterns in the hi buffer);
+// hi + lo carries 22 bits of the fp32 value, far beyond the 8 that survive.
+__global__ void pair_to_bf16_kernel(__half * __restrict__ hi, const __half * __restrict__ lo, size_t n2) {
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (size_t) gridDim.x * blockDim.x) {
+        const float2 h = __half22float2(((const __half2 *) hi)[i]);
+        float2 v = h;
+        if (lo) { const float2 l = __half22float2(((const __half2 *) lo)[i]); v.x += l.x; v.y += l.y; }
+        const __nv_bfloat162 o = __floats2bfloat162_rn(v.x, v.y);
+        ((uint32_t *) hi)[i] = *(const uint32_t *) &o;
+    }
+}
+
+cudaError_t launch_pair_to_bf16(__half * hi, const __half * lo, size_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    if (n % 2) return cudaErrorInvalidValue;
+    const int grid = (int) min((size_t) 148 * 16, (n / 2 + 255) / 256);
+    pair_to_bf16_kernel<<<grid, 256, 0, st>>>(hi, lo, n / 2);
+    return cudaGetLastError();
+}
+
+// the activation rounding of a matrix product whose matrix is stored as F16 (1) / BF16 (2); 0 = F32, none
+__device__ __forceinline__ float round_act(float x, int store) {
+    if (store == 1) return __half2float(__float2half_rn(x));
+    if (store == 2) return __bfloat162float(__float2bfloat16_rn(x));
+    return x;
+}
+
 // AdaLN conditioning: mod[v][j] = b[j] + sum_k W[j][k] * silu(emb[v][k])
 // (compute_adaln3, src/miocodec.cpp:310-319 and :654-655). One warp per output row j, all voices.
 __global__ void cond_silu_kernel(const float * __restrict__ voice_table, int n, float * __restrict__ out) {
@@ -482,15 +576,17 @@ __global__ void cond_silu_kernel(const float * __restrict__ voice_table, int n, 
 // one warp per output row j (its 128 weights live in registers), looping over the voices of this blockIdx.y
 __global__ void cond_kernel(const float * __restrict__ voice_silu, int n_voices, int adaln_dim,
                             const float * __restrict__ w, const float * __restrict__ b, int cond_rows,
-                            float * __restrict__ mod) {
+                            const uint8_t * __restrict__ row_store, float * __restrict__ mod) {
     const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (j >= cond_rows) return;
     const float bj = b[j];
+    const int store = row_store ? row_store[j] : 0;      // storage type of the matrix this row came from
     if (adaln_dim == 128) {
         const float4 wj = __ldg((const float4 *) (w + (size_t) j * 128) + lane);
         for (int v = blockIdx.y; v < n_voices; v += gridDim.y) {
-            const float4 s = __ldg((const float4 *) (voice_silu + (size_t) v * 128) + lane);
+            float4 s = __ldg((const float4 *) (voice_silu + (size_t) v * 128) + lane);
+            if (store) s = make_float4(round_act(s.x, store), round_act(s.y, store), round_act(s.z, store), round_act(s.w, store));
             // same summation order per lane as the strided loop below would not matter: fp32 dot of 128 terms,
             // reduced over the warp; the reference's ggml_mul_mat sums in SIMD lanes of its own order
             float acc = wj.x * s.x + wj.y * s.y + wj.z * s.z + wj.w * s.w;
@@ -501,19 +597,19 @@ __global__ void cond_kernel(const float * __restrict__ voice_silu, int n_voices,
     }
     for (int v = blockIdx.y; v < n_voices; v += gridDim.y) {
         float acc = 0.f;
-        for (int k = lane; k < adaln_dim; k += 32) acc += w[(size_t) j * adaln_dim + k] * voice_silu[(size_t) v * adaln_dim + k];
+        for (int k = lane; k < adaln_dim; k += 32) acc += w[(size_t) j * adaln_dim + k] * round_act(voice_silu[(size_t) v * adaln_dim + k], store);
         acc = warp_sum(acc);
         if (lane == 0) mod[(size_t) v * cond_rows + j] = acc + bj;
     }
 }
 
 cudaError_t launch_cond(const float * voice_table, int n_voices, int adaln_dim, const float * w, const float * b,
-                        int cond_rows, float * silu_scratch, float * mod, cudaStream_t st) {
+                        int cond_rows, const uint8_t * row_store, float * silu_scratch, float * mod, cudaStream_t st) {
     if (n_voices <= 0) return cudaSuccess;
     const int n = n_voices * adaln_dim;
     cond_silu_kernel<<<(n + 255) / 256, 256, 0, st>>>(voice_table, n, silu_scratch);
     dim3 grid((cond_rows + 7) / 8, min(n_voices, 8));
-    cond_kernel<<<grid, 256, 0, st>>>(silu_scratch, n_voices, adaln_dim, w, b, cond_rows, mod);
+    cond_kernel<<<grid, 256, 0, st>>>(silu_scratch, n_voices, adaln_dim, w, b, cond_rows, row_store, mod);
     return cudaGetLastError();
 }
 

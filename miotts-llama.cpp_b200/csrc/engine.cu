@@ -96,6 +96,12 @@ __global__ void split_weights_kernel(const float * __restrict__ w, size_t n, flo
     }
 }
 
+// BF16-stored matrix: its values are BF16 numbers, kept as bit patterns in the fp16-typed operand buffer
+__global__ void bf16_weights_kernel(const float * __restrict__ w, size_t n, __half * __restrict__ out) {
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x)
+        out[i] = __ushort_as_half((unsigned short) (__float_as_uint(w[i]) >> 16));
+}
+
 template <class T>
 static std::string dev_alloc(T ** p, size_t n) {
     CK(cudaMalloc((void **) p, std::max<size_t>(n, 1) * sizeof(T)));
@@ -115,8 +121,8 @@ engine::~engine() {
     cudaSetDevice(device);
     if (stream && own_stream) cudaStreamSynchronize(stream);
     auto F = [](void * p) { if (p) cudaFree(p); };
-    F(x768); F(qkv_hi); F(qkv_lo); F(x512); F(y512); F(x256); F(y256); F(x128); F(y128); F(spec); F(mod); F(peak);
-    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(h512_hi); F(h512_lo); F(gn_part); F(gn_mr); F(voice_silu); F(attn_b1); F(attn_b2); F(err_flag);
+    F(x768); F(qkv_hi); F(qkv_lo); F(x512); F(y512); F(xu0); F(yu0); F(xu1); F(yu1); F(spec); F(mod); F(peak);
+    F(aA_hi); F(aA_lo); F(aFF_hi); F(aFF_lo); F(c16); F(hH_hi); F(hH_lo); F(gn_part); F(gn_mr); F(voice_silu); F(attn_b1); F(attn_b2); F(err_flag);
     F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_seg_cu); F(d_out_off); F(d_voice_table); F(d_wave);
     for (void * p : w_allocs) F(p);
     F(d_emit); F(d_emit_jobs); F(d_pcm); F(w.rope_pre); F(w.rope_t); F(istft_spec);
@@ -147,9 +153,10 @@ struct loader {
         if (ne) ne->assign(t->ne, t->ne + 4);
         return true;
     }
-    bool is_f16(const std::string & name) {
+    // gemm_weight::store of a matrix: 0 F32, 1 F16, 2 BF16
+    int store_of(const std::string & name) {
         const gguf_tensor * t = g.find(name);
-        return t && (t->dtype == GT_F16 || t->dtype == GT_BF16);
+        return !t ? 0 : t->dtype == GT_F16 ? 1 : t->dtype == GT_BF16 ? 2 : 0;
     }
     float * vec(const std::string & name, size_t expect) {
         std::vector<float> h;
@@ -169,8 +176,10 @@ struct loader {
         return d;
     }
     // B[N][Ktot] fp32 on the host -> split fp16 on the device (+ tensor maps)
-    bool pack(gemm_weight & W, const std::vector<float> & B, int N, int K, int taps, int npass) {
-        W.N = N; W.K = K; W.taps = taps; W.npass = npass;
+    // store 1 / 2 (F16 / BF16-stored matrix): one pass on operands of that type; the values are exactly representable
+    bool pack(gemm_weight & W, const std::vector<float> & B, int N, int K, int taps, int npass, int store = 0) {
+        if (store != 0) npass = 1;
+        W.N = N; W.K = K; W.taps = taps; W.npass = npass; W.store = store;
         const size_t n = (size_t) N * K * taps;
         if (B.size() != n) { err = "internal: weight size mismatch"; return false; }
         float scale = 1.f;
@@ -193,7 +202,8 @@ struct loader {
             if (cudaMalloc(&W.lo, n * sizeof(__half)) != cudaSuccess) { err = "cudaMalloc failed (weights)"; return false; }
             E.w_allocs.push_back(W.lo);
         }
-        split_weights_kernel<<<296, 256>>>(tmp, n, scale, W.hi, W.lo);
+        if (store == 2) bf16_weights_kernel<<<296, 256>>>(tmp, n, W.hi);
+        else split_weights_kernel<<<296, 256>>>(tmp, n, scale, W.hi, W.lo);
         cudaError_t ce = cudaDeviceSynchronize();
         cudaFree(tmp);
         if (ce != cudaSuccess) { err = std::string("split_weights_kernel: ") + cudaGetErrorString(ce); return false; }
@@ -217,13 +227,14 @@ struct loader {
     bool linear(gemm_weight & W, const std::vector<std::string> & names, int K, bool interleave2 = false) {
         std::vector<std::vector<float>> parts(names.size());
         int N = 0;
-        bool f16 = true;
+        const int store = store_of(names[0]);
         for (size_t i = 0; i < names.size(); i++) {
             std::vector<int64_t> ne;
             if (!get(names[i], parts[i], &ne)) return false;
             if (ne[0] != K) { err = "tensor " + names[i] + ": unexpected input width"; return false; }
             N += (int) ne[1];
-            f16 = f16 && is_f16(names[i]);
+            // the matrices of one stacked projection run as ONE product, so they must agree on the operand type
+            if (store_of(names[i]) != store) { err = "tensors " + names[0] + " and " + names[i] + " are stored in different types (F32/F16/BF16); matrices of one stacked projection must share a type"; return false; }
         }
         std::vector<float> B((size_t) N * K);
         if (interleave2) {   // two equally sized matrices, rows interleaved (gate/up)
@@ -236,10 +247,9 @@ struct loader {
             size_t off = 0;
             for (auto & p : parts) { memcpy(&B[off], p.data(), p.size() * sizeof(float)); off += p.size(); }
         }
-        // F16/BF16-stored matrices: the reference rounds the activations to that type too (ggml-cpu.c:1291-1326);
-        // we keep the split-precision activations (closer to exact) and the stored weight values exactly.
-        (void) f16;
-        return pack(W, B, N, K, 1, 3);
+        // F16/BF16-stored matrices: the reference rounds the activations to that type and multiplies once
+        // (ggml-cpu.c:1291-1326); pack() then selects the single-pass product on operands of that type
+        return pack(W, B, N, K, 1, 3, store);
     }
     // Conv1d k=3: ggml ne [3, IC, OC] == row-major [OC][IC][3] -> B[oc][tap*IC + ic]; operands rounded to fp16 (npass 1)
     bool conv3(gemm_weight & W, const std::string & name, int C) {
@@ -252,32 +262,41 @@ struct loader {
                 for (int t = 0; t < 3; t++) B[(size_t) oc * 3 * C + (size_t) t * C + ic] = h[((size_t) oc * C + ic) * 3 + t];
         return pack(W, B, C, C, 3, 1);
     }
-    // ConvTranspose1d: ggml ne [k, Cout, Cin] == row-major [Cin][Cout][k]; stride f, trim (k-f)/2 per side.
-    //   y[f*q + r][co] = b[co] + sum_{d=-1..1} sum_ci x[q+d][ci] * W[ci][co][r + trim - f*d]      (k == 3f)
-    //   y[f*q + r][co] = b[co] + sum_ci x[q][ci] * W[ci][co][r]                                   (k == f)
+    // ConvTranspose1d: ggml ne [k, Cout, Cin] == row-major [Cin][Cout][k]; stride f, then trim = (k-f)/2 samples dropped
+    // at each end (src/miocodec.cpp:683-696), i.e. PyTorch's ConvTranspose1d(padding=trim).  As a tap-GEMM over the
+    // INPUT rows, output row f*q + r (r < f) of N = f*Cout columns:
+    //   y[f*q + r][co] = b[co] + sum_{d=-D..D} sum_ci x[q+d][ci] * W[ci][co][r + trim - f*d]     (kernel index in [0, k))
+    // with D = floor((f - 1 + trim) / f): 0 for k == f, 1 for k <= 3f, 2 for k <= 5f.  Kernel positions a (r, d) pair
+    // does not have are zero columns of B; input rows outside the utterance are the zero pad rows of the row space.
     bool convT(gemm_weight & W, const std::string & name, int Cin, int Cout, int k, int f) {
         std::vector<float> h; std::vector<int64_t> ne;
         if (!get(name, h, &ne)) return false;
         if (ne[0] != k || ne[1] != Cout || ne[2] != Cin) { err = "tensor " + name + ": unexpected ConvTranspose shape"; return false; }
-        int taps;
-        if (k == f) taps = 1;
-        else if (k == 3 * f) taps = 3;
-        else { err = "ConvTranspose1d with kernel " + std::to_string(k) + " / stride " + std::to_string(f) + " is not supported (need k == f or k == 3f)"; return false; }
+        if (f < 1 || k < f || (k - f) % 2 != 0) {
+            // the reference's trim (k-f)/2 per side only restores the length f*L when k - f is even (src/miocodec.cpp:689-696)
+            err = "ConvTranspose1d " + name + ": kernel " + std::to_string(k) + " / stride " + std::to_string(f) + " needs k >= f and (k - f) even";
+            return false;
+        }
         const int trim = (k - f) / 2;
+        const int D = (f - 1 + trim) / f;
+        if (D > 2) { err = "ConvTranspose1d " + name + ": kernel " + std::to_string(k) + " wider than 5 x stride " + std::to_string(f) + " is not supported"; return false; }
+        const int taps = 2 * D + 1;
         const int N = f * Cout;
+        const int store = store_of(name);
+        // ggml has no BF16 ConvTranspose1d kernel either (ops.cpp:6069-6082 dispatches on F16 / F32 only and aborts)
+        if (store == 2) { err = "ConvTranspose1d " + name + ": BF16 kernels are not supported (the reference aborts on them too)"; return false; }
         std::vector<float> B((size_t) N * taps * Cin, 0.f);
         for (int r = 0; r < f; r++)
             for (int co = 0; co < Cout; co++)
                 for (int t = 0; t < taps; t++) {
-                    const int d = (taps == 3) ? t - 1 : 0;
+                    const int d = t - D;
                     const int kk = r + trim - f * d;
                     if (kk < 0 || kk >= k) continue;
                     float * dst = &B[((size_t) (r * Cout + co) * taps + t) * Cin];
                     for (int ci = 0; ci < Cin; ci++) dst[ci] = h[((size_t) ci * Cout + co) * k + kk];
                 }
-        const bool f16 = is_f16(name);
-        (void) f16;
-        return pack(W, B, N, Cin, taps, 3);
+        // F16-stored kernel: activations rounded to F16, one pass (ggml-cpu/ops.cpp:5909-5995)
+        return pack(W, B, N, Cin, taps, 3, store);
     }
     bool resblock(resblock_w & R, const std::string & p, int C) {
         R.C = C;
@@ -346,11 +365,15 @@ std::string engine::load(const std::string & path, int dev) {
             return "missing/invalid miocodec.wave_upsampler.factors / kernel_sizes";
         int32_t f[4] = {0}, k[4] = {0};
         if (!g.read_raw(*tf, f, sizeof(int32_t) * hp.up_stages) || !g.read_raw(*tk, k, sizeof(int32_t) * hp.up_stages)) return "short read (upsampler geometry)";
-        int total = 2;
-        for (int s = 0; s < hp.up_stages; s++) { hp.up_factor[s] = f[s]; hp.up_kernel[s] = k[s]; total *= f[s]; }
+        int total = 2;     // wave_upsample doubles the rate first (stride 2 is fixed in the graph, src/miocodec.cpp:624)
+        for (int s = 0; s < hp.up_stages; s++) {
+            if (f[s] < 1 || f[s] > 64 || k[s] < 1) return "invalid upsampler factor / kernel size";
+            hp.up_factor[s] = f[s]; hp.up_kernel[s] = k[s]; total *= f[s];
+            hp.up_res[s] = total;
+        }
         hp.frames_per_code = total;
-        if (hp.up_factor[0] != 3 || hp.up_factor[1] != 3) return "unsupported upsampler factors (row-space resolutions are built for 2 x 3 x 3)";
-        if (hp.frames_per_code * hp.hop != hp.samples_per_token) return "inconsistent samples_per_token";
+        if (hp.frames_per_code > 4096) return "invalid upsampler factors";
+        if (hp.frames_per_code * hp.hop != hp.samples_per_token) return "inconsistent samples_per_token (2 * prod(factors) * hop_length)";
     }
     {
         const gguf_tensor * te = g.find("token_embd");
@@ -389,6 +412,7 @@ std::string engine::load(const std::string & path, int dev) {
     w.dec.resize(hp.dec_layers);
     w.cond_rows = hp.dec_layers * 2 * 3 * C + 2 * C;
     std::vector<float> cw((size_t) w.cond_rows * hp.adaln_dim), cb(w.cond_rows);
+    std::vector<uint8_t> cstore(w.cond_rows, 0);     // F16/BF16-stored conditioning matrices: silu(emb) rounded to that type
     for (int i = 0; i < hp.dec_layers; i++) {
         const std::string p = "wave_decoder.blk." + std::to_string(i) + ".";
         dec_layer_w & l = w.dec[i];
@@ -404,6 +428,7 @@ std::string engine::load(const std::string & path, int dev) {
             const size_t row0 = (size_t) (i * 2 + j) * 3 * C;
             memcpy(&cw[row0 * hp.adaln_dim], hw.data(), hw.size() * sizeof(float));
             memcpy(&cb[row0], hb.data(), hb.size() * sizeof(float));
+            std::fill(cstore.begin() + row0, cstore.begin() + row0 + 3 * C, (uint8_t) L.store_of(p + nm[j] + ".weight"));
         }
     }
     {
@@ -413,9 +438,13 @@ std::string engine::load(const std::string & path, int dev) {
         const size_t row0 = (size_t) hp.dec_layers * 2 * 3 * C;
         memcpy(&cw[row0 * hp.adaln_dim], hw.data(), hw.size() * sizeof(float));
         memcpy(&cb[row0], hb.data(), hb.size() * sizeof(float));
+        std::fill(cstore.begin() + row0, cstore.end(), (uint8_t) L.store_of("wave_decoder.norm_cond.weight"));
     }
     w.cond_w = L.vec_host(cw); w.cond_b = L.vec_host(cb);
     if (!w.cond_w || !w.cond_b) return L.err;
+    CK(cudaMalloc((void **) &w.cond_store, cstore.size()));
+    w_allocs.push_back(w.cond_store);
+    CK(cudaMemcpy(w.cond_store, cstore.data(), cstore.size(), cudaMemcpyHostToDevice));
 
     // upsampler stages
     w.upT.resize(hp.up_stages); w.upT_b.resize(hp.up_stages); w.snake_ea.resize(hp.up_stages); w.snake_eb.resize(hp.up_stages);
@@ -427,7 +456,7 @@ std::string engine::load(const std::string & path, int dev) {
         if (!t) return "missing tensor: " + un + ".weight";
         const int cout = (int) t->ne[1];
         hp.up_ch[s] = cout;
-        if (cout != (s == 0 ? 256 : 128)) return "unsupported upsampler widths (kernels are built for 512 -> 256 -> 128)";
+        if (cout < 64 || cout % 64 != 0 || cout > 4096) return "unsupported upsampler width " + std::to_string(cout) + " (channel counts must be multiples of 64)";
         if (!L.convT(w.upT[s], un + ".weight", cin, cout, hp.up_kernel[s], hp.up_factor[s])) return L.err;
         w.upT_b[s] = L.vec(un + ".bias", cout);
         std::vector<float> a, b;
@@ -444,7 +473,7 @@ std::string engine::load(const std::string & path, int dev) {
         const gguf_tensor * t = g.find("wave_upsampler.out_proj.weight");
         if (!t) return "missing tensor: wave_upsampler.out_proj.weight";
         hp.out_proj_dim = (int) t->ne[1];
-        if (hp.out_proj_dim != 512) return "unsupported out_proj width (kernels are built for 512)";
+        if (hp.out_proj_dim < 64 || hp.out_proj_dim % 64 != 0 || hp.out_proj_dim > 4096) return "unsupported out_proj width (must be a multiple of 64)";
         if (!L.linear(w.out_proj, {"wave_upsampler.out_proj.weight"}, cin)) return L.err;
         w.out_proj_b = L.vec("wave_upsampler.out_proj.bias", hp.out_proj_dim);
         std::vector<float> a, b;
@@ -464,7 +493,7 @@ std::string engine::load(const std::string & path, int dev) {
             memcpy(&B[(size_t) (2 * f + 1) * P], &hw[(size_t) (NF + f) * P], P * sizeof(float));
             bb[2 * f] = hb[f]; bb[2 * f + 1] = hb[NF + f];
         }
-        if (!L.pack(w.head, B, 2 * NF, P, 1, 3)) return L.err;
+        if (!L.pack(w.head, B, 2 * NF, P, 1, 3, L.store_of("istft_head.out.weight"))) return L.err;
         w.head_b = L.vec_host(bb);
     }
     {   // periodic Hann window (istft_cache, src/istft.cpp:29-31)
@@ -574,7 +603,10 @@ static std::string make_view(a_view & v, __half * hi, __half * lo, int rows, int
 std::string engine::ensure_workspace() {
     if (ws_ready) return {};
     CK(cudaSetDevice(device));
-    const size_t R1 = (size_t) max_rows1, R2 = 2 * R1, R6 = 6 * R1, R18 = 18 * R1;
+    // rows per code: 1 (prenet), 2 (decoder), 2*f0 and 2*f0*f1 = frames per code (upsampler stages)
+    const size_t R1 = (size_t) max_rows1, R2 = 2 * R1, Ru0 = (size_t) hp.up_res[0] * R1, Ru1 = (size_t) hp.up_res[1] * R1;
+    const size_t c0 = (size_t) hp.up_ch[0], c1 = (size_t) hp.up_ch[1], P = (size_t) hp.out_proj_dim;
+    const size_t n_ff = std::max({R1 * 3072, Ru0 * c0, Ru1 * c1}), n_c16 = std::max({R2 * 512, Ru0 * c0, Ru1 * c1});
     std::string e;
 #define A(ptr, n) if (!(e = dev_alloc(&ptr, (size_t) (n))).empty()) return e;
     if (istft_only) {   // mio_istft_ctx_create: no decoder workspace (run_istft_only grows its own staging buffer)
@@ -584,10 +616,10 @@ std::string engine::ensure_workspace() {
         return {};
     }
     A(x768, R1 * 768); A(qkv_hi, std::max(R1 * 2304, R2 * 1536)); A(qkv_lo, std::max(R1 * 2304, R2 * 1536));
-    A(x512, R2 * 512); A(y512, R2 * 512); A(x256, R6 * 256); A(y256, R6 * 256); A(x128, R18 * 128); A(y128, R18 * 128);
-    A(spec, R18 * SPEC_LD);
-    A(aA_hi, R1 * 1024); A(aA_lo, R1 * 1024); A(aFF_hi, R1 * 3072); A(aFF_lo, R1 * 3072);
-    A(c16, R1 * 2304); A(h512_hi, R18 * 512); A(h512_lo, R18 * 512);
+    A(x512, R2 * 512); A(y512, R2 * 512); A(xu0, Ru0 * c0); A(yu0, Ru0 * c0); A(xu1, Ru1 * c1); A(yu1, Ru1 * c1);
+    A(spec, Ru1 * SPEC_LD);
+    A(aA_hi, R1 * 1024); A(aA_lo, R1 * 1024); A(aFF_hi, n_ff); A(aFF_lo, n_ff);
+    A(c16, n_c16); A(hH_hi, Ru1 * P); A(hH_lo, Ru1 * P);
     A(gn_part, (size_t) (max_rows1 / GN_SEG_CODES + max_utts + 1) * 32);
     A(gn_mr, (size_t) max_utts * 32);
     A(attn_b1, R1); A(attn_b2, R2);
@@ -599,19 +631,19 @@ std::string engine::ensure_workspace() {
     CK(cudaMemset(err_flag, 0, sizeof(int)));
     // stale rows beyond the current batch are only ever multiplied into masked outputs, but start finite
     CK(cudaMemset(aA_hi, 0, R1 * 1024 * 2)); CK(cudaMemset(aA_lo, 0, R1 * 1024 * 2));
-    CK(cudaMemset(aFF_hi, 0, R1 * 3072 * 2)); CK(cudaMemset(aFF_lo, 0, R1 * 3072 * 2));
-    CK(cudaMemset(c16, 0, R1 * 2304 * 2));
-    CK(cudaMemset(h512_hi, 0, R18 * 512 * 2)); CK(cudaMemset(h512_lo, 0, R18 * 512 * 2));
+    CK(cudaMemset(aFF_hi, 0, n_ff * 2)); CK(cudaMemset(aFF_lo, 0, n_ff * 2));
+    CK(cudaMemset(c16, 0, n_c16 * 2));
+    CK(cudaMemset(hH_hi, 0, Ru1 * P * 2)); CK(cudaMemset(hH_lo, 0, Ru1 * P * 2));
     if (!(e = make_view(vA768, aA_hi, aA_lo, (int) R1, 768)).empty()) return e;
     if (!(e = make_view(vA512, aA_hi, aA_lo, (int) R2, 512)).empty()) return e;
     if (!(e = make_view(vFF2048, aFF_hi, aFF_lo, (int) R1, 2048)).empty()) return e;
     if (!(e = make_view(vFF1536, aFF_hi, aFF_lo, (int) R2, 1536)).empty()) return e;
-    if (!(e = make_view(vFF256, aFF_hi, aFF_lo, (int) R6, 256)).empty()) return e;
-    if (!(e = make_view(vFF128, aFF_hi, aFF_lo, (int) R18, 128)).empty()) return e;
+    if (!(e = make_view(vFFu0, aFF_hi, aFF_lo, (int) Ru0, (int) c0)).empty()) return e;
+    if (!(e = make_view(vFFu1, aFF_hi, aFF_lo, (int) Ru1, (int) c1)).empty()) return e;
     if (!(e = make_view(vC512, c16, nullptr, (int) R2, 512)).empty()) return e;
-    if (!(e = make_view(vC256, c16, nullptr, (int) R6, 256)).empty()) return e;
-    if (!(e = make_view(vC128, c16, nullptr, (int) R18, 128)).empty()) return e;
-    if (!(e = make_view(vH512, h512_hi, h512_lo, (int) R18, 512)).empty()) return e;
+    if (!(e = make_view(vCu0, c16, nullptr, (int) Ru0, (int) c0)).empty()) return e;
+    if (!(e = make_view(vCu1, c16, nullptr, (int) Ru1, (int) c1)).empty()) return e;
+    if (!(e = make_view(vH, hH_hi, hH_lo, (int) Ru1, (int) P)).empty()) return e;
     ws_ready = true;
     return {};
 }
@@ -824,6 +856,13 @@ cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_pa
     p.a_hi = A.hi; p.a_lo = A.lo; p.lda = A.K; p.a_rows = A.rows;
     p.b_hi = W.hi; p.b_lo = W.lo;
     if (A.K != W.K) return cudaErrorInvalidValue;
+    if (W.store == 2) {   // BF16-stored matrix: the activation pair becomes one BF16 operand, in place (every operand buffer feeds one product)
+        if (W.taps != 1) return cudaErrorInvalidValue;
+        cudaError_t e = launch_pair_to_bf16(A.hi, A.lo, (size_t) M * A.K, stream);
+        if (e != cudaSuccess) return e;
+        launches++;
+        p.bf16 = 1;
+    }
     launches++;
     prof_begin(W.npass == 3 ? CAT_GEMM_SPLIT : CAT_GEMM_F16, 2.0 * M * (double) W.N * W.K * W.taps, 0.0);
     cudaError_t ce;
@@ -1000,7 +1039,8 @@ std::string engine::run_attention(int rows, int D, int n_head, int window, int r
 std::string engine::run_chunk(const chunk_info & c) {
     cur_row0 = c.row0; cur_utt0 = c.utt0; cur_rows1 = c.rows1; cur_n_utts = c.n_utts; cur_scu0 = c.scu0; cur_n_segs = c.n_segs;
     const row_map rm = rmap();
-    const int R1 = c.rows1, R2 = 2 * R1, R6 = 6 * R1, R18 = 18 * R1;
+    const int R1 = c.rows1, R2 = 2 * R1, rd0 = hp.up_res[0], rd1 = hp.up_res[1], Ru0 = rd0 * R1, Ru1 = rd1 * R1;
+    const int c0 = hp.up_ch[0], c1 = hp.up_ch[1], P = hp.out_proj_dim, f0 = hp.up_factor[0], f1 = hp.up_factor[1];
     const int D = hp.prenet_dim, C = hp.dec_dim;
     gemm_params p;
     std::string e;
@@ -1090,32 +1130,32 @@ std::string engine::run_chunk(const chunk_info & c) {
     for (int b = 0; b < hp.resnet_blocks; b++)
         if (!(e = run_resblock(w.post[b], x512, y512, vC512, R2, 2, "post" + std::to_string(b))).empty()) return e;
     if (taps_on()) tap_f32("post", x512, R2, C);
-    // 8. upsampler stage 0: ConvT(512->256, k9 s3) + bias + trim + Snake, then resblock
+    // 8. upsampler stage 0: ConvT(512 -> c0, kernel k0, stride f0) + bias + trim + Snake, then resblock
     CKR(CAT_SPLIT, (double) (R2) * 8.0 * (C), launch_split(x512, R2, C, rm, 2, vA512.hi, vA512.lo, stream));
-    p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = x256; p.ld_out = 3 * 256; p.bias = w.upT_b[0]; p.bias_mod = 256;
+    p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = xu0; p.ld_out = f0 * c0; p.bias = w.upT_b[0]; p.bias_mod = c0;
     p.snake_ea = w.snake_ea[0]; p.snake_eb = w.snake_eb[0];
     CKG(gemm(w.upT[0], vA512, R2, p));
-    if (taps_on()) tap_f32("up0_snake", x256, R6, 256);
-    if (!(e = run_resblock(w.up_res[0], x256, y256, vC256, R6, 6, "upres0")).empty()) return e;
-    if (taps_on()) tap_f32("up0", x256, R6, 256);
-    //    stage 1: ConvT(256->128, k9 s3)
-    CKR(CAT_SPLIT, (double) (R6) * 8.0 * (256), launch_split(x256, R6, 256, rm, 6, vFF256.hi, vFF256.lo, stream));
-    p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = x128; p.ld_out = 3 * 128; p.bias = w.upT_b[1]; p.bias_mod = 128;
+    if (taps_on()) tap_f32("up0_snake", xu0, Ru0, c0);
+    if (!(e = run_resblock(w.up_res[0], xu0, yu0, vCu0, Ru0, rd0, "upres0")).empty()) return e;
+    if (taps_on()) tap_f32("up0", xu0, Ru0, c0);
+    //    stage 1: ConvT(c0 -> c1, kernel k1, stride f1)
+    CKR(CAT_SPLIT, (double) (Ru0) * 8.0 * (c0), launch_split(xu0, Ru0, c0, rm, rd0, vFFu0.hi, vFFu0.lo, stream));
+    p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = xu1; p.ld_out = f1 * c1; p.bias = w.upT_b[1]; p.bias_mod = c1;
     p.snake_ea = w.snake_ea[1]; p.snake_eb = w.snake_eb[1];
-    CKG(gemm(w.upT[1], vFF256, R6, p));
-    if (taps_on()) tap_f32("up1_snake", x128, R18, 128);
-    if (!(e = run_resblock(w.up_res[1], x128, y128, vC128, R18, 18, "upres1")).empty()) return e;
-    if (taps_on()) tap_f32("up1", x128, R18, 128);
-    // 8b. out_proj 128 -> 512 + bias + Snake -> split operand of the head
-    CKR(CAT_SPLIT, (double) (R18) * 8.0 * (128), launch_split(x128, R18, 128, rm, 18, vFF128.hi, vFF128.lo, stream));
-    p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = vH512.hi; p.out_lo = vH512.lo; p.ld_h = 512; p.bias = w.out_proj_b;
+    CKG(gemm(w.upT[1], vFFu0, Ru0, p));
+    if (taps_on()) tap_f32("up1_snake", xu1, Ru1, c1);
+    if (!(e = run_resblock(w.up_res[1], xu1, yu1, vCu1, Ru1, rd1, "upres1")).empty()) return e;
+    if (taps_on()) tap_f32("up1", xu1, Ru1, c1);
+    // 8b. out_proj c1 -> P + bias + Snake -> split operand of the head
+    CKR(CAT_SPLIT, (double) (Ru1) * 8.0 * (c1), launch_split(xu1, Ru1, c1, rm, rd1, vFFu1.hi, vFFu1.lo, stream));
+    p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = vH.hi; p.out_lo = vH.lo; p.ld_h = P; p.bias = w.out_proj_b;
     p.snake_ea = w.out_snake_ea; p.snake_eb = w.out_snake_eb;
-    CKG(gemm(w.out_proj, vFF128, R18, p));
-    if (taps_on()) tap_f16("out_snake", vH512.hi, vH512.lo, (size_t) R18 * 512);
-    // 9. head: 512 -> 394, exp/clamp/cos/sin -> interleaved (re, im)
+    CKG(gemm(w.out_proj, vFFu1, Ru1, p));
+    if (taps_on()) tap_f16("out_snake", vH.hi, vH.lo, (size_t) Ru1 * P);
+    // 9. head: P -> 394, exp/clamp/cos/sin -> interleaved (re, im)
     p = gemm_params(); p.epi = EPI_HEAD; p.out_f32 = spec; p.ld_out = SPEC_LD; p.bias = w.head_b;
-    CKG(gemm(w.head, vH512, R18, p));
-    if (taps_on()) tap_f32("spec", spec, R18, 2 * hp.n_freq, SPEC_LD);
+    CKG(gemm(w.head, vH, Ru1, p));
+    if (taps_on()) tap_f32("spec", spec, Ru1, 2 * hp.n_freq, SPEC_LD);
     // ISTFT
     if (!(e = run_istft(c, spec)).empty()) return e;
     return {};
@@ -1168,7 +1208,7 @@ std::string engine::run_impl(bool peak_normalize, float * host_dst, int16_t * ho
     launches = 0;
     snaps.clear();
     // AdaLN conditioning vectors of every voice of the batch (compute_adaln3, src/miocodec.cpp:310-319)
-    if (lay.n_utts > 0) CKR(CAT_COND, 0.0, launch_cond(d_voice_table, n_voices, hp.adaln_dim, w.cond_w, w.cond_b, w.cond_rows, voice_silu, mod, stream));
+    if (lay.n_utts > 0) CKR(CAT_COND, 0.0, launch_cond(d_voice_table, n_voices, hp.adaln_dim, w.cond_w, w.cond_b, w.cond_rows, w.cond_store, voice_silu, mod, stream));
     if (lay.n_utts > 0) launches++;   // two kernels (silu of the embeddings, then the GEMV rows)
     if (host_pcm) { std::string e = ensure_pcm(); if (!e.empty()) return e; }
     if ((host_dst || host_pcm) && !copy_stream) {

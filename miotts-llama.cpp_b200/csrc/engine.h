@@ -69,10 +69,10 @@ struct engine {
     int64_t launches = 0;
 
     // ---- workspace (device)
-    float *x768 = nullptr, *x512 = nullptr, *y512 = nullptr, *x256 = nullptr, *y256 = nullptr,
-          *x128 = nullptr, *y128 = nullptr, *spec = nullptr, *mod = nullptr, *peak = nullptr;
+    float *x768 = nullptr, *x512 = nullptr, *y512 = nullptr, *xu0 = nullptr, *yu0 = nullptr,
+          *xu1 = nullptr, *yu1 = nullptr, *spec = nullptr, *mod = nullptr, *peak = nullptr;
     __half *aA_hi = nullptr, *aA_lo = nullptr, *aFF_hi = nullptr, *aFF_lo = nullptr, *c16 = nullptr,
-           *h512_hi = nullptr, *h512_lo = nullptr, *qkv_hi = nullptr, *qkv_lo = nullptr;
+           *hH_hi = nullptr, *hH_lo = nullptr, *qkv_hi = nullptr, *qkv_lo = nullptr;
     bool attn_simt = false;           // MIO_ATTN=simt: CUDA-core validation kernel
     double2 * gn_part = nullptr;      // [segments][32] (sum, sum of squares) of the GroupNorm being computed
     float * voice_silu = nullptr;     // [max_voices][128] silu(voice embedding), input of cond_kernel
@@ -80,7 +80,7 @@ struct engine {
     int2 * attn_b1 = nullptr;         // [max_rows1]   valid key range per prenet row (attn_bounds_kernel)
     int2 * attn_b2 = nullptr;         // [2*max_rows1] valid key range per decoder row
     int * err_flag = nullptr;
-    a_view vA768, vA512, vFF2048, vFF1536, vFF256, vFF128, vFF512, vC512, vC256, vC128, vH512;
+    a_view vA768, vA512, vFF2048, vFF1536, vFFu0, vFFu1, vFF512, vC512, vCu0, vCu1, vH;
     bool vFF512_ready = false;
     std::vector<void *> w_allocs;     // every weight allocation (freed in the destructor)
     int max_utts = 4096;

@@ -8,7 +8,7 @@
 // (fp16 pairs, ~22 significant bits) and D = a_hi*b_hi + a_hi*b_lo + a_lo*b_hi with FP32 accumulation (npass = 3);
 // conv1d layers run one exact-in-kind pass (npass = 1).
 //
-// Tap-GEMM: D[m][n] = sum_{tap} sum_k A[m + tap - (taps==3)][k] * B[n][tap*K + k].  Row shifts are plain TMA
+// Tap-GEMM: D[m][n] = sum_{tap} sum_k A[m + tap - taps/2][k] * B[n][tap*K + k], taps in {1, 3, 5}.  Row shifts are plain TMA
 // coordinates; out-of-range rows are zero-filled by TMA and utterances are separated by zero rows, which is the
 // zero padding of conv1d / the missing taps of ConvTranspose1d.
 //
@@ -233,7 +233,7 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     const int num_tiles = tiles_n * tiles_m;
     const int kb_per_tap = p.K / G3_BK;
     const int num_kb = p.taps * kb_per_tap;
-    const int shift0 = (p.taps == 3) ? -1 : 0;
+    const int shift0 = -(p.taps / 2);                      // taps 1 / 3 / 5: rows m, m-1..m+1, m-2..m+2
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA_hi);
@@ -286,6 +286,8 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     } else if (warp == 1) {
         // ===== MMA issuer (leader CTA only) =====
         if (leader && lane == 0) {
+            // operand format of kind::f16: bits 7-9 (A) and 10-12 (B), 0 = F16, 1 = BF16 (BF16-stored matrices, npass 1)
+            const uint32_t idesc = cfg::IDESC | (p.bf16 ? ((1u << 7) | (1u << 10)) : 0u);
             if constexpr (CHUNK > 0) {
                 int it = 0, ci = 0;                               // ci: running chunk counter = accumulator hand-offs
                 for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
@@ -308,14 +310,14 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                                 const uint64_t da_lo = umma_desc(sa + cfg::A_BYTES), db_lo = umma_desc(sb + cfg::B_BYTES);
                                 // cross terms first: they are 2^-11 of the hi*hi terms, so their truncations are free
 #pragma unroll
-                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_lo + (uint64_t) (k * 2), cfg::IDESC, (j > 0 || k > 0) ? 1u : 0u);
+                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_lo + (uint64_t) (k * 2), idesc, (j > 0 || k > 0) ? 1u : 0u);
 #pragma unroll
-                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_lo + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), cfg::IDESC, 1u);
+                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_lo + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), idesc, 1u);
 #pragma unroll
-                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), cfg::IDESC, 1u);
+                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), idesc, 1u);
                             } else {
 #pragma unroll
-                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), cfg::IDESC, (j > 0 || k > 0) ? 1u : 0u);
+                                for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), idesc, (j > 0 || k > 0) ? 1u : 0u);
                             }
                             umma_commit_pair(&empty[s]);
                         }
@@ -341,23 +343,23 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                     const uint64_t da_lo = umma_desc(sa + cfg::A_BYTES), db_lo = umma_desc(sb + cfg::B_BYTES);
                     if (NPASS == 3 && p.mma_order == 2) {          // pass-major inside the k-block: +1.3 % (profiles/r1n_summary.md)
 #pragma unroll
-                        for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), cfg::IDESC, (kb > 0 || k > 0) ? 1u : 0u);
+                        for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), idesc, (kb > 0 || k > 0) ? 1u : 0u);
 #pragma unroll
-                        for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_lo + (uint64_t) (k * 2), cfg::IDESC, 1u);
+                        for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_hi + (uint64_t) (k * 2), db_lo + (uint64_t) (k * 2), idesc, 1u);
 #pragma unroll
-                        for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_lo + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), cfg::IDESC, 1u);
+                        for (int k = 0; k < G3_BK / 16; k++) umma_f16_pair(d_tmem, da_lo + (uint64_t) (k * 2), db_hi + (uint64_t) (k * 2), idesc, 1u);
                     } else {
 #pragma unroll
                     for (int k = 0; k < G3_BK / 16; k++) {
                         const uint64_t adv = (uint64_t) (k * 2);
-                        umma_f16_pair(d_tmem, da_hi + adv, db_hi + adv, cfg::IDESC, (kb > 0 || k > 0) ? 1u : 0u);
+                        umma_f16_pair(d_tmem, da_hi + adv, db_hi + adv, idesc, (kb > 0 || k > 0) ? 1u : 0u);
                         if (NPASS == 3) {
                             if (p.mma_order == 1) {
-                                umma_f16_pair(d_tmem, da_lo + adv, db_hi + adv, cfg::IDESC, 1u);
-                                umma_f16_pair(d_tmem, da_hi + adv, db_lo + adv, cfg::IDESC, 1u);
+                                umma_f16_pair(d_tmem, da_lo + adv, db_hi + adv, idesc, 1u);
+                                umma_f16_pair(d_tmem, da_hi + adv, db_lo + adv, idesc, 1u);
                             } else {
-                                umma_f16_pair(d_tmem, da_hi + adv, db_lo + adv, cfg::IDESC, 1u);
-                                umma_f16_pair(d_tmem, da_lo + adv, db_hi + adv, cfg::IDESC, 1u);
+                                umma_f16_pair(d_tmem, da_hi + adv, db_lo + adv, idesc, 1u);
+                                umma_f16_pair(d_tmem, da_lo + adv, db_hi + adv, idesc, 1u);
                             }
                         }
                     }
@@ -550,18 +552,22 @@ static cudaError_t set_attr_inst() {
     }
     return e;
 }
+template <int BN, int NPASS>
+static cudaError_t set_attr_np() {
+    cudaError_t e;
+    if ((e = set_attr_inst<BN, NPASS, EPI_STORE>()) != cudaSuccess) return e;
+    if ((e = set_attr_inst<BN, NPASS, EPI_RESID>()) != cudaSuccess) return e;
+    if constexpr (BN >= 128) { if ((e = set_attr_inst<BN, NPASS, EPI_SWIGLU>()) != cudaSuccess) return e; }
+    if ((e = set_attr_inst<BN, NPASS, EPI_SPLIT>()) != cudaSuccess) return e;
+    if ((e = set_attr_inst<BN, NPASS, EPI_SNAKE>()) != cudaSuccess) return e;
+    if ((e = set_attr_inst<BN, NPASS, EPI_HEAD>()) != cudaSuccess) return e;
+    return set_attr_inst<BN, NPASS, EPI_QKV>();
+}
 template <int BN>
 static cudaError_t set_attr_bn() {
     cudaError_t e;
-    if ((e = set_attr_inst<BN, 1, EPI_STORE>()) != cudaSuccess) return e;
-    if ((e = set_attr_inst<BN, 1, EPI_RESID>()) != cudaSuccess) return e;
-    if ((e = set_attr_inst<BN, 3, EPI_STORE>()) != cudaSuccess) return e;
-    if ((e = set_attr_inst<BN, 3, EPI_RESID>()) != cudaSuccess) return e;
-    if constexpr (BN >= 128) { if ((e = set_attr_inst<BN, 3, EPI_SWIGLU>()) != cudaSuccess) return e; }
-    if ((e = set_attr_inst<BN, 3, EPI_SPLIT>()) != cudaSuccess) return e;
-    if ((e = set_attr_inst<BN, 3, EPI_SNAKE>()) != cudaSuccess) return e;
-    if ((e = set_attr_inst<BN, 3, EPI_HEAD>()) != cudaSuccess) return e;
-    return set_attr_inst<BN, 3, EPI_QKV>();
+    if ((e = set_attr_np<BN, 1>()) != cudaSuccess) return e;
+    return set_attr_np<BN, 3>();
 }
 // The opt-in to > 48 KB of dynamic shared memory is stored per device, so every context sets it for ITS device
 // (a process-wide "done" flag would leave the second GPU of a multi-device process without it).
@@ -581,18 +587,18 @@ static cudaError_t launch_tc3_epi(const gemm_params & p, const CUtensorMap & a_h
         case EPI_RESID: return launch_tc3_pick<BN, NPASS, EPI_RESID>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
         default: break;
     }
-    if constexpr (NPASS == 3) {
-        switch (p.epi) {
-            case EPI_SWIGLU:
-                if (p.N % 64 != 0) return cudaErrorInvalidValue;
-                if constexpr (BN >= 128) return launch_tc3_pick<BN, 3, EPI_SWIGLU>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
-                else return cudaErrorInvalidValue;   // a (gate, up) pair row needs 64 accumulator columns per warp
-            case EPI_SPLIT: return launch_tc3_pick<BN, 3, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
-            case EPI_SNAKE: return launch_tc3_pick<BN, 3, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
-            case EPI_HEAD: return launch_tc3_pick<BN, 3, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
-            case EPI_QKV: return launch_tc3_pick<BN, 3, EPI_QKV>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
-            default: break;
-        }
+    // NPASS 1 with these epilogues: F16/BF16-stored matrices (the reference rounds the activations to that type and
+    // multiplies once, ggml-cpu.c:1291-1326)
+    switch (p.epi) {
+        case EPI_SWIGLU:
+            if (p.N % 64 != 0) return cudaErrorInvalidValue;
+            if constexpr (BN >= 128) return launch_tc3_pick<BN, NPASS, EPI_SWIGLU>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+            else return cudaErrorInvalidValue;   // a (gate, up) pair row needs 64 accumulator columns per warp
+        case EPI_SPLIT: return launch_tc3_pick<BN, NPASS, EPI_SPLIT>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+        case EPI_SNAKE: return launch_tc3_pick<BN, NPASS, EPI_SNAKE>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+        case EPI_HEAD: return launch_tc3_pick<BN, NPASS, EPI_HEAD>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+        case EPI_QKV: return launch_tc3_pick<BN, NPASS, EPI_QKV>(p, a_hi, a_lo, b_hi, b_lo, o0, o1, num_sms, st);
+        default: break;
     }
     return cudaErrorInvalidValue;
 }
@@ -601,7 +607,7 @@ cudaError_t launch_gemm_tc3(const gemm_params & p, const CUtensorMap & tmA_hi, c
                             const CUtensorMap & tmB_hi, const CUtensorMap & tmB_lo, const CUtensorMap & tmO0,
                             const CUtensorMap & tmO1, int bn, int num_sms, cudaStream_t st) {
     if (p.M <= 0) return cudaSuccess;
-    if (p.K % G3_BK != 0 || (p.taps != 1 && p.taps != 3)) return cudaErrorInvalidValue;
+    if (p.K % G3_BK != 0 || (p.taps != 1 && p.taps != 3 && p.taps != 5) || (p.bf16 && p.npass != 1)) return cudaErrorInvalidValue;
     if (bn == 256) {
         if (p.npass == 3) return launch_tc3_epi<256, 3>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, num_sms, st);
         return launch_tc3_epi<256, 1>(p, tmA_hi, tmA_lo, tmB_hi, tmB_lo, tmO0, tmO1, num_sms, st);

@@ -4,7 +4,7 @@
 // and the parity tests use it to separate tensor-core plumbing / accumulation effects from model bugs
 // (profiles/r2_parity_attribution.md).
 //
-// Tap-GEMM: D[m][n] = sum_{tap} sum_k A[m + tap - (taps==3)][k] * B[n][tap*K + k].
+// Tap-GEMM: D[m][n] = sum_{tap} sum_k A[m + tap - taps/2][k] * B[n][tap*K + k].
 #include "kernels.cuh"
 #include "ptx.cuh"
 
@@ -151,6 +151,9 @@ __device__ __forceinline__ void gemm_epilogue(const gemm_params & p, int row, in
 // Selected with mio_ctx_set_option("gemm", "simt"); used by the parity tests to separate tensor-core plumbing
 // bugs from model bugs.  64x64 tile, 256 threads, 2 rows x 8 columns per thread.
 // ---------------------------------------------------------------------------------------------
+// BF16-stored matrices keep their bit patterns in the __half buffers (npass 1)
+__device__ __forceinline__ float bf16_bits_to_float(__half h) { return __uint_as_float((uint32_t) __half_as_ushort(h) << 16); }
+
 template <int EPI>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(const gemm_params p) {
     __shared__ float As[16][64 + 1];
@@ -159,7 +162,7 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const gemm_params p) {
     const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
     const int tr = (tid >> 3) * 2, tc = (tid & 7) * 8;
     const int Ktot = p.taps * p.K;
-    const int shift0 = (p.taps == 3) ? -1 : 0;
+    const int shift0 = -(p.taps / 2);
     float acc[2][8];
 #pragma unroll
     for (int i = 0; i < 2; i++)
@@ -173,14 +176,14 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const gemm_params p) {
             const int ar = m0 + r + tap + shift0;
             float a = 0.f;
             if (ar >= 0 && ar < p.a_rows) {
-                a = __half2float(p.a_hi[(size_t) ar * p.lda + kc]);
+                a = p.bf16 ? bf16_bits_to_float(p.a_hi[(size_t) ar * p.lda + kc]) : __half2float(p.a_hi[(size_t) ar * p.lda + kc]);
                 if (p.npass == 3) a += __half2float(p.a_lo[(size_t) ar * p.lda + kc]);
             }
             As[kk][r] = a;
             const int bn = n0 + r;
             float b = 0.f;
             if (bn < p.N) {
-                b = __half2float(p.b_hi[(size_t) bn * Ktot + kg]);
+                b = p.bf16 ? bf16_bits_to_float(p.b_hi[(size_t) bn * Ktot + kg]) : __half2float(p.b_hi[(size_t) bn * Ktot + kg]);
                 if (p.npass == 3) b += __half2float(p.b_lo[(size_t) bn * Ktot + kg]);
             }
             Bs[kk][r] = b;

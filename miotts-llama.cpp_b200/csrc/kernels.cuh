@@ -21,8 +21,9 @@ enum epi_kind : int {
 };
 
 struct gemm_params {
-    int M = 0, N = 0, K = 0, taps = 1;     // D[M][N] = sum_tap A[row + tap - (taps==3)][K] * B[N][tap*K + k]
+    int M = 0, N = 0, K = 0, taps = 1;     // D[M][N] = sum_tap A[row + tap - taps/2][K] * B[N][tap*K + k], taps 1 / 3 / 5
     int npass = 3;                         // 3: (a_hi + a_lo)(b_hi + b_lo) without lo*lo; 1: a_hi * b_hi
+    int bf16 = 0;                          // npass 1 only: both operands hold BF16 bit patterns (BF16-stored matrices)
     int mma_order = 2;                     // MIO_MMA_ORDER: 2 (default) = pass-major inside a 64-wide k-block (4 x hi*hi, 4 x
                                            // hi*lo, 4 x lo*hi), 0 / 1 = the three passes interleaved per 16-wide k step
     int chunk = 0;                         // > 0: chunked accumulation (gemm3.cu): a fresh tensor-core accumulator every chunk * 64 of K,
@@ -105,8 +106,12 @@ cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map
 cudaError_t launch_split(const float * x, int rows, int C, const row_map & rm, int row_div, __half * hi, __half * lo,
                          cudaStream_t st);
 // mod[voice][cond_rows] = W[cond_rows][128] * silu(emb[voice]) + b
+// row_store[cond_rows] (or nullptr): 1 / 2 where the row's matrix is stored as F16 / BF16 -> silu(emb) rounded to that type
 cudaError_t launch_cond(const float * voice_table, int n_voices, int adaln_dim, const float * w, const float * b,
-                        int cond_rows, float * silu_scratch /*[n_voices*adaln_dim]*/, float * mod, cudaStream_t st);
+                        int cond_rows, const uint8_t * row_store, float * silu_scratch /*[n_voices*adaln_dim]*/, float * mod,
+                        cudaStream_t st);
+// (hi, lo) fp16 operand pair -> BF16 bit patterns in the hi buffer, in place (BF16-stored matrices); n even
+cudaError_t launch_pair_to_bf16(__half * hi, const __half * lo, size_t n, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------ ISTFT
 struct istft_params {

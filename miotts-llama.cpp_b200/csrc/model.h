@@ -23,6 +23,7 @@ struct hparams {                      // defaults: src/miocodec.cpp:59-85
     float rope_theta = 10000.f, norm_eps = 1e-5f, gn_eps = 1e-6f;
     int vocab = 12800;
     int up_factor[4] = {3, 3, 1, 1}, up_kernel[4] = {9, 9, 1, 1}, up_ch[4] = {256, 128, 0, 0};
+    int up_res[4] = {6, 18, 0, 0};   // rows per code after stage s: 2 * f_0 * ... * f_s
     int out_proj_dim = 512;
     int frames_per_code = 18;
 };
@@ -31,6 +32,9 @@ struct hparams {                      // defaults: src/miocodec.cpp:59-85
 struct gemm_weight {
     int N = 0, K = 0, taps = 1;       // Ktot = taps*K
     int npass = 3;                    // 3 = split precision (hi*hi + hi*lo + lo*hi), 1 = fp16 operands (conv1d)
+    int store = 0;                    // how the file stores the matrix: 0 F32, 1 F16, 2 BF16.  1 / 2: the reference rounds the
+                                      // activations to that type and multiplies once (ggml-cpu.c:1291-1326) -> npass 1, and
+                                      // for 2 both operands hold BF16 bit patterns
     float out_scale = 1.f;            // epilogue multiplier (inverse of the power-of-two weight pre-scale)
     __half * hi = nullptr;
     __half * lo = nullptr;
@@ -66,6 +70,7 @@ struct weights {
     std::vector<dec_layer_w> dec;
     // all AdaLN conditioning linears stacked: rows = 16*1536 + 1024, K = 128 (fp32; tiny GEMV per utterance)
     float * cond_w = nullptr; float * cond_b = nullptr; int cond_rows = 0;
+    uint8_t * cond_store = nullptr;               // [cond_rows] storage type of the matrix each row came from (gemm_weight::store)
     std::vector<gemm_weight> upT; std::vector<float *> upT_b, snake_ea, snake_eb;   // per stage
     gemm_weight out_proj; float *out_proj_b, *out_snake_ea, *out_snake_eb;
     gemm_weight head; float * head_b;             // columns interleaved (logmag_f, phase_f)

@@ -15,7 +15,7 @@ import os
 import struct
 import numpy as np
 
-GGML_F32, GGML_F16, GGML_I32 = 0, 1, 26
+GGML_F32, GGML_F16, GGML_I32, GGML_BF16 = 0, 1, 26, 30
 _KV_U32, _KV_F32, _KV_STR = 4, 6, 8
 _ALIGN = 32
 
@@ -26,7 +26,7 @@ def _s(b: str) -> bytes:
 
 
 class GGUFWriter:
-    """Tiny GGUF v3 writer: u32 / f32 / string KVs, F32 / F16 / I32 tensors."""
+    """Tiny GGUF v3 writer: u32 / f32 / string KVs, F32 / F16 / BF16 / I32 tensors."""
 
     def __init__(self, arch: str):
         self.kv: list[tuple[str, int, object]] = [("general.architecture", _KV_STR, arch)]
@@ -36,7 +36,12 @@ class GGUFWriter:
     def add_f32(self, k, v): self.kv.append((k, _KV_F32, float(v)))
     def add_str(self, k, v): self.kv.append((k, _KV_STR, str(v)))
 
-    def add_tensor(self, name: str, arr: np.ndarray):
+    def add_tensor(self, name: str, arr: np.ndarray, bf16: bool = False):
+        if bf16:     # arr: float32 values -> BF16 bit patterns (round to nearest even), stored as uint16
+            b = np.ascontiguousarray(arr, dtype=np.float32).view(np.uint32)
+            b = ((b + 0x7FFF + ((b >> 16) & 1)) >> 16).astype(np.uint16)
+            self.tensors.append((name, b, GGML_BF16))
+            return
         if arr.dtype == np.float32: t = GGML_F32
         elif arr.dtype == np.float16: t = GGML_F16
         elif arr.dtype == np.int32: t = GGML_I32
@@ -149,9 +154,29 @@ def synth_tensors(seed: int = 0, hp: dict | None = None, scale_embd: float = 0.0
     return hp, out
 
 
-def write_codec_gguf(path: str, seed: int = 0, hp: dict | None = None, f16_matrices: bool = False) -> dict:
-    """Write a random-init miocodec.gguf; returns the hyper-parameter dict used."""
+def bf16_round(a: np.ndarray) -> np.ndarray:
+    """float32 -> nearest BF16 value (ties to even), returned as float32."""
+    b = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+    return (((b + 0x7FFF + ((b >> 16) & 1)) >> 16) << 16).astype(np.uint32).view(np.float32)
+
+
+def write_codec_gguf(path: str, seed: int = 0, hp: dict | None = None, f16_matrices: bool = False,
+                     matrices: str = "f32", convs: str | None = None, pre_round: str | None = None) -> dict:
+    """Write a random-init miocodec.gguf; returns the hyper-parameter dict used.
+
+    matrices: storage type of the 2-D matrices (linear layers, conditioning linears, token table): "f32" | "f16" | "bf16".
+    convs:    storage type of the conv / ConvTranspose kernels: "f32" | "f16" (default: "f16" when matrices == "f16").
+    pre_round: round the VALUES of those tensors to "f16" / "bf16" but keep the storage chosen above -- two files that
+              hold identical numbers in different storage types isolate the reference's activation rounding.
+    f16_matrices: the round-1 switch (F16 for everything >= 2-D but the token table and the conditioning linears).
+    """
+    hp = dict(hp or {})
+    if "up_factors" in hp and "samples_per_token" not in hp:
+        fpc = 2 * int(np.prod(hp["up_factors"]))
+        hp["samples_per_token"] = fpc * hp.get("hop_length", DEFAULT_HP["hop_length"])
     hp, tensors = synth_tensors(seed, hp)
+    if convs is None:
+        convs = "f16" if matrices == "f16" else "f32"
     w = GGUFWriter("miocodec")
     for k in ("sample_rate", "n_fft", "hop_length", "samples_per_token"):
         w.add_u32("miocodec." + k, hp[k])
@@ -168,6 +193,15 @@ def write_codec_gguf(path: str, seed: int = 0, hp: dict | None = None, f16_matri
     for name, arr in tensors:
         if f16_matrices and arr.ndim >= 2 and name != "token_embd" and not name.endswith("_cond.weight"):
             arr = arr.astype(np.float16)
+        elif arr.dtype == np.float32 and arr.ndim >= 2:
+            kind = matrices if arr.ndim == 2 else convs
+            rnd = pre_round if pre_round is not None else kind
+            if rnd == "f16": arr = arr.astype(np.float16).astype(np.float32)
+            elif rnd == "bf16": arr = bf16_round(arr)
+            if kind == "f16": arr = arr.astype(np.float16)
+            elif kind == "bf16":
+                w.add_tensor(name, arr, bf16=True)
+                continue
         w.add_tensor(name, arr)
     w.write(path)
     return hp

@@ -156,6 +156,23 @@ def ref_stream_session(gguf_path: str, voice_path: str, codes, skip_llm: bool = 
     return out[:n].copy(), chunks[: nch.value].copy(), stats
 
 
+def ref_tts_skip_llm(gguf_path: str, voice_path: str, text: str, peak_normalize: bool = True, wav_path: str | None = None,
+                     max_samples: int = 1764 * 4096):
+    """The reference's TestToSpeech::synthesize_to_vector (and synthesize_to_file when wav_path is given) with skip_llm on
+    raw token text.  Returns the samples, or None when the reference refuses the request."""
+    L = C.CDLL(lib_path())
+    L.mio_ref_tts_skip_llm.restype = C.c_long
+    L.mio_ref_tts_skip_llm.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_void_p, C.c_long]
+    out = np.empty(max_samples, dtype=np.float32)
+    n = L.mio_ref_tts_skip_llm(gguf_path.encode(), voice_path.encode(), text.encode(), int(peak_normalize),
+                               wav_path.encode() if wav_path else None, out.ctypes.data, out.size)
+    if n == -1:
+        return None
+    if n < 0:
+        raise RuntimeError(f"mio_ref_tts_skip_llm failed ({n})")
+    return out[:n].copy()
+
+
 def ref_istft_tables(n_fft: int = 392, win_length: int = 392) -> dict:
     """The tables of the reference's istft_cache (src/istft.cpp:7-41), through its own getters."""
     L = C.CDLL(lib_path())

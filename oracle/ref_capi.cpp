@@ -196,6 +196,31 @@ long mio_ref_stream_session(const char * codec_gguf, const char * voice_path, co
     return rc;
 }
 
+// TestToSpeech::synthesize_to_vector / synthesize_to_file with skip_llm (/root/reference/src/test-to-speech.cpp:248-345):
+// `text` is raw "<|s_N|>" token text (anything else in it is skipped by the reference's own parser).  wav_path != NULL
+// writes the file through the reference's writer; out (may be NULL) receives the samples.  Returns the sample count,
+// -1 when the reference refuses the request (e.g. no codes parse), < -1 on set-up errors.
+long mio_ref_tts_skip_llm(const char * codec_gguf, const char * voice_path, const char * text, int peak_normalize,
+                          const char * wav_path, float * out, long out_cap) {
+    stderr_mute m;
+    TestToSpeech::Config cfg;
+    cfg.codec_path = codec_gguf;
+    TestToSpeech tts(cfg);
+    VoiceModel voice;
+    if (!tts.is_ready() || !voice.load_from_file(voice_path)) return -2;
+    TestToSpeech::Options opt;
+    opt.skip_llm = true;
+    opt.apply_peak_normalization = peak_normalize != 0;
+    std::vector<float> audio;
+    if (!tts.synthesize_to_vector(voice, text, audio, opt)) return -1;
+    if (wav_path && !tts.synthesize_to_file(voice, text, wav_path, opt)) return -1;
+    if (out) {
+        if ((long) audio.size() > out_cap) return -3;
+        memcpy(out, audio.data(), audio.size() * sizeof(float));
+    }
+    return (long) audio.size();
+}
+
 // wav_write (/root/reference/src/wav-writer.cpp:24-45): 44-byte RIFF header + PCM16 (clamp(s*32767) truncated).
 int mio_ref_wav_write(const char * path, const float * samples, long n, int sample_rate) {
     return wav_write(std::string(path), std::vector<float>(samples, samples + n), sample_rate) ? 0 : -1;

@@ -66,17 +66,17 @@ def reference_floor(gguf, codes, emb):
         return FLOOR_SNR_DB, FLOOR_MAXABS
     waves = []
     for tag in ("v3", "v4"):
-        if tag not in _floor_refs:
+        if (tag, gguf) not in _floor_refs:
             old = os.environ.get("MIO_REF_VARIANT")
             os.environ["MIO_REF_VARIANT"] = tag
             try:
-                _floor_refs[tag] = ref.Reference(gguf)
+                _floor_refs[(tag, gguf)] = ref.Reference(gguf)
             finally:
                 if old is None:
                     os.environ.pop("MIO_REF_VARIANT", None)
                 else:
                     os.environ["MIO_REF_VARIANT"] = old
-        waves.append(_floor_refs[tag].decode_wave(codes, emb))
+        waves.append(_floor_refs[(tag, gguf)].decode_wave(codes, emb))
     return snr_db(waves[0], waves[1]), float(np.abs(waves[0] - waves[1]).max())
 
 

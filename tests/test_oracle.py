@@ -157,3 +157,54 @@ def test_reference_orchestrator_live_session(assets):
     a2, ch2, st2 = ref.ref_stream_session(assets[0], assets[1][vid], g["codes"][:30], skip_llm=True)
     assert np.array_equal(a2, R.decode_wave(g["codes"][:30], synth.synth_voice(vid))) and st2["decode_calls"] == 0
     R.close()
+
+
+VARIANTS = {
+    "kernels [7,5]": (dict(hp=dict(up_kernels=(7, 5))), 57.0),
+    "kernels [15,3]": (dict(hp=dict(up_kernels=(15, 3))), 57.0),
+    "factors [2,2], widths 384/192, out_proj 448": (dict(hp=dict(up_factors=(2, 2), up_kernels=(4, 10), up_channels=(384, 192), out_proj_dim=448)), 57.0),
+    "factors [1,9]": (dict(hp=dict(up_factors=(1, 9), up_kernels=(3, 27))), 57.0),
+    "F16 matrices + kernels": (dict(matrices="f16"), 47.0),
+    "BF16 matrices": (dict(matrices="bf16"), 31.0),
+}
+
+
+@pytest.mark.parametrize("name", list(VARIANTS))
+def test_port_follows_the_reference_on_other_geometries_and_storage_types(tmp_path, name):
+    """SURVEY.md row A16 / Appendix A 'Linear': the geometry of the upsampler is read from the file, and matrices
+    stored as F16 / BF16 make ggml round the activations to that type.  The port, told the storage types, must land at
+    the reference's own cross-build distance for such a file (F32 ~59.5 dB, F16 ~49.5 dB, BF16 ~34.5 dB); told
+    nothing, it sits measurably further away (checked for F16)."""
+    from miocodec_b200 import synth
+    from oracle import port, ref
+    if not ref.available():
+        pytest.skip("oracle/_ref is not built on this host")
+    kw, bar = VARIANTS[name]
+    path = str(tmp_path / "variant.gguf")
+    hp = synth.write_codec_gguf(path, seed=2, **kw)
+    _, tensors = synth.synth_tensors(2, kw.get("hp"))
+    W, store = dict(tensors), {}
+    kind = kw.get("matrices", "f32")
+    if kind != "f32":
+        for n, a in tensors:
+            if a.dtype == np.float32 and a.ndim >= 2:
+                if a.ndim == 2:
+                    W[n] = a.astype(np.float16).astype(np.float32) if kind == "f16" else synth.bf16_round(a)
+                    store[n] = kind
+                elif kind == "f16":
+                    W[n] = a.astype(np.float16).astype(np.float32)
+                    store[n] = "f16"
+    codes, emb = synth.synth_codes(40, 3), synth.synth_voice(2)
+    R = ref.Reference(path)
+    want = R.decode_spec(codes, emb)
+    R.close()
+    got = port.decode(W, hp, codes, emb, store=store)
+    fpc = hp["samples_per_token"] // hp["hop_length"]
+    assert got.shape == want.shape == (fpc * 40, 394)
+    s = snr_db(got, want)
+    print(f"{name}: port vs reference {s:.2f} dB")
+    assert s > bar
+    if kind == "f16":
+        blind = snr_db(port.decode(W, hp, codes, emb), want)
+        print(f"{name}: port ignoring the storage type {blind:.2f} dB")
+        assert blind < s - 0.2
