@@ -59,6 +59,25 @@ def make_workload(name: str, rank: int, world: int):
     return dict(desc=desc, lens=lens, cu=cu, codes=codes, voice_table=vt, voice_ids=vids)
 
 
+def bench_config(wl, world: int):
+    """The `config` object of the JSON line: identical in both arms (--impl b200 / --impl reference) by construction."""
+    total_codes = int(wl["cu"][-1])
+    return {"workload": wl["desc"], "codes_per_gpu_per_step": total_codes,
+            "audio_s_per_gpu_per_step": total_codes * 1764 / 44100.0,
+            "weights": "random-init miocodec.gguf layout, seed 0", "parallelism": f"utterance-sharded x{world}",
+            "l2": "per-step working set (GBs of activations) far exceeds the 126 MB L2; no explicit flush"}
+
+
+def mem_available_bytes() -> int:
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) * 1024
+    except OSError:
+        pass
+    return 0
+
+
 class stdout_to_stderr:
     """Route C-level stdout (fd 1) to stderr while NCCL initialises: its version banner goes to stdout and the
     contract is ONE JSON line there."""
@@ -196,7 +215,7 @@ def run_reference(args):
     sample = f"{n_utts} utterances of the workload ({audio_s:.0f} audio-s) per step, {procs} independent reference contexts x 4 ggml threads"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": {"workload": wl["desc"], "sample": sample},
+            "dtype": "f32", "data": "synthetic", "config": bench_config(wl, args.gpus),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs * 4, "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -204,55 +223,240 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------ streaming (C4)
+def streaming_session(codec, S: int, N: int):
+    """S concurrent streams of N codes in lock-step under the reference's streaming policy (full-prefix re-decode at the
+    commit cadence, src/test-to-speech.cpp:499-571).  Codes are pushed 20 at a time (the cadence is evaluated per code inside
+    the library, so the decode schedule is the one-code-per-tick schedule of the reference).  Returns (emitted samples,
+    wall seconds, StreamProfile counters of stream 0)."""
+    from miocodec_b200 import synth
+    streams = [codec.open_stream(synth.synth_voice(i % N_VOICES)) for i in range(S)]
+    codes = [synth.synth_codes(N, 4000 + i) for i in range(S)]
+    t0 = time.perf_counter()
+    emitted = 0
+    for k in range(0, N, 20):
+        for i, st in enumerate(streams):
+            st.push(codes[i][k:k + 20])
+            if k + 20 >= N:
+                st.finish()
+        codec.step_streams(streams)
+        for st in streams:
+            while True:                       # 256k-sample reads: a 16 MB buffer per read costs more than the copy
+                a, _ = st.read(1 << 18)
+                emitted += a.size
+                if a.size < (1 << 18):
+                    break
+    dt = time.perf_counter() - t0
+    stats = streams[0].stats()
+    for st in streams:
+        st.close()
+    return emitted, dt, stats
+
+
+def cpu_streaming_baseline(N: int):
+    """The reference's OWN streaming session (oracle/_ref: unmodified src/test-to-speech.cpp LLM branch, scripted stub
+    LLM, the reference's CPU codec on its fixed 4 ggml threads) for ONE stream of N codes: emitted audio-s per second."""
+    from miocodec_b200 import synth
+    from oracle import ref
+    if not ref.available():
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref unavailable on this host"}
+    gguf, voices = synth.ensure_assets()
+    codes = synth.synth_codes(N, 4000)
+    t0 = time.perf_counter()
+    out, chunks, st = ref.ref_stream_session(gguf, voices[0], codes)
+    dt = time.perf_counter() - t0
+    return {"value": (len(out) / 44100.0) / dt, "unit": UNIT, "cores": 4, "kind": "reference", "seconds": dt,
+            "decode_calls": st["decode_calls"], "decoded_codes": st["decoded_codes"],
+            "sample": f"1 stream of {N} codes through TestToSpeech::synthesize_stream_profiled (stub LLM, model load included), 4 ggml threads"}
+
+
+def c4_block(codec, S: int = 1024, N: int = 700, sessions: int = 1, cpu: bool = True):
+    streaming_session(codec, 32, 100)                     # warm-up: stream state, pinned emit buffers, shapes
+    runs = [streaming_session(codec, S, N) for _ in range(sessions)]
+    emitted, _, st = runs[-1]
+    dt = float(np.mean([r[1] for r in runs]))
+    audio_s = emitted / codec.sample_rate
+    redecode = st["decoded_codes"] / N
+    peaks = measured_peaks()
+    ach = FLOP_PER_CODE * st["decoded_codes"] * S / dt / 1e12
+    blk = {"metric": "streaming codec+ISTFT emitted audio-sec/sec", "value": audio_s / dt, "unit": UNIT, "seconds_per_session": dt,
+           "sessions": sessions, "workload": f"C4: {S} concurrent streams x {N} codes, lock-step, reference streaming policy",
+           "decode_calls_per_stream": st["decode_calls"], "decoded_codes_per_stream": st["decoded_codes"],
+           "redecode_factor": redecode, "decoded_audio_s_per_s": audio_s * redecode / dt,
+           "timing": "host wall clock around the whole session: pushes, steps, D2H of every emitted chunk into host buffers",
+           "roofline": {"bound": "tensor", "unit": "TFLOP/s", "peak": peaks["tf_sus"], "achieved": ach, "frac": ach / peaks["tf_sus"],
+                        "note": "algorithmic FLOPs of the codes the policy re-decodes / session wall time"}}
+    if cpu:
+        try:
+            blk["cpu_baseline"] = cpu_streaming_baseline(N)
+        except Exception as e:  # noqa: BLE001
+            blk["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"}
+    return blk
+
+
 def run_streaming(args):
-    """BASELINE config C4: 1024 concurrent streams per GPU, 700 codes each, lock-step, the reference's streaming policy
-    (full-prefix re-decode at the commit cadence).  Metric: EMITTED audio-seconds per wall-second (the policy re-decodes
-    ~10x the emitted audio).  Codes are pushed 20 at a time (the cadence is evaluated per code inside the library, so
-    the decode schedule is the one-code-per-tick schedule of the reference)."""
+    """--workload c4: BASELINE config C4 alone (1024 concurrent streams per GPU, 700 codes each).  Metric: EMITTED
+    audio-seconds per wall-second (the policy re-decodes ~10x the emitted audio)."""
     import torch
     from miocodec_b200 import binding, synth
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     gguf, _ = synth.ensure_assets()
     codec = binding.MioCodec(gguf, local)
-    S, N = 1024, 700
-
-    def session():
-        streams = [codec.open_stream(synth.synth_voice(i % N_VOICES)) for i in range(S)]
-        codes = [synth.synth_codes(N, 4000 + i) for i in range(S)]
-        t0 = time.perf_counter()
-        emitted = 0
-        for k in range(0, N, 20):
-            for i, s in enumerate(streams):
-                s.push(codes[i][k:k + 20])
-                if k + 20 >= N:
-                    s.finish()
-            codec.step_streams(streams)
-            for s in streams:
-                while True:                       # 256k-sample reads: a 16 MB buffer per read costs more than the copy
-                    a, _ = s.read(1 << 18)
-                    emitted += a.size
-                    if a.size < (1 << 18):
-                        break
-        dt = time.perf_counter() - t0
-        st = streams[0].stats()
-        for s in streams:
-            s.close()
-        return emitted, dt, st
-
-    session() if args.warmup > 0 else None
-    vals = [session() for _ in range(max(1, min(args.steps, 3)))]
-    emitted, dt, st = vals[-1]
-    dt = float(np.mean([v[1] for v in vals]))
-    audio_s = emitted / codec.sample_rate
-    line = {"metric": "streaming codec+ISTFT emitted audio-sec/sec", "value": audio_s / dt, "unit": UNIT, "n_gpus": 1,
-            "steps": len(vals), "warmup": 1 if args.warmup > 0 else 0, "ms_per_step": dt * 1e3, "higher_is_better": True,
-            "config": {"workload": "C4: 1024 concurrent streams x 700 codes, lock-step, reference streaming policy",
-                       "decode_calls_per_stream": st["decode_calls"], "decoded_codes_per_stream": st["decoded_codes"],
-                       "redecode_factor": st["decoded_codes"] / N},
-            "decoded_audio_s_per_s": audio_s * st["decoded_codes"] / N / dt, "data": "synthetic"}
+    blk = c4_block(codec, sessions=max(1, min(args.steps, 3)), cpu=not args.no_cpu_baseline)
+    line = {"metric": blk["metric"], "value": blk["value"], "unit": UNIT, "n_gpus": 1, "steps": blk["sessions"], "warmup": 1,
+            "ms_per_step": blk["seconds_per_session"] * 1e3, "higher_is_better": True, "data": "synthetic",
+            "config": {"workload": blk["workload"]}, **{k: v for k, v in blk.items() if k not in ("metric", "value", "unit", "workload")}}
     print(json.dumps(line))
     codec.close()
+
+
+# ------------------------------------------------------------------------------------------------ latency (C2)
+def c2_block(codec, stream, cpu: bool = True):
+    """BASELINE config C2: ONE 700-code utterance, batch 1.  Device time per decode (CUDA events, resident input) and the
+    host-to-host latency of the synchronous single-utterance call."""
+    import torch
+    wl = make_workload("c2", 0, 1)
+    emb = wl["voice_table"][int(wl["voice_ids"][0])]
+    codec.batch_upload(wl["codes"], wl["cu"], wl["voice_table"], wl["voice_ids"])
+    for _ in range(5):
+        codec.batch_run(False)
+    codec.batch_sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    runs = 50
+    e0.record(stream)
+    for _ in range(runs):
+        codec.batch_run(False)
+    e1.record(stream)
+    codec.batch_sync()
+    dev_ms = e0.elapsed_time(e1) / runs
+    launches = codec.kernel_launches()
+    lat = []
+    for i in range(103):
+        t1 = time.perf_counter()
+        codec.decode_wave(wl["codes"], emb)
+        if i >= 3:
+            lat.append((time.perf_counter() - t1) * 1e3)
+    lat.sort()
+    audio_s = 700 * codec.samples_per_token / codec.sample_rate
+    blk = {"workload": wl["desc"], "device_ms": dev_ms, "launches": launches, "value": audio_s / (dev_ms / 1e3), "unit": UNIT,
+           "latency": {"p50_ms": lat[len(lat) // 2], "p99_ms": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "min_ms": lat[0],
+                       "runs": len(lat), "call": "mio_decode_wave (pageable host buffers, synchronous)"},
+           "e2e": {"value": audio_s / (lat[len(lat) // 2] / 1e3), "unit": UNIT, "h2d_bytes_per_step": 700 * 4 + 128 * 4,
+                   "d2h_bytes_per_step": 700 * codec.samples_per_token * 4}}
+    if cpu:
+        try:
+            from oracle import ref
+            if ref.available():
+                v, a_s, busy, wall = cpu_reference_run(wl, 1, 1)
+                blk["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 4, "kind": "reference", "ms": busy * 1e3,
+                                       "sample": "the same utterance, once, 1 reference context = 4 ggml threads + 1-thread ISTFT"}
+        except Exception as e:  # noqa: BLE001
+            blk["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"}
+    return blk
+
+
+# ------------------------------------------------------------------------------------------------ strong scaling (C5)
+def c5_block(codec, stream, rank: int, world: int, local: int, barrier, sweeps: int = 2):
+    """BASELINE config C5 as stated: ONE sweep of 4096 utterances (50-750 codes, 2-30 s), sharded by utterance over the
+    ranks (strong scaling).  Device-resident time, and three end-to-end deliveries of PCM16 audio to the host:
+      per_rank_host   every rank copies its shard into its own pinned buffer (N consumers)
+      gather_rank0    the path's one exchange step: shards go to rank 0 over NCCL/NVLink size-exact, rank 0 copies them to
+                      ONE pinned buffer (copy of shard r overlapped with the arrival of shard r+1)
+      shared_pinned   every rank copies its shard straight into its slice of ONE /dev/shm buffer page-locked by all ranks
+    All times: max over ranks of the host wall clock between barriers (device idle on both sides)."""
+    import torch
+    import torch.distributed as dist
+    from miocodec_b200 import binding, sharding
+    wl = make_workload("c5", rank, world)
+    rng = np.random.default_rng(5)
+    all_lens = rng.integers(50, 751, size=4096)
+    spc = codec.samples_per_token
+    counts = sharding.shard_counts(all_lens, world, spc)
+    total = int(sum(counts))
+    mine = counts[rank]
+    audio_all = total / codec.sample_rate
+    blk = {"workload": wl["desc"], "utterances": 4096, "total_codes": int(all_lens.sum()), "audio_s": audio_all, "scaling": "strong",
+           "sweeps": sweeps, "delivery": "PCM16 (2 bytes per sample; the float32 form is the headline block's e2e)"}
+
+    def tmax(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
+    # ---- device resident
+    codec.batch_upload(wl["codes"], wl["cu"], wl["voice_table"], wl["voice_ids"])
+    codec.batch_run(False)
+    codec.batch_sync()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(sweeps):
+        codec.batch_run(False)
+    e1.record(stream)
+    barrier()
+    ms = tmax(e0.elapsed_time(e1)) / sweeps
+    blk.update(ms_per_sweep=ms, value=audio_all / (ms / 1e3), unit=UNIT, gpu_launches_per_sweep=codec.kernel_launches())
+
+    need = (total + (total if world > 1 else 0)) * 2           # all ranks' pinned shards + rank 0's gathered copy, one box
+    short = 1.0 if mem_available_bytes() < 3 * need + (8 << 30) else 0.0
+    if tmax(short) > 0.0:                                       # a collective decision: every rank skips or none does
+        blk["e2e"] = {"skipped": f"host has {mem_available_bytes() >> 30} GiB available, the pinned delivery buffers need {need >> 30} GiB"}
+        return blk
+    h_codes = binding.pinned_empty(len(wl["codes"]), np.int32); h_codes[:] = wl["codes"]
+    h_pcm = binding.pinned_empty(mine, np.int16)
+
+    def timed(fn):
+        fn()                                   # warm-up (first touch of the buffers, NCCL channels)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(sweeps):
+            fn()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        barrier()
+        return tmax(dt) / sweeps
+
+    def per_rank():
+        codec.decode_pcm16_batch(h_codes, wl["cu"], wl["voice_table"], wl["voice_ids"], out=h_pcm)
+    s1 = timed(per_rank)
+    e2e = {"per_rank_host": {"value": audio_all / s1, "unit": UNIT, "ms_per_sweep": s1 * 1e3,
+                             "h2d_bytes": int(len(wl["codes"]) * 4), "d2h_bytes": int(mine * 2)}}
+    if world > 1:
+        host_all = torch.empty(total, dtype=torch.int16).pin_memory() if rank == 0 else None
+
+        def gathered():
+            codec.batch_upload(h_codes, wl["cu"], wl["voice_table"], wl["voice_ids"])
+            codec.batch_run(False)
+            ptr, n = codec.pcm16_device()
+            sharding.gather_to_rank0(sharding.device_tensor(ptr, n, "int16", local), counts, host_all)
+        s2 = timed(gathered)
+        e2e["gather_rank0_nccl"] = {"value": audio_all / s2, "unit": UNIT, "ms_per_sweep": s2 * 1e3,
+                                    "nvlink_bytes_to_rank0": int((total - counts[0]) * 2), "d2h_bytes_rank0": int(total * 2)}
+        if rank == 0:      # placement check: rank 0's own shard lands at offset 0 of the rank-major buffer
+            assert np.array_equal(host_all[: counts[0]].numpy()[:4096], h_pcm[:4096])
+        del host_all
+        try:
+            name = f"mio_c5_{os.environ.get('MASTER_PORT', '0')}"
+            off = int(sum(counts[:rank]))
+            if rank == 0:
+                shared = sharding.SharedPinnedBuffer(name, total, np.int16, off, mine, create=True)
+            barrier()
+            if rank != 0:
+                shared = sharding.SharedPinnedBuffer(name, total, np.int16, off, mine, create=False)
+
+            def direct():
+                codec.decode_pcm16_batch(h_codes, wl["cu"], wl["voice_table"], wl["voice_ids"], out=shared.mine)
+            s3 = timed(direct)
+            e2e["shared_pinned"] = {"value": audio_all / s3, "unit": UNIT, "ms_per_sweep": s3 * 1e3, "d2h_bytes_per_rank": int(mine * 2)}
+            ok = np.array_equal(np.asarray(shared.mine[:4096]), h_pcm[:4096])
+            barrier()
+            shared.close(unlink=(rank == 0))
+            assert ok
+        except Exception as e:  # noqa: BLE001
+            e2e["shared_pinned"] = {"skipped": f"{type(e).__name__}: {e}"}
+    blk["e2e"] = e2e
+    return blk
 
 
 def bind_to_gpu_numa_node(local: int):
@@ -288,6 +492,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-latency", action="store_true",
                     help="skip C2's 100-call latency loop (use under ncu: the loop adds ~16k profiled launches)")
+    ap.add_argument("--no-extra", action="store_true",
+                    help="headline measurement only: skip the c5 (strong scaling + gather), c2 (latency) and c4 (streaming) blocks")
     ap.add_argument("--gemm", default=None)
     ap.add_argument("--chunk", type=int, default=None, help="max_chunk_codes of the context (workspace rows)")
     args = ap.parse_args()
@@ -396,6 +602,15 @@ def main():
                    "runs": len(lat), "call": "mio_decode_wave (pageable host buffers, synchronous)"}
     assert np.isfinite(h_wave[:: max(1, len(h_wave) // 4096)]).all()
 
+    # ---- the other BASELINE configurations, as blocks of the same line (default run only)
+    extra = {}
+    if args.workload == "c3" and not args.no_extra:
+        del h_wave
+        extra["c5"] = c5_block(codec, stream, rank, world, local, barrier)
+        if world == 1:
+            extra["c2"] = c2_block(codec, stream, cpu=not args.no_cpu_baseline)
+            extra["c4"] = c4_block(codec, cpu=not args.no_cpu_baseline)
+
     # ---- max over ranks / whole-job aggregation
     t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
     a = torch.tensor([audio_s], dtype=torch.float64, device="cuda")
@@ -435,9 +650,7 @@ def main():
             "scaling": "strong" if args.workload == "c5" else "weak",   # C5 shards ONE 4096-utterance sweep over the ranks
             "vs_baseline": None,
             "dtype": "f16x2-split operands, f32 accumulate (f16 operands in conv1d like the reference)", "data": "synthetic",
-            "config": {"workload": wl["desc"], "codes_per_gpu_per_step": total_codes, "audio_s_per_gpu_per_step": audio_s,
-                       "weights": "random-init miocodec.gguf layout, seed 0", "parallelism": f"utterance-sharded x{world}", "cpus_bound_per_rank": numa,
-                       "l2": "per-step working set (GBs of activations) far exceeds the 126 MB L2; no explicit flush"},
+            "config": bench_config(wl, world), "cpus_bound_per_rank": numa,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms_max / args.steps},
             "gpu_launches": launches,
@@ -453,6 +666,7 @@ def main():
                                  f"share of step {g['ms'] / prof_ms:.2f}"},
             "stages": stages,
             **({"latency": latency} if latency else {}),
+            **extra,
             "whole_path": {"algorithmic_tflops": FLOP_PER_CODE * total_codes * world * args.steps / (dev_ms_max / 1e3) / 1e12},
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -128,6 +128,10 @@ int  mio_decode_pcm16_batch(mio_ctx * ctx, const int32_t * codes_concat, const i
                             const float * voice_table, int n_voices, const int32_t * voice_ids,
                             int peak_normalize, int16_t * pcm_out, int64_t pcm_cap);
 int  mio_batch_fetch_pcm16(mio_ctx * ctx, int16_t * pcm_out, int64_t pcm_cap);
+/* PCM16 image of the resident waveform, converted on the context's stream and LEFT ON THE DEVICE (int16,
+ * samples_per_token*sum(T); valid until the next upload).  The sharded sweep's one exchange step (the final
+ * gather of variable-length waveforms to the collecting rank) sends this buffer peer to peer.  NULL on error. */
+void * mio_batch_pcm16_device(mio_ctx * ctx);
 /* The 44-byte RIFF/WAVE header wav_write emits (src/wav-writer.cpp:7-37): PCM, mono, 16 bit. */
 int  mio_wav_header(int sample_rate, int64_t n_samples, uint8_t out44[44]);
 /* header + samples to a file: byte-identical to wav_write(path, samples, sample_rate) when pcm came from the

@@ -304,6 +304,14 @@ int mio_batch_fetch_pcm16(mio_ctx * c, int16_t * out, int64_t cap) {
     });
 }
 
+void * mio_batch_pcm16_device(mio_ctx * c) {
+    if (!c) { fail(MIO_ERR_ARG, "bad argument"); return nullptr; }
+    int16_t * p = nullptr;
+    const std::string e = c->E.pcm16_device(&p);
+    if (!e.empty()) { fail(MIO_ERR_CUDA, e); return nullptr; }
+    return p;
+}
+
 // ---- host-side neighbours of the path
 int64_t mio_parse_speech_tokens(const char * text, int64_t text_len, int32_t * out, int64_t cap) {
     if (!text || text_len < 0 || cap < 0 || (!out && cap > 0)) return fail(MIO_ERR_ARG, "bad argument");

@@ -1298,6 +1298,19 @@ std::string engine::fetch_pcm16(int16_t * out, int64_t cap) {
     return {};
 }
 
+// PCM16 image of the resident waveform, left ON THE DEVICE (mio_batch_pcm16_device): converted on the context's stream,
+// valid until the next upload; the multi-GPU gather sends it to the collecting rank over NVLink.
+std::string engine::pcm16_device(int16_t ** out) {
+    *out = nullptr;
+    if (!batch_ran) return "mio_batch_pcm16_device before mio_batch_run";
+    CK(cudaSetDevice(device));
+    std::string e = ensure_pcm();
+    if (!e.empty()) return e;
+    CKR(CAT_PEAK, (double) wave_samples * 6.0, launch_pcm16(d_wave, d_pcm, 0, wave_samples, stream));
+    *out = d_pcm;
+    return {};
+}
+
 // spectrogram of utterance `utt` of a single-chunk batch (mio_decode_spec)
 std::string engine::fetch_spec(int utt, float * out, int64_t cap) {
     if (!batch_ran) return "fetch before run";

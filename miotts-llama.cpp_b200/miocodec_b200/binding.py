@@ -20,7 +20,7 @@ MIO_OK, MIO_ERR_ARG, MIO_ERR_IO, MIO_ERR_FORMAT, MIO_ERR_CUDA, MIO_ERR_RANGE, MI
 # every symbol include/miocodec_b200.h declares (tests check the library exports exactly these)
 EXPORTS = [
     "mio_ctx_create", "mio_istft_ctx_create", "mio_ctx_destroy", "mio_ctx_sample_rate", "mio_ctx_n_fft", "mio_ctx_hop_length",
-    "mio_ctx_samples_per_token", "mio_ctx_frames_per_code", "mio_ctx_vocab", "mio_ctx_device", "mio_ctx_set_option",
+    "mio_batch_pcm16_device", "mio_ctx_samples_per_token", "mio_ctx_frames_per_code", "mio_ctx_vocab", "mio_ctx_device", "mio_ctx_set_option",
     "mio_ctx_set_stream", "mio_voice_load", "mio_print_tensors", "mio_decode_spec", "mio_istft", "mio_decode_wave",
     "mio_decode_wave_batch", "mio_batch_upload", "mio_batch_run", "mio_batch_fetch", "mio_batch_sync",
     "mio_batch_kernel_launches", "mio_batch_wave_device", "mio_stream_default_config", "mio_stream_open",
@@ -79,6 +79,8 @@ def lib() -> C.CDLL:
     L.mio_batch_kernel_launches.restype = i64
     L.mio_batch_wave_device.argtypes = [vp]
     L.mio_batch_wave_device.restype = vp
+    L.mio_batch_pcm16_device.argtypes = [vp]
+    L.mio_batch_pcm16_device.restype = vp
     L.mio_stream_default_config.argtypes = [vp, C.POINTER(StreamConfig)]
     L.mio_stream_default_config.restype = None
     L.mio_stream_open.argtypes = [vp, f32p, C.POINTER(StreamConfig), C.POINTER(vp)]
@@ -252,6 +254,17 @@ class MioCodec:
             out = np.empty(self._total, dtype=np.float32)
         _check(lib().mio_batch_fetch(self._h, out.ctypes.data, out.size))
         return out
+
+    def wave_device(self) -> tuple[int, int]:
+        """(device pointer, samples) of the resident float waveform of the last batch."""
+        return int(lib().mio_batch_wave_device(self._h) or 0), self._total
+
+    def pcm16_device(self) -> tuple[int, int]:
+        """(device pointer, samples) of the PCM16 image of the resident waveform, converted on the context's stream."""
+        p = lib().mio_batch_pcm16_device(self._h)
+        if not p:
+            raise MioError(-3, lib().mio_last_error().decode("utf-8", "replace"))
+        return int(p), self._total
 
     def kernel_launches(self) -> int:
         return int(lib().mio_batch_kernel_launches(self._h))
