@@ -60,6 +60,7 @@ __device__ __forceinline__ uint32_t sw128(int row, int chunk) { return (uint32_t
 // every layer.
 __global__ void attn_bounds_kernel(const int32_t * __restrict__ row_utt, const int32_t * __restrict__ start,
                                    const int32_t * __restrict__ len, int rows, int row_div, int half_w, int2 * __restrict__ bounds) {
+    pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rows) return;
     const int u = row_utt[i / row_div];
@@ -74,7 +75,7 @@ __global__ void attn_bounds_kernel(const int32_t * __restrict__ row_utt, const i
 
 cudaError_t launch_attn_bounds(const row_map & rm, int rows, int row_div, int window, int2 * bounds, cudaStream_t st) {
     if (rows <= 0) return cudaSuccess;
-    attn_bounds_kernel<<<(rows + 255) / 256, 256, 0, st>>>(rm.row_utt, rm.start, rm.len, rows, row_div, window / 2, bounds);
+    launch_k(attn_bounds_kernel, dim3((rows + 255) / 256), dim3(256), 0, st, rm.row_utt, rm.start, rm.len, rows, row_div, window / 2, bounds);
     return cudaGetLastError();
 }
 
@@ -82,6 +83,7 @@ __global__ void __launch_bounds__(128, 4) attention_tc_kernel(
         const __grid_constant__ CUtensorMap tm_in_hi, const __grid_constant__ CUtensorMap tm_in_lo,
         const __grid_constant__ CUtensorMap tm_out_hi, const __grid_constant__ CUtensorMap tm_out_lo,
         int rows, int D, const int2 * __restrict__ bounds, int rev) {
+    pdl_sync();
     extern __shared__ uint8_t at_smem_raw[];
     const uint32_t raw = smem_u32(at_smem_raw);
     uint8_t * smem = at_smem_raw + ((1024u - (raw & 1023u)) & 1023u);
@@ -254,7 +256,7 @@ cudaError_t launch_attention_tc(const CUtensorMap & tm_in_hi, const CUtensorMap 
     if (rows <= 0) return cudaSuccess;
     if (D != n_head * 64 || window / 2 != 32) return cudaErrorInvalidValue;
     dim3 grid((rows + AT_QB - 1) / AT_QB, n_head);
-    attention_tc_kernel<<<grid, 128, AT_SMEM, st>>>(tm_in_hi, tm_in_lo, tm_out_hi, tm_out_lo, rows, D, bounds, rev ? 1 : 0);
+    launch_k(attention_tc_kernel, dim3(grid), dim3(128), AT_SMEM, st, tm_in_hi, tm_in_lo, tm_out_hi, tm_out_lo, rows, D, bounds, rev ? 1 : 0);
     return cudaGetLastError();
 }
 

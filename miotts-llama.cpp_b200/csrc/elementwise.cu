@@ -3,6 +3,7 @@
 // Semantics follow the reference graph (src/miocodec.cpp:205-420) as executed by the ggml CPU backend
 // (formulae: SURVEY.md Appendix A).
 #include "kernels.cuh"
+#include "ptx.cuh"
 
 #include <cuda_bf16.h>
 
@@ -11,6 +12,12 @@
 #include <cstring>
 
 namespace mio {
+
+bool pdl_enabled() {
+    static const bool on = [] { const char * e = getenv("MIO_PDL"); return e && e[0] == '1';   /* off until verified on the GPU: MIO_PDL=1 */ }();
+    return on;
+}
+
 
 __device__ __forceinline__ void split_half(float x, __half & hi, __half & lo) {
     hi = __float2half_rn(x);
@@ -34,6 +41,7 @@ __device__ __forceinline__ float warp_max(float v) {
 // device error flag (the reference aborts in GGML_ASSERT, ggml-cpu/ops.cpp:4811).
 __global__ void gather_embed_kernel(const float4 * __restrict__ table, const int32_t * __restrict__ codes,
                                     float4 * __restrict__ x, int D4, int vocab, int * __restrict__ err) {
+    pdl_sync();
     const int row = blockIdx.x;
     int code = codes[row];
     const bool pad = code < 0;
@@ -52,7 +60,7 @@ __global__ void gather_embed_kernel(const float4 * __restrict__ table, const int
 cudaError_t launch_gather(const float * table, const int32_t * codes_padded, float * x, int rows, int D, int vocab,
                           int * err_flag, cudaStream_t st) {
     if (rows <= 0) return cudaSuccess;
-    gather_embed_kernel<<<rows, 192, 0, st>>>((const float4 *) table, codes_padded, (float4 *) x, D / 4, vocab, err_flag);
+    launch_k(gather_embed_kernel, dim3(rows), dim3(192), 0, st, (const float4 *) table, codes_padded, (float4 *) x, D / 4, vocab, err_flag);
     return cudaGetLastError();
 }
 
@@ -67,6 +75,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(
         const float * __restrict__ mod, int mod_ld, int shift_off, int scale_off,
         const int32_t * __restrict__ row_utt, const int32_t * __restrict__ voice, int row_div,
         __half * __restrict__ out_hi, __half * __restrict__ out_lo, float * __restrict__ out_f32, int rev) {
+    pdl_sync();
     constexpr int D = NV * 128;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int row = (rev ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * 8 + warp;
@@ -137,10 +146,10 @@ cudaError_t launch_layernorm(const float * x, int rows, int D, float eps, const 
     if (rows <= 0) return cudaSuccess;
     const int grid = (rows + 7) / 8;
     if (D == 768) {
-        layernorm_kernel<6><<<grid, 256, 0, st>>>(x, rows, eps, w, b, mod, mod_ld, shift_off, scale_off, rm.row_utt,
+        launch_k(layernorm_kernel<6>, dim3(grid), dim3(256), 0, st, x, rows, eps, w, b, mod, mod_ld, shift_off, scale_off, rm.row_utt,
                                                   rm.voice, row_div, out_hi, out_lo, out_f32, rev ? 1 : 0);
     } else if (D == 512) {
-        layernorm_kernel<4><<<grid, 256, 0, st>>>(x, rows, eps, w, b, mod, mod_ld, shift_off, scale_off, rm.row_utt,
+        launch_k(layernorm_kernel<4>, dim3(grid), dim3(256), 0, st, x, rows, eps, w, b, mod, mod_ld, shift_off, scale_off, rm.row_utt,
                                                   rm.voice, row_div, out_hi, out_lo, out_f32, rev ? 1 : 0);
     } else {
         return cudaErrorInvalidValue;
@@ -168,6 +177,7 @@ __global__ void __launch_bounds__(128) attention_kernel(
         const __half * __restrict__ qkv_hi, const __half * __restrict__ qkv_lo, int rows, int D, int half_w,
         const int32_t * __restrict__ row_utt, const int32_t * __restrict__ start, const int32_t * __restrict__ len,
         int row_div, __half * __restrict__ out_hi, __half * __restrict__ out_lo) {
+    pdl_sync();
     extern __shared__ float att_smem[];
     float * Ks = att_smem;                         // [KROWS][65]
     float * Vs = Ks + ATT_KROWS * ATT_KLD;         // [KROWS][64]
@@ -274,7 +284,7 @@ cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, 
     if (rows <= 0) return cudaSuccess;
     if (D != n_head * 64 || window / 2 != ATT_HALF) return cudaErrorInvalidValue;
     dim3 grid((rows + ATT_QB - 1) / ATT_QB, n_head);
-    attention_kernel<<<grid, 128, ATT_SMEM, st>>>(qkv_hi, qkv_lo, rows, D, window / 2, rm.row_utt, rm.start, rm.len, row_div,
+    launch_k(attention_kernel, dim3(grid), dim3(128), ATT_SMEM, st, qkv_hi, qkv_lo, rows, D, window / 2, rm.row_utt, rm.start, rm.len, row_div,
                                                   out_hi, out_lo);
     return cudaGetLastError();
 }
@@ -293,6 +303,7 @@ cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, 
 __global__ void __launch_bounds__(256) gn_stats_kernel(const float * __restrict__ x, int C, const int32_t * __restrict__ start,
                                                        const int32_t * __restrict__ len, const int32_t * __restrict__ seg_cu,
                                                        int n_utts, int row_div, double2 * __restrict__ part, int rev) {
+    pdl_sync();
     __shared__ float2 red[8][32];
     const int sb = rev ? gridDim.x - 1 - blockIdx.x : blockIdx.x;
     int lo = 0, hi = n_utts;                       // largest u with seg_cu[u] <= sb
@@ -341,6 +352,7 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(const float * __restrict_
 __global__ void __launch_bounds__(256) gn_stats_generic_kernel(const float * __restrict__ x, int C, const int32_t * __restrict__ start,
                                                                const int32_t * __restrict__ len, const int32_t * __restrict__ seg_cu,
                                                                int n_utts, int row_div, double2 * __restrict__ part) {
+    pdl_sync();
     const int sb = blockIdx.x;
     int lo = 0, hi = n_utts;
     while (hi - lo > 1) {
@@ -373,10 +385,10 @@ cudaError_t launch_gn_stats(const float * x, int C, const row_map & rm, int row_
     if (total_segs <= 0) return cudaSuccess;
     if (C <= 0 || C % 32 != 0) return cudaErrorInvalidValue;
     if (C != 512 && C != 256 && C != 128) {
-        gn_stats_generic_kernel<<<total_segs, 256, 0, st>>>(x, C, rm.start, rm.len, seg_cu, rm.n_utts, row_div, part);
+        launch_k(gn_stats_generic_kernel, dim3(total_segs), dim3(256), 0, st, x, C, rm.start, rm.len, seg_cu, rm.n_utts, row_div, part);
         return cudaGetLastError();
     }
-    gn_stats_kernel<<<total_segs, 256, 0, st>>>(x, C, rm.start, rm.len, seg_cu, rm.n_utts, row_div, part, rev ? 1 : 0);
+    launch_k(gn_stats_kernel, dim3(total_segs), dim3(256), 0, st, x, C, rm.start, rm.len, seg_cu, rm.n_utts, row_div, part, rev ? 1 : 0);
     return cudaGetLastError();
 }
 
@@ -389,6 +401,7 @@ __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x));
 __global__ void gn_finalize_kernel(const double2 * __restrict__ part, const int32_t * __restrict__ seg_cu,
                                    const int32_t * __restrict__ len, int n_utts, int row_div,
                                    int cpg, float eps, float2 * __restrict__ mr) {
+    pdl_sync();
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= n_utts * 32) return;
     const int u = idx >> 5, g = idx & 31;
@@ -420,6 +433,7 @@ __global__ void __launch_bounds__(256) gn_apply_silu_kernel(
         const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt, int row_div,
         const float2 * __restrict__ mr, const float * __restrict__ w, const float * __restrict__ b, __half * __restrict__ out,
         int rows_per_block, int rev) {
+    pdl_sync();
     const int C8 = C >> 3;                       // threads per row: 64, 32 or 16
     const int rpp = 256 / C8;                    // rows per pass of the block
     const int c = (threadIdx.x % C8) * 8;
@@ -468,6 +482,7 @@ template <bool PRECISE>
 __global__ void __launch_bounds__(256) gn_apply_silu_generic_kernel(
         const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt, int row_div,
         const float2 * __restrict__ mr, const float * __restrict__ w, const float * __restrict__ b, __half * __restrict__ out) {
+    pdl_sync();
     const int C2 = C >> 1, cpg = C / 32;
     const size_t total = (size_t) rows * C2;
     for (size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t) gridDim.x * blockDim.x) {
@@ -489,7 +504,7 @@ cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map
                                  __half * out, cudaStream_t st, bool rev) {
     if (rows <= 0) return cudaSuccess;
     if (C <= 0 || C % 64 != 0) return cudaErrorInvalidValue;
-    gn_finalize_kernel<<<(rm.n_utts * 32 + 255) / 256, 256, 0, st>>>(part, seg_cu, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
+    launch_k(gn_finalize_kernel, dim3((rm.n_utts * 32 + 255) / 256), dim3(256), 0, st, part, seg_cu, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
     static int precise_set = -1;
     if (precise_set < 0) {
         const char * ev = getenv("MIO_GN_PRECISE");
@@ -497,19 +512,20 @@ cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map
     }
     if (C != 128 && C != 256 && C != 512 && C != 1024 && C != 2048) {     // the fast kernel needs C / 8 to divide 256
         const int grid = (int) min((size_t) 148 * 16, ((size_t) rows * (C / 2) + 255) / 256);
-        if (precise_set) gn_apply_silu_generic_kernel<true><<<grid, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out);
-        else gn_apply_silu_generic_kernel<false><<<grid, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out);
+        if (precise_set) launch_k(gn_apply_silu_generic_kernel<true>, dim3(grid), dim3(256), 0, st, x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out);
+        else launch_k(gn_apply_silu_generic_kernel<false>, dim3(grid), dim3(256), 0, st, x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out);
         return cudaGetLastError();
     }
     const int rpb = (rows >= GNA_ROWS * 148 * 2) ? GNA_ROWS : 16;      // few rows: more, shorter blocks (latency mode)
-    if (precise_set) gn_apply_silu_kernel<true><<<(rows + rpb - 1) / rpb, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb, rev ? 1 : 0);
-    else gn_apply_silu_kernel<false><<<(rows + rpb - 1) / rpb, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb, rev ? 1 : 0);
+    if (precise_set) launch_k(gn_apply_silu_kernel<true>, dim3((rows + rpb - 1) / rpb), dim3(256), 0, st, x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb, rev ? 1 : 0);
+    else launch_k(gn_apply_silu_kernel<false>, dim3((rows + rpb - 1) / rpb), dim3(256), 0, st, x, rows, C, rm.row_utt, row_div, mr_scratch, w, b, out, rpb, rev ? 1 : 0);
     return cudaGetLastError();
 }
 
 // fp32 -> (hi, lo) fp16 operand pair, zeros on pad rows (inputs of the ConvTranspose GEMMs, which read row+-1)
 __global__ void split_kernel(const float * __restrict__ x, int rows, int C, const int32_t * __restrict__ row_utt,
                              int row_div, __half * __restrict__ hi, __half * __restrict__ lo) {
+    pdl_sync();
     const int C4 = C / 4;
     const size_t total = (size_t) rows * C4;
     for (size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t) gridDim.x * blockDim.x) {
@@ -534,7 +550,7 @@ cudaError_t launch_split(const float * x, int rows, int C, const row_map & rm, i
     if (rows <= 0) return cudaSuccess;
     const size_t total = (size_t) rows * (C / 4);
     const int grid = (int) min((size_t) 148 * 16, (total + 255) / 256);
-    split_kernel<<<grid, 256, 0, st>>>(x, rows, C, rm.row_utt, row_div, hi, lo);
+    launch_k(split_kernel, dim3(grid), dim3(256), 0, st, x, rows, C, rm.row_utt, row_div, hi, lo);
     return cudaGetLastError();
 }
 
@@ -542,6 +558,7 @@ cudaError_t launch_split(const float * x, int rows, int C, const row_map & rm, i
 // and multiplies once.  The (hi, lo) operand pair becomes one BF16 operand IN PLACE (bit patterns in the hi buffer);
 // hi + lo carries 22 bits of the fp32 value, far beyond the 8 that survive.
 __global__ void pair_to_bf16_kernel(__half * __restrict__ hi, const __half * __restrict__ lo, size_t n2) {
+    pdl_sync();
     for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (size_t) gridDim.x * blockDim.x) {
         const float2 h = __half22float2(((const __half2 *) hi)[i]);
         float2 v = h;
@@ -555,7 +572,7 @@ cudaError_t launch_pair_to_bf16(__half * hi, const __half * lo, size_t n, cudaSt
     if (n == 0) return cudaSuccess;
     if (n % 2) return cudaErrorInvalidValue;
     const int grid = (int) min((size_t) 148 * 16, (n / 2 + 255) / 256);
-    pair_to_bf16_kernel<<<grid, 256, 0, st>>>(hi, lo, n / 2);
+    launch_k(pair_to_bf16_kernel, dim3(grid), dim3(256), 0, st, hi, lo, n / 2);
     return cudaGetLastError();
 }
 
@@ -569,6 +586,7 @@ __device__ __forceinline__ float round_act(float x, int store) {
 // AdaLN conditioning: mod[v][j] = b[j] + sum_k W[j][k] * silu(emb[v][k])
 // (compute_adaln3, src/miocodec.cpp:310-319 and :654-655). One warp per output row j, all voices.
 __global__ void cond_silu_kernel(const float * __restrict__ voice_table, int n, float * __restrict__ out) {
+    pdl_sync();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = silu_f(voice_table[i]);
 }
@@ -577,6 +595,7 @@ __global__ void cond_silu_kernel(const float * __restrict__ voice_table, int n, 
 __global__ void cond_kernel(const float * __restrict__ voice_silu, int n_voices, int adaln_dim,
                             const float * __restrict__ w, const float * __restrict__ b, int cond_rows,
                             const uint8_t * __restrict__ row_store, float * __restrict__ mod) {
+    pdl_sync();
     const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (j >= cond_rows) return;
@@ -607,9 +626,9 @@ cudaError_t launch_cond(const float * voice_table, int n_voices, int adaln_dim, 
                         int cond_rows, const uint8_t * row_store, float * silu_scratch, float * mod, cudaStream_t st) {
     if (n_voices <= 0) return cudaSuccess;
     const int n = n_voices * adaln_dim;
-    cond_silu_kernel<<<(n + 255) / 256, 256, 0, st>>>(voice_table, n, silu_scratch);
+    launch_k(cond_silu_kernel, dim3((n + 255) / 256), dim3(256), 0, st, voice_table, n, silu_scratch);
     dim3 grid((cond_rows + 7) / 8, min(n_voices, 8));
-    cond_kernel<<<grid, 256, 0, st>>>(silu_scratch, n_voices, adaln_dim, w, b, cond_rows, row_store, mod);
+    launch_k(cond_kernel, dim3(grid), dim3(256), 0, st, silu_scratch, n_voices, adaln_dim, w, b, cond_rows, row_store, mod);
     return cudaGetLastError();
 }
 
@@ -617,6 +636,7 @@ cudaError_t launch_cond(const float * voice_table, int n_voices, int adaln_dim, 
 // per-utterance peak normalisation: gain = 0.95/max|s| if peak > 1e-8 (src/test-to-speech.cpp:289-300)
 __global__ void peak_max_kernel(const float * __restrict__ wave, const int32_t * __restrict__ len,
                                 const int64_t * __restrict__ out_off, int spc, float * __restrict__ peak) {
+    pdl_sync();
     const int u = blockIdx.y;
     const int64_t n = (int64_t) len[u] * spc;
     const float * w = wave + out_off[u];
@@ -627,6 +647,7 @@ __global__ void peak_max_kernel(const float * __restrict__ wave, const int32_t *
 }
 __global__ void peak_scale_kernel(float * __restrict__ wave, const int32_t * __restrict__ len,
                                   const int64_t * __restrict__ out_off, int spc, const float * __restrict__ peak) {
+    pdl_sync();
     const int u = blockIdx.y;
     const float pk = peak[u];
     if (!(pk > 1e-8f)) return;
@@ -642,8 +663,8 @@ cudaError_t launch_peak_normalize(float * wave, const int32_t * len, const int64
     cudaError_t e = cudaMemsetAsync(peak_scratch, 0, sizeof(float) * n_utts, st);
     if (e != cudaSuccess) return e;
     dim3 grid(32, n_utts);
-    peak_max_kernel<<<grid, 256, 0, st>>>(wave, len, out_off, samples_per_code, peak_scratch);
-    peak_scale_kernel<<<grid, 256, 0, st>>>(wave, len, out_off, samples_per_code, peak_scratch);
+    launch_k(peak_max_kernel, dim3(grid), dim3(256), 0, st, wave, len, out_off, samples_per_code, peak_scratch);
+    launch_k(peak_scale_kernel, dim3(grid), dim3(256), 0, st, wave, len, out_off, samples_per_code, peak_scratch);
     return cudaGetLastError();
 }
 
@@ -654,6 +675,7 @@ __device__ __forceinline__ int pcm16_of(float s) { return __float2int_rz(fminf(f
 
 __global__ void __launch_bounds__(256) pcm16_kernel(const float * __restrict__ wave, int16_t * __restrict__ pcm,
                                                     int64_t begin, int64_t end) {
+    pdl_sync();
     // absolute sample indices: [va, vb) is the 8-sample-aligned body (bases are 256-byte aligned allocations)
     int64_t va = (begin + 7) & ~(int64_t) 7, vb = end & ~(int64_t) 7;
     if (va > vb) { va = end; vb = end; }
@@ -679,7 +701,7 @@ cudaError_t launch_pcm16(const float * wave, int16_t * pcm, int64_t begin, int64
     if (end <= begin) return cudaSuccess;
     const int64_t n8 = (end - begin) >> 3;
     const int grid = (int) std::min<int64_t>((int64_t) 148 * 8, std::max<int64_t>(1, (n8 + 255) / 256));
-    pcm16_kernel<<<grid, 256, 0, st>>>(wave, pcm, begin, end);
+    launch_k(pcm16_kernel, dim3(grid), dim3(256), 0, st, wave, pcm, begin, end);
     return cudaGetLastError();
 }
 

@@ -254,6 +254,8 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     cluster_sync_all();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
+    // everything above (barriers, TMEM allocation, descriptor prefetch, cluster rendezvous) ran under the predecessor's tail
+    pdl_sync();
 
     if (warp < EPI_WARP0) {
     // chunked variant: this warpgroup (producer, MMA issuer, two idle warps) hands its registers to the epilogue warpgroups
@@ -521,7 +523,7 @@ static cudaError_t launch_tc3_inst(const gemm_params & p, const CUtensorMap & a_
     const int tiles = ((p.N + BN - 1) / BN) * ((p.M + 255) / 256);
     int clusters = num_sms / 2;
     if (tiles < clusters) clusters = tiles;
-    gemm_tc3_kernel<BN, NPASS, EPI, CHUNK><<<2 * clusters, CHUNK > 0 ? G3_THREADS_CHUNKED : G3_THREADS, cfg::SMEM_BYTES, st>>>(
+    launch_k(gemm_tc3_kernel<BN, NPASS, EPI, CHUNK>, dim3(2 * clusters), dim3(CHUNK > 0 ? G3_THREADS_CHUNKED : G3_THREADS), cfg::SMEM_BYTES, st, 
         a_hi, a_lo, b_hi, b_lo, o0, o1, p);
     return cudaGetLastError();
 }

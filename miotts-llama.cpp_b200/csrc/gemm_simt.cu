@@ -156,6 +156,7 @@ __device__ __forceinline__ float bf16_bits_to_float(__half h) { return __uint_as
 
 template <int EPI>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(const gemm_params p) {
+    pdl_sync();
     __shared__ float As[16][64 + 1];
     __shared__ float Bs[16][64 + 1];
     const int tid = threadIdx.x;
@@ -212,13 +213,13 @@ cudaError_t launch_gemm_simt(const gemm_params & p, cudaStream_t st) {
     if (p.M <= 0) return cudaSuccess;
     dim3 grid((p.N + 63) / 64, (p.M + 63) / 64);
     switch (p.epi) {
-        case EPI_STORE: gemm_simt_kernel<EPI_STORE><<<grid, 256, 0, st>>>(p); break;
-        case EPI_RESID: gemm_simt_kernel<EPI_RESID><<<grid, 256, 0, st>>>(p); break;
-        case EPI_SWIGLU: gemm_simt_kernel<EPI_SWIGLU><<<grid, 256, 0, st>>>(p); break;
-        case EPI_SPLIT: gemm_simt_kernel<EPI_SPLIT><<<grid, 256, 0, st>>>(p); break;
-        case EPI_SNAKE: gemm_simt_kernel<EPI_SNAKE><<<grid, 256, 0, st>>>(p); break;
-        case EPI_HEAD: gemm_simt_kernel<EPI_HEAD><<<grid, 256, 0, st>>>(p); break;
-        case EPI_QKV: gemm_simt_kernel<EPI_QKV><<<grid, 256, 0, st>>>(p); break;
+        case EPI_STORE: launch_k(gemm_simt_kernel<EPI_STORE>, dim3(grid), dim3(256), 0, st, p); break;
+        case EPI_RESID: launch_k(gemm_simt_kernel<EPI_RESID>, dim3(grid), dim3(256), 0, st, p); break;
+        case EPI_SWIGLU: launch_k(gemm_simt_kernel<EPI_SWIGLU>, dim3(grid), dim3(256), 0, st, p); break;
+        case EPI_SPLIT: launch_k(gemm_simt_kernel<EPI_SPLIT>, dim3(grid), dim3(256), 0, st, p); break;
+        case EPI_SNAKE: launch_k(gemm_simt_kernel<EPI_SNAKE>, dim3(grid), dim3(256), 0, st, p); break;
+        case EPI_HEAD: launch_k(gemm_simt_kernel<EPI_HEAD>, dim3(grid), dim3(256), 0, st, p); break;
+        case EPI_QKV: launch_k(gemm_simt_kernel<EPI_QKV>, dim3(grid), dim3(256), 0, st, p); break;
         default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

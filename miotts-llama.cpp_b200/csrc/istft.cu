@@ -33,6 +33,7 @@ __device__ __forceinline__ void bulk_load_1d(void * dst, const void * src, uint3
 
 __global__ void __launch_bounds__(IST_THREADS, 2) istft_kernel(istft_params p, const float * __restrict__ tw392g,
                                                             const float * __restrict__ tw196g) {
+    pdl_sync();
     extern __shared__ __align__(16) float ist_smem[];
     float * slots = ist_smem;
     float * tw392 = slots + IST_SLOTS * IST_SLOT_FLOATS;
@@ -156,7 +157,7 @@ cudaError_t launch_istft(const istft_params & p, cudaStream_t st) {
     if (p.total_chunks <= 0) return cudaSuccess;
     if (p.spec_ld % 4 != 0 || p.spec_ld < 2 * IST_NFREQ) return cudaErrorInvalidValue;   // 16-byte rows for the bulk copies
     if (!p.tw) return cudaErrorInvalidValue;
-    istft_kernel<<<p.total_chunks, IST_THREADS, IST_SMEM, st>>>(p, p.tw, p.tw + 392);
+    launch_k(istft_kernel, dim3(p.total_chunks), dim3(IST_THREADS), IST_SMEM, st, p, p.tw, p.tw + 392);
     return cudaGetLastError();
 }
 

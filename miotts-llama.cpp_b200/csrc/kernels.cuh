@@ -9,6 +9,26 @@
 
 namespace mio {
 
+// ------------------------------------------------------------------------------------------ launches
+// Programmatic dependent launch (PDL): every kernel of the decode sequence is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization and executes `griddepcontrol.wait` (pdl_wait(), ptx.cuh) before it
+// touches anything its predecessor wrote, then `griddepcontrol.launch_dependents`.  The NEXT kernel's CTAs are therefore
+// scheduled while this kernel's last CTAs drain, and their launch latency and prologue (barrier init, TMEM allocation,
+// tensor-map prefetch) run under the predecessor's tail instead of after it: ~160 launches per decode, which is most of
+// what a single short utterance (BASELINE config C2) spends its time on.  MIO_PDL=0 launches plain (A/B switch).
+bool pdl_enabled();
+template <class... P, class... A>
+inline cudaError_t launch_k(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A &&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, P(args)...);
+}
+
 // ------------------------------------------------------------------------------------------ GEMM
 enum epi_kind : int {
     EPI_STORE = 0,   // out_f32[row][col] = acc*s + bias

@@ -8,6 +8,12 @@
 
 namespace mio {
 
+// programmatic dependent launch (kernels.cuh launch_k): wait = the predecessor grid has completed and its writes are visible;
+// launch_dependents = the successor grid may be scheduled once every CTA of this grid has said so (or exited)
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() { pdl_wait(); pdl_launch_dependents(); }
+
 __device__ __forceinline__ uint32_t smem_u32(const void * p) { return (uint32_t) __cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint64_t * bar, uint32_t count) {

@@ -5,6 +5,7 @@
 //   * the crossfade with the previously emitted tail, the tail update and the cut [begin, end) of the window
 //     (emit_range, :367-417) run in a device kernel, so only the newly committed samples cross PCIe
 #include "stream.h"
+#include "ptx.cuh"
 
 #include <chrono>
 
@@ -27,6 +28,7 @@ struct emit_job {                 // one firing stream in the current round
 //   a = (j+1)/(xf+1), out = (1-a)*tail[j] + a*x   (products and sum rounded separately like the reference's
 //   scalar loop, :388-395); new tail = last `xfade` samples of the last chunk, or the whole last chunk if shorter.
 __global__ void stream_emit_kernel(const float * __restrict__ wave, float * __restrict__ emit, const emit_job * __restrict__ jobs) {
+    pdl_sync();
     const emit_job J = jobs[blockIdx.x];
     const int64_t n = J.end - J.begin;
     if (n <= 0) return;
@@ -179,7 +181,7 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
         }
         if (cudaMemcpyAsync(E.d_emit_jobs, jobs.data(), jobs.size() * sizeof(emit_job), cudaMemcpyHostToDevice, E.stream) != cudaSuccess)
             return "cudaMemcpyAsync failed (emit jobs)";
-        stream_emit_kernel<<<(unsigned) jobs.size(), 256, 0, E.stream>>>(E.d_wave, (float *) E.d_emit, (const emit_job *) E.d_emit_jobs);
+        launch_k(stream_emit_kernel, dim3((unsigned) jobs.size()), dim3(256), 0, E.stream, E.d_wave, (float *) E.d_emit, (const emit_job *) E.d_emit_jobs);
         E.launches++;
         if (cudaGetLastError() != cudaSuccess) return "stream_emit_kernel launch failed";
         if (emit_total > 0 &&
