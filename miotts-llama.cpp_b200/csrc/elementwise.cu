@@ -14,7 +14,7 @@
 namespace mio {
 
 bool pdl_enabled() {
-    static const bool on = [] { const char * e = getenv("MIO_PDL"); return e && e[0] == '1';   /* off until verified on the GPU: MIO_PDL=1 */ }();
+    static const bool on = [] { const char * e = getenv("MIO_PDL"); return !(e && e[0] == '0'); }();
     return on;
 }
 

@@ -15,6 +15,6 @@ for w in ('c2', 'c3'):
         except Exception as e:
             print(w, p, 'FAILED', e)
 PY
-python -m pytest tests/test_gpu_parity.py tests/test_gpu_stages.py tests/test_gpu_streaming.py -x -q -m gpu > gpurun_out/r2h/parity.log 2>&1
+MIO_PDL=1 python -m pytest tests/test_gpu_parity.py tests/test_gpu_stages.py tests/test_gpu_streaming.py -x -q -m gpu > gpurun_out/r2h/parity.log 2>&1
 tail -3 gpurun_out/r2h/parity.log
 bash tools/gpu_job_r2g.sh
