@@ -61,6 +61,12 @@ def device_tensor(ptr: int, n: int, dtype: str = "float32", device: int = 0):
     return torch.as_tensor(_DevicePointer(ptr, n, typestr), device=torch.device("cuda", device))
 
 
+def _wire(t):
+    """Bytes on the wire: NCCL's torch binding has no int16, and a gather only moves bytes."""
+    import torch
+    return t.view(torch.uint8) if t.dtype == torch.int16 else t
+
+
 def gather_to_rank0(local, counts: list[int], host_out=None, group=None):
     """The one exchange step of the sharded path: the variable-length shards of the waveform go to rank 0,
     SIZE-EXACT (every rank knows every count, so nothing is padded to the largest shard and no size exchange is needed).
@@ -77,7 +83,7 @@ def gather_to_rank0(local, counts: list[int], host_out=None, group=None):
     assert local.numel() == counts[rank], (local.numel(), counts[rank])
     if rank != 0:
         if counts[rank] > 0:
-            dist.send(local, dst=0, group=group)
+            dist.send(_wire(local), dst=0, group=group)
         return None
     total = sum(counts)
     on_gpu = local.is_cuda
@@ -87,7 +93,7 @@ def gather_to_rank0(local, counts: list[int], host_out=None, group=None):
         out[: counts[0]].copy_(local)
         for r in range(1, world):
             if counts[r] > 0:
-                dist.recv(out[int(offs[r]): int(offs[r + 1])], src=r, group=group)
+                dist.recv(_wire(out[int(offs[r]): int(offs[r + 1])]), src=r, group=group)
         return out
     # device shards -> one host buffer: receive into per-rank staging, copy out on a side stream as each one lands
     assert host_out.numel() >= total
@@ -103,7 +109,7 @@ def gather_to_rank0(local, counts: list[int], host_out=None, group=None):
         if counts[r] == 0:
             continue
         stage[r] = torch.empty(counts[r], dtype=local.dtype, device=local.device)
-        dist.recv(stage[r], src=r, group=group)
+        dist.recv(_wire(stage[r]), src=r, group=group)
         ev = torch.cuda.Event()
         ev.record(main)
         with torch.cuda.stream(side):

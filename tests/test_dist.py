@@ -30,6 +30,16 @@ def _worker(rank, world, port, lens, q):
             ok = ok and np.array_equal(waves[i], _fake_wave(i, int(n)))
     else:
         ok = waves is None
+    # the PCM16 form bench.py's c5 block uses: size-exact shards of int16 into one preallocated host buffer on rank 0
+    counts = sharding.shard_counts(lens, world, SPC)
+    pcm = torch.from_numpy((local % 30000).astype(np.int16))
+    host = torch.empty(sum(counts), dtype=torch.int16) if rank == 0 else None
+    got = sharding.gather_to_rank0(pcm, counts, host)
+    if rank == 0:
+        for i, (o, n) in enumerate(sharding.utterance_slices(lens, world, SPC)):
+            ok = ok and np.array_equal(got[o: o + n].numpy(), (_fake_wave(i, int(lens[i])) % 30000).astype(np.int16))
+    else:
+        ok = ok and got is None
     # timing contract of bench.py: max over ranks
     t = torch.tensor([float(rank + 1)], dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
