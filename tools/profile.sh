@@ -7,7 +7,7 @@ TAG=${1:-rX}; shift || true
 WHAT=${*:-list attn istft gn ln gemm}
 OUT=gpurun_out/$TAG
 mkdir -p "$OUT"
-BENCH="python bench.py --steps 1 --warmup 1 --no-cpu-baseline"
+BENCH="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-extra"
 NCU="ncu --clock-control none"
 
 full() {   # name regex skip count [import-source]
@@ -22,7 +22,7 @@ full() {   # name regex skip count [import-source]
 
 for w in $WHAT; do
   case $w in
-    list)  $NCU --metrics gpu__time_duration.sum --csv --log-file "$OUT/launches.csv" python bench.py --steps 1 --warmup 3 --no-cpu-baseline > "$OUT/launches.log" 2>&1 ;;
+    list)  $NCU --metrics gpu__time_duration.sum --csv --log-file "$OUT/launches.csv" python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-extra > "$OUT/launches.log" 2>&1 ;;
     attn)  full attn "attention" 19 2 ;;        # one prenet-layer and one decoder-layer launch of the 2nd step
     istft) full istft "istft" 1 1 ;;
     gn)    full gn "gn_" 30 4 ;;
