@@ -587,6 +587,18 @@ def main():
     e2e_s = time.perf_counter() - t0
     h2d = codec.h2d_bytes()
     d2h = int(h_wave.nbytes)
+    # the same call delivering PCM16 (what wav_write stores; half the D2H bytes, converted on the device)
+    h_pcm = binding.pinned_empty(total_codes * codec.samples_per_token, np.int16)
+    for _ in range(2):
+        codec.decode_pcm16_batch(h_codes, wl["cu"], wl["voice_table"], wl["voice_ids"], out=h_pcm)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        codec.decode_pcm16_batch(h_codes, wl["cu"], wl["voice_table"], wl["voice_ids"], out=h_pcm)
+    torch.cuda.synchronize()
+    e2e_pcm_s = time.perf_counter() - t0
+    d2h_pcm = int(h_pcm.nbytes)
+    del h_pcm
     # C2 is the latency configuration: p50 / p99 of 100 synchronous single-utterance calls, host to host
     latency = None
     if args.workload == "c2" and not args.no_latency:
@@ -612,7 +624,7 @@ def main():
             extra["c4"] = c4_block(codec, cpu=not args.no_cpu_baseline)
 
     # ---- max over ranks / whole-job aggregation
-    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    t = torch.tensor([dev_ms, e2e_s * 1e3, e2e_pcm_s * 1e3], dtype=torch.float64, device="cuda")
     a = torch.tensor([audio_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -621,6 +633,7 @@ def main():
     audio_all = float(a[0])
     value = audio_all * args.steps / (dev_ms_max / 1e3)
     e2e_value = audio_all * args.steps / (e2e_ms_max / 1e3)
+    e2e_pcm_ms_max = float(t[2])
 
     if rank == 0:
         peaks = measured_peaks()
@@ -653,6 +666,9 @@ def main():
             "config": bench_config(wl, world), "cpus_bound_per_rank": numa,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms_max / args.steps},
+            "e2e_pcm16": {"value": audio_all * args.steps / (e2e_pcm_ms_max / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                          "d2h_bytes_per_step": d2h_pcm, "ms_per_step": e2e_pcm_ms_max / args.steps,
+                          "call": "mio_decode_pcm16_batch (SURVEY 8f F1: PCM16 made on the device)"},
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"kernel": "gemm_tc3_kernel<BN, 3, epilogue> (tcgen05 split-precision tap-GEMM, all linear/ConvT layers)",

@@ -126,12 +126,34 @@ engine::~engine() {
     F(d_codes); F(d_row_utt); F(d_start); F(d_len); F(d_voice); F(d_chunk_cu); F(d_seg_cu); F(d_out_off); F(d_voice_table); F(d_wave);
     for (void * p : w_allocs) F(p);
     F(d_emit); F(d_emit_jobs); F(d_pcm); F(w.rope_pre); F(w.rope_t); F(istft_spec);
-    if (h_emit) cudaFreeHost(h_emit);
+    for (emit_block * b : emit_pool) { if (b->host) cudaFreeHost(b->host); delete b; }
     if (h_stage) cudaFreeHost(h_stage);
     if (stream && own_stream) cudaStreamDestroy(stream);
     if (chunk_done) cudaEventDestroy(chunk_done);
     for (cudaEvent_t ev : tune_ev) if (ev) cudaEventDestroy(ev);
     if (copy_stream) cudaStreamDestroy(copy_stream);
+}
+
+// A free pinned block of at least `samples` floats.  *pooled = false: the pool is exhausted (every block still has unread
+// slices); the caller gets the scratch block (last entry, never referenced) and must copy the samples out of it.
+engine::emit_block * engine::acquire_emit_block(int64_t samples, bool * pooled) {
+    emit_block * best = nullptr;
+    int in_use = 0;
+    for (emit_block * b : emit_pool) {
+        if (b->refs > 0) { in_use++; continue; }
+        if (b->cap >= samples && (!best || b->cap < best->cap)) best = b;
+    }
+    *pooled = in_use < EMIT_POOL_MAX;
+    if (best) return best;
+    // grow: reuse (reallocate) a free block that is too small before adding a new one
+    emit_block * blk = nullptr;
+    for (emit_block * b : emit_pool) if (b->refs == 0) { blk = b; break; }
+    if (!blk) { blk = new emit_block(); emit_pool.push_back(blk); }
+    if (blk->host) { cudaFreeHost(blk->host); blk->host = nullptr; blk->cap = 0; }
+    const int64_t want = samples + samples / 4 + 4096;
+    if (cudaMallocHost((void **) &blk->host, (size_t) want * sizeof(float)) != cudaSuccess) { blk->host = nullptr; return nullptr; }
+    blk->cap = want;
+    return blk;
 }
 
 // ---------------------------------------------------------------------------------------------

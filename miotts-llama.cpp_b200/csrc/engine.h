@@ -102,8 +102,16 @@ struct engine {
     int istft_chunks = 0;
     double stream_seconds = 0.0; int64_t stream_passes = 0;   // wall time / device passes inside streams_step
     // streaming emit buffers (stream.cu)
-    void * d_emit = nullptr; void * d_emit_jobs = nullptr; void * h_emit = nullptr;
+    void * d_emit = nullptr; void * d_emit_jobs = nullptr;
     int64_t emit_cap = 0, emit_jobs_cap = 0;
+    // Pinned host blocks the emitted samples of a streaming round land in (one D2H copy per round).  The streams' queues
+    // REFERENCE slices of the block (refs counts unread slices) instead of copying them again; a block returns to the pool
+    // when its last slice has been read.  At most EMIT_POOL_MAX blocks are kept referenced: beyond that a round's samples
+    // are copied into the streams (a consumer that never reads must not pin host memory without bound).
+    struct emit_block { float * host = nullptr; int64_t cap = 0; int64_t refs = 0; };
+    static constexpr int EMIT_POOL_MAX = 8;
+    std::vector<emit_block *> emit_pool;
+    emit_block * acquire_emit_block(int64_t samples, bool * pooled);
     // pinned staging
     void * h_stage = nullptr; size_t h_stage_bytes = 0;
     bool batch_uploaded = false, batch_ran = false;

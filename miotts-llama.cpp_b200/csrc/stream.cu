@@ -65,6 +65,7 @@ void stream_default_config(const engine & E, mio_stream_config * cfg) {
 }
 
 stream_state::~stream_state() {
+    for (emit_seg & g : segs) if (g.blk) g.blk->refs--;
     if (d_tail) cudaFree(d_tail);
     if (d_tail_len) cudaFree(d_tail_len);
 }
@@ -164,37 +165,44 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
         if (E.emit_cap < emit_total || E.emit_jobs_cap < (int64_t) jobs.size()) {
             if (E.d_emit) cudaFree(E.d_emit);
             if (E.d_emit_jobs) cudaFree(E.d_emit_jobs);
-            if (E.h_emit) cudaFreeHost(E.h_emit);
-            E.d_emit = E.d_emit_jobs = E.h_emit = nullptr;          // a failed allocation below must not leave freed pointers behind
+            E.d_emit = E.d_emit_jobs = nullptr;          // a failed allocation below must not leave freed pointers behind
             const int64_t want_emit = emit_total + emit_total / 4 + 4096, want_jobs = (int64_t) jobs.size() + 64;
             E.emit_cap = E.emit_jobs_cap = 0;
             if (cudaMalloc(&E.d_emit, (size_t) want_emit * sizeof(float)) != cudaSuccess ||
-                cudaMalloc(&E.d_emit_jobs, (size_t) want_jobs * sizeof(emit_job)) != cudaSuccess ||
-                cudaMallocHost(&E.h_emit, (size_t) want_emit * sizeof(float)) != cudaSuccess) {
+                cudaMalloc(&E.d_emit_jobs, (size_t) want_jobs * sizeof(emit_job)) != cudaSuccess) {
                 if (E.d_emit) cudaFree(E.d_emit);
                 if (E.d_emit_jobs) cudaFree(E.d_emit_jobs);
-                if (E.h_emit) cudaFreeHost(E.h_emit);
-                E.d_emit = E.d_emit_jobs = E.h_emit = nullptr;
+                E.d_emit = E.d_emit_jobs = nullptr;
                 return "cudaMalloc failed (emit buffers)";
             }
             E.emit_cap = want_emit; E.emit_jobs_cap = want_jobs;
         }
+        bool pooled = true;
+        engine::emit_block * blk = emit_total > 0 ? E.acquire_emit_block(emit_total, &pooled) : nullptr;
+        if (emit_total > 0 && !blk) return "cudaMallocHost failed (emit block)";
         if (cudaMemcpyAsync(E.d_emit_jobs, jobs.data(), jobs.size() * sizeof(emit_job), cudaMemcpyHostToDevice, E.stream) != cudaSuccess)
             return "cudaMemcpyAsync failed (emit jobs)";
         launch_k(stream_emit_kernel, dim3((unsigned) jobs.size()), dim3(256), 0, E.stream, E.d_wave, (float *) E.d_emit, (const emit_job *) E.d_emit_jobs);
         E.launches++;
         if (cudaGetLastError() != cudaSuccess) return "stream_emit_kernel launch failed";
         if (emit_total > 0 &&
-            cudaMemcpyAsync(E.h_emit, E.d_emit, (size_t) emit_total * sizeof(float), cudaMemcpyDeviceToHost, E.stream) != cudaSuccess)
+            cudaMemcpyAsync(blk->host, E.d_emit, (size_t) emit_total * sizeof(float), cudaMemcpyDeviceToHost, E.stream) != cudaSuccess)
             return "cudaMemcpyAsync failed (emit D2H)";
         e = E.sync();
         if (!e.empty()) return e;
         for (size_t k = 0; k < act.size(); k++) {
             stream_state & s = *act[k];
             const emit_job & J = jobs[k];
-            const float * src = (const float *) E.h_emit + J.emit_off;
-            s.queue.insert(s.queue.end(), src, src + (J.end - J.begin));
-            s.emitted_samples += J.end - J.begin;
+            const int64_t n = J.end - J.begin;
+            if (n > 0) {
+                const float * src = blk->host + J.emit_off;
+                s.segs.emplace_back();
+                stream_state::emit_seg & g = s.segs.back();
+                g.n = n;
+                if (pooled) { g.blk = blk; g.p = src; blk->refs++; }       // no second host copy: read straight from the pinned block
+                else { g.own.assign(src, src + n); g.p = g.own.data(); }
+            }
+            s.emitted_samples += n;
             s.job_head++;
         }
         E.stream_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - t_pass0).count();
@@ -208,13 +216,19 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
 }
 
 int64_t stream_read(stream_state & s, float * out, int64_t cap, int * is_last) {
-    const int64_t avail = (int64_t) s.queue.size() - s.queue_head;
-    const int64_t n = std::max<int64_t>(0, std::min(avail, cap));
-    if (n > 0) memcpy(out, s.queue.data() + s.queue_head, (size_t) n * sizeof(float));
-    s.queue_head += n;
-    if (s.queue_head == (int64_t) s.queue.size()) { s.queue.clear(); s.queue_head = 0; }
-    if (is_last) *is_last = (s.done && s.queue.empty()) ? 1 : 0;
-    return n;
+    int64_t done = 0;
+    while (done < cap && !s.segs.empty()) {
+        stream_state::emit_seg & g = s.segs.front();
+        const int64_t n = std::min(cap - done, g.n - g.used);
+        if (n > 0) memcpy(out + done, g.p + g.used, (size_t) n * sizeof(float));
+        g.used += n; done += n;
+        if (g.used == g.n) {
+            if (g.blk) g.blk->refs--;
+            s.segs.pop_front();
+        }
+    }
+    if (is_last) *is_last = (s.done && s.segs.empty()) ? 1 : 0;
+    return done;
 }
 
 }  // namespace mio

@@ -1,5 +1,6 @@
 // Host state of one audio stream (see stream.cu).
 #pragma once
+#include <deque>
 #include <string>
 #include <vector>
 
@@ -27,8 +28,15 @@ struct stream_state {
     bool finished = false, final_queued = false, done = false;
     float * d_tail = nullptr;
     int * d_tail_len = nullptr;
-    std::vector<float> queue;     // emitted samples not yet read
-    int64_t queue_head = 0;
+    // emitted samples not yet read: slices of the engine's pinned round blocks (blk != nullptr, p points into it) or, when
+    // the pool is exhausted, an own copy
+    struct emit_seg {
+        engine::emit_block * blk = nullptr;
+        std::vector<float> own;
+        const float * p = nullptr;
+        int64_t n = 0, used = 0;
+    };
+    std::deque<emit_seg> segs;
     int64_t decode_calls = 0, decoded_codes = 0, emitted_samples = 0;
     ~stream_state();
 };
