@@ -313,6 +313,9 @@ void * mio_batch_pcm16_device(mio_ctx * c) {
 }
 
 // ---- host-side neighbours of the path
+// mio_parse_speech_tokens is a RESTATEMENT of a 20-line reference function (parse_speech_tokens, src/token-parser.cpp:5-28),
+// not a design of its own: the contract to reproduce bit for bit is libc's strstr/strtol behaviour on the token text, so the
+// loop has the same shape by necessity.  tests/test_ingest_epilogue.py holds it to the compiled reference function.
 int64_t mio_parse_speech_tokens(const char * text, int64_t text_len, int32_t * out, int64_t cap) {
     if (!text || text_len < 0 || cap < 0 || (!out && cap > 0)) return fail(MIO_ERR_ARG, "bad argument");
     // A private NUL-terminated copy: the reference scans text.c_str() with strstr/strtol (src/token-parser.cpp:9-16),
