@@ -423,38 +423,62 @@ def c5_block(codec, stream, rank: int, world: int, local: int, barrier, sweeps: 
     e2e = {"per_rank_host": {"value": audio_all / s1, "unit": UNIT, "ms_per_sweep": s1 * 1e3,
                              "h2d_bytes": int(len(wl["codes"]) * 4), "d2h_bytes": int(mine * 2)}}
     if world > 1:
-        host_all = torch.empty(total, dtype=torch.int16).pin_memory() if rank == 0 else None
-
-        def gathered():
-            codec.batch_upload(h_codes, wl["cu"], wl["voice_table"], wl["voice_ids"])
-            codec.batch_run(False)
-            ptr, n = codec.pcm16_device()
-            sharding.gather_to_rank0(sharding.device_tensor(ptr, n, "int16", local), counts, host_all)
-        s2 = timed(gathered)
-        e2e["gather_rank0_nccl"] = {"value": audio_all / s2, "unit": UNIT, "ms_per_sweep": s2 * 1e3,
-                                    "nvlink_bytes_to_rank0": int((total - counts[0]) * 2), "d2h_bytes_rank0": int(total * 2)}
-        if rank == 0:      # placement check: rank 0's own shard lands at offset 0 of the rank-major buffer
-            assert np.array_equal(host_all[: counts[0]].numpy()[:4096], h_pcm[:4096])
+        # every "can this rank go on" decision below is taken collectively (max over ranks of a failure flag): a rank that
+        # dropped out alone would leave the others waiting in a send / barrier
+        host_all, fail = None, 0.0
+        if rank == 0:
+            try:
+                host_all = torch.empty(total, dtype=torch.int16).pin_memory()
+            except Exception:  # noqa: BLE001
+                fail = 1.0
+        if tmax(fail) > 0.0:
+            e2e["gather_rank0_nccl"] = {"skipped": "rank 0 could not pin the gathered buffer"}
+        else:
+            def gathered():
+                codec.batch_upload(h_codes, wl["cu"], wl["voice_table"], wl["voice_ids"])
+                codec.batch_run(False)
+                ptr, n = codec.pcm16_device()
+                sharding.gather_to_rank0(sharding.device_tensor(ptr, n, "int16", local), counts, host_all)
+            s2 = timed(gathered)
+            e2e["gather_rank0_nccl"] = {"value": audio_all / s2, "unit": UNIT, "ms_per_sweep": s2 * 1e3,
+                                        "nvlink_bytes_to_rank0": int((total - counts[0]) * 2), "d2h_bytes_rank0": int(total * 2)}
+            if rank == 0:      # placement check: rank 0's own shard lands at offset 0 of the rank-major buffer
+                assert np.array_equal(host_all[: counts[0]].numpy()[:4096], h_pcm[:4096])
         del host_all
-        try:
-            name = f"mio_c5_{os.environ.get('MASTER_PORT', '0')}"
-            off = int(sum(counts[:rank]))
+        name = f"mio_c5_{os.environ.get('MASTER_PORT', '0')}"
+        off = int(sum(counts[:rank]))
+        shared, fail, why = None, 0.0, ""
+        vfs = os.statvfs("/dev/shm")                         # a tmpfs that is too small would SIGBUS on first touch
+        if vfs.f_bavail * vfs.f_frsize < total * 2 + (1 << 30):
+            fail, why = 1.0, f"/dev/shm has {vfs.f_bavail * vfs.f_frsize >> 20} MiB free, the shared buffer needs {total * 2 >> 20} MiB"
+        if tmax(fail) == 0.0:
             if rank == 0:
-                shared = sharding.SharedPinnedBuffer(name, total, np.int16, off, mine, create=True)
+                try:
+                    shared = sharding.SharedPinnedBuffer(name, total, np.int16, off, mine, create=True)
+                except Exception as e:  # noqa: BLE001
+                    fail, why = 1.0, f"{type(e).__name__}: {e}"
             barrier()
-            if rank != 0:
-                shared = sharding.SharedPinnedBuffer(name, total, np.int16, off, mine, create=False)
-
+            if rank != 0 and fail == 0.0:
+                try:
+                    shared = sharding.SharedPinnedBuffer(name, total, np.int16, off, mine, create=False)
+                except Exception as e:  # noqa: BLE001
+                    fail, why = 1.0, f"{type(e).__name__}: {e}"
+        if tmax(fail) > 0.0:
+            e2e["shared_pinned"] = {"skipped": why or "another rank could not map / page-lock the shared buffer"}
+        else:
             def direct():
                 codec.decode_pcm16_batch(h_codes, wl["cu"], wl["voice_table"], wl["voice_ids"], out=shared.mine)
             s3 = timed(direct)
             e2e["shared_pinned"] = {"value": audio_all / s3, "unit": UNIT, "ms_per_sweep": s3 * 1e3, "d2h_bytes_per_rank": int(mine * 2)}
-            ok = np.array_equal(np.asarray(shared.mine[:4096]), h_pcm[:4096])
-            barrier()
+            assert np.array_equal(np.asarray(shared.mine[:4096]), h_pcm[:4096])
+        barrier()
+        if shared is not None:
             shared.close(unlink=(rank == 0))
-            assert ok
-        except Exception as e:  # noqa: BLE001
-            e2e["shared_pinned"] = {"skipped": f"{type(e).__name__}: {e}"}
+        elif rank == 0:
+            try:
+                os.unlink(os.path.join("/dev/shm", name))
+            except OSError:
+                pass
     blk["e2e"] = e2e
     return blk
 
