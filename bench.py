@@ -445,6 +445,52 @@ def c5_block(codec, stream, rank: int, world: int, local: int, barrier, sweeps: 
             if rank == 0:      # placement check: rank 0's own shard lands at offset 0 of the rank-major buffer
                 assert np.array_equal(host_all[: counts[0]].numpy()[:4096], h_pcm[:4096])
         del host_all
+        # the same gather with no transfer step: conversion kernels store straight into rank 0's buffer over NVLink, the
+        # shard is decoded in groups and rank 0's host copy of group g runs under everybody's decode of group g+1
+        G = 8
+        pg, fail = None, 0.0
+        try:
+            pg = sharding.P2PGather(all_lens, spc, G, local)
+        except Exception as e:  # noqa: BLE001
+            fail, why_p2p = 1.0, f"{type(e).__name__}: {e}"
+        if tmax(fail) > 0.0:
+            e2e["gather_rank0_p2p"] = {"skipped": why_p2p if fail else "another rank could not map the job buffer"}
+            if pg is not None:
+                pg.close()
+        else:
+            local_groups = sharding.split_groups(wl["lens"], G)
+            cu = wl["cu"]
+
+            def p2p():
+                for g, ids in enumerate(local_groups):
+                    if len(ids):
+                        a, b = int(ids[0]), int(ids[-1]) + 1
+                        codec.batch_upload(h_codes[cu[a]: cu[b]], (cu[a: b + 1] - cu[a]).astype(np.int32), wl["voice_table"], wl["voice_ids"][a:b])
+                        codec.batch_run(False)
+                    pg.put(codec, g)
+                pg.finish()
+            s4 = timed(p2p)
+            e2e["gather_rank0_p2p"] = {"value": audio_all / s4, "unit": UNIT, "ms_per_sweep": s4 * 1e3, "groups": G,
+                                       "nvlink_bytes_to_rank0": int((total - counts[0]) * 2), "d2h_bytes_rank0": int(total * 2),
+                                       "how": "pcm16 kernels store into rank 0's IPC-mapped buffer; D2H of group g under the decode of group g+1"}
+            # every rank checks its own slices in the job buffer; rank 0 checks everybody's bytes on the host by checksum
+            goff, ok = 0, True
+            for g, ids in enumerate(local_groups):
+                n = pg.count[rank][g]
+                if n:
+                    got = sharding.device_tensor(pg.ptr + 2 * pg.off[rank][g], n, "int16", local).cpu().numpy()
+                    ok = ok and np.array_equal(got, h_pcm[goff: goff + n])
+                goff += n
+            sums = torch.zeros(world, dtype=torch.float64, device="cuda")
+            sums[rank] = float(np.asarray(h_pcm, dtype=np.int64).sum())
+            dist.all_reduce(sums)
+            if rank == 0:
+                host = pg.host.numpy()
+                for r in range(world):
+                    tot = sum(int(host[pg.off[r][g]: pg.off[r][g] + pg.count[r][g]].astype(np.int64).sum()) for g in range(G))
+                    ok = ok and float(tot) == float(sums[r])
+            pg.close()
+            assert ok, "P2P gather placed bytes wrongly"
         name = f"mio_c5_{os.environ.get('MASTER_PORT', '0')}"
         off = int(sum(counts[:rank]))
         shared, fail, why = None, 0.0, ""

@@ -132,6 +132,18 @@ int  mio_batch_fetch_pcm16(mio_ctx * ctx, int16_t * pcm_out, int64_t pcm_cap);
  * samples_per_token*sum(T); valid until the next upload).  The sharded sweep's one exchange step (the final
  * gather of variable-length waveforms to the collecting rank) sends this buffer peer to peer.  NULL on error. */
 void * mio_batch_pcm16_device(mio_ctx * ctx);
+/* The same conversion stored straight into a caller-supplied DEVICE buffer of at least samples_per_token*sum(T) int16
+ * (asynchronous on the context's stream).  The buffer may be ANOTHER GPU's memory mapped into this process (CUDA IPC /
+ * peer access): the stores then cross NVLink inside the kernel and the gather needs no separate transfer step. */
+int  mio_batch_pcm16_to_device(mio_ctx * ctx, void * dst_device, int64_t cap);
+/* Device buffers shared between the processes of one box (one process per GPU): the collecting rank allocates, exports a
+ * 64-byte handle (cudaIpcGetMemHandle), every other rank opens it on ITS device (cudaIpcOpenMemHandle with lazy peer access)
+ * and passes the mapped pointer (+ its slice offset) to mio_batch_pcm16_to_device. */
+void * mio_device_alloc(int device, size_t bytes);
+void   mio_device_free(void * p);
+int    mio_ipc_export(const void * device_ptr, uint8_t out_handle[64]);
+void * mio_ipc_open(const uint8_t handle[64], int device);
+int    mio_ipc_close(void * p);
 /* The 44-byte RIFF/WAVE header wav_write emits (src/wav-writer.cpp:7-37): PCM, mono, 16 bit. */
 int  mio_wav_header(int sample_rate, int64_t n_samples, uint8_t out44[44]);
 /* header + samples to a file: byte-identical to wav_write(path, samples, sample_rate) when pcm came from the

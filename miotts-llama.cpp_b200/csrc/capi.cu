@@ -312,6 +312,48 @@ void * mio_batch_pcm16_device(mio_ctx * c) {
     return p;
 }
 
+int mio_batch_pcm16_to_device(mio_ctx * c, void * dst_device, int64_t cap) {
+    return guarded([&]() -> int {
+        if (!c) return fail(MIO_ERR_ARG, "bad argument");
+        TRY(c->E.pcm16_to_device((int16_t *) dst_device, cap));
+        return MIO_OK;
+    });
+}
+
+// ---- device buffers shared between the processes of one box (the P2P form of the gather, sharding.P2PGather)
+void * mio_device_alloc(int device, size_t bytes) {
+    void * p = nullptr;
+    if (cudaSetDevice(device) != cudaSuccess || cudaMalloc(&p, bytes ? bytes : 1) != cudaSuccess) {
+        fail(MIO_ERR_CUDA, "cudaMalloc failed");
+        return nullptr;
+    }
+    return p;
+}
+void mio_device_free(void * p) { if (p) cudaFree(p); }
+int mio_ipc_export(const void * device_ptr, uint8_t out_handle[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    if (!device_ptr || !out_handle) return fail(MIO_ERR_ARG, "bad argument");
+    cudaIpcMemHandle_t h;
+    const cudaError_t e = cudaIpcGetMemHandle(&h, const_cast<void *>(device_ptr));
+    if (e != cudaSuccess) return fail(MIO_ERR_CUDA, std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e));
+    memcpy(out_handle, &h, 64);
+    return MIO_OK;
+}
+void * mio_ipc_open(const uint8_t handle[64], int device) {
+    if (!handle) { fail(MIO_ERR_ARG, "bad argument"); return nullptr; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    void * p = nullptr;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);   // peer access device -> owner comes with it
+    if (e != cudaSuccess) { fail(MIO_ERR_CUDA, std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e)); return nullptr; }
+    return p;
+}
+int mio_ipc_close(void * p) {
+    if (!p) return MIO_OK;
+    return cudaIpcCloseMemHandle(p) == cudaSuccess ? MIO_OK : fail(MIO_ERR_CUDA, "cudaIpcCloseMemHandle failed");
+}
+
 // ---- host-side neighbours of the path
 // mio_parse_speech_tokens is a RESTATEMENT of a 20-line reference function (parse_speech_tokens, src/token-parser.cpp:5-28),
 // not a design of its own: the contract to reproduce bit for bit is libc's strstr/strtol behaviour on the token text, so the

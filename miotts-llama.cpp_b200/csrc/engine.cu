@@ -1333,6 +1333,17 @@ std::string engine::pcm16_device(int16_t ** out) {
     return {};
 }
 
+// The same conversion with the result stored straight into a caller-supplied DEVICE buffer -- which may be another GPU's
+// memory mapped into this process (CUDA IPC / peer access): the stores then travel over NVLink and the sharded sweep's
+// gather needs no separate transfer step (mio_batch_pcm16_to_device; sharding.P2PGather).
+std::string engine::pcm16_to_device(int16_t * dst, int64_t cap) {
+    if (!batch_ran) return "mio_batch_pcm16_to_device before mio_batch_run";
+    if (!dst || cap < wave_samples) return "bad argument: destination too small";
+    CK(cudaSetDevice(device));
+    CKR(CAT_PEAK, (double) wave_samples * 6.0, launch_pcm16(d_wave, dst, 0, wave_samples, stream));
+    return {};
+}
+
 // spectrogram of utterance `utt` of a single-chunk batch (mio_decode_spec)
 std::string engine::fetch_spec(int utt, float * out, int64_t cap) {
     if (!batch_ran) return "fetch before run";

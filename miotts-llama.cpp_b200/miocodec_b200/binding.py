@@ -20,7 +20,8 @@ MIO_OK, MIO_ERR_ARG, MIO_ERR_IO, MIO_ERR_FORMAT, MIO_ERR_CUDA, MIO_ERR_RANGE, MI
 # every symbol include/miocodec_b200.h declares (tests check the library exports exactly these)
 EXPORTS = [
     "mio_ctx_create", "mio_istft_ctx_create", "mio_ctx_destroy", "mio_ctx_sample_rate", "mio_ctx_n_fft", "mio_ctx_hop_length",
-    "mio_batch_pcm16_device", "mio_ctx_samples_per_token", "mio_ctx_frames_per_code", "mio_ctx_vocab", "mio_ctx_device", "mio_ctx_set_option",
+    "mio_batch_pcm16_device", "mio_batch_pcm16_to_device", "mio_device_alloc", "mio_device_free",
+    "mio_ipc_export", "mio_ipc_open", "mio_ipc_close", "mio_ctx_samples_per_token", "mio_ctx_frames_per_code", "mio_ctx_vocab", "mio_ctx_device", "mio_ctx_set_option",
     "mio_ctx_set_stream", "mio_voice_load", "mio_print_tensors", "mio_decode_spec", "mio_istft", "mio_decode_wave",
     "mio_decode_wave_batch", "mio_batch_upload", "mio_batch_run", "mio_batch_fetch", "mio_batch_sync",
     "mio_batch_kernel_launches", "mio_batch_wave_device", "mio_stream_default_config", "mio_stream_open",
@@ -81,6 +82,15 @@ def lib() -> C.CDLL:
     L.mio_batch_wave_device.restype = vp
     L.mio_batch_pcm16_device.argtypes = [vp]
     L.mio_batch_pcm16_device.restype = vp
+    L.mio_batch_pcm16_to_device.argtypes = [vp, vp, C.c_int64]
+    L.mio_device_alloc.argtypes = [C.c_int, C.c_size_t]
+    L.mio_device_alloc.restype = vp
+    L.mio_device_free.argtypes = [vp]
+    L.mio_device_free.restype = None
+    L.mio_ipc_export.argtypes = [vp, C.c_char_p]
+    L.mio_ipc_open.argtypes = [C.c_char_p, C.c_int]
+    L.mio_ipc_open.restype = vp
+    L.mio_ipc_close.argtypes = [vp]
     L.mio_stream_default_config.argtypes = [vp, C.POINTER(StreamConfig)]
     L.mio_stream_default_config.restype = None
     L.mio_stream_open.argtypes = [vp, f32p, C.POINTER(StreamConfig), C.POINTER(vp)]
@@ -117,6 +127,34 @@ def lib() -> C.CDLL:
     L.mio_debug_gemm.argtypes = [vp, C.c_int, C.c_int, C.c_int, f32p, f32p, C.c_int, f32p]
     _lib = L
     return L
+
+
+def device_alloc(device: int, nbytes: int) -> int:
+    p = lib().mio_device_alloc(device, nbytes)
+    if not p:
+        raise MioError(MIO_ERR_CUDA, lib().mio_last_error().decode("utf-8", "replace"))
+    return int(p)
+
+
+def device_free(ptr: int):
+    lib().mio_device_free(C.c_void_p(ptr))
+
+
+def ipc_export(ptr: int) -> bytes:
+    buf = C.create_string_buffer(64)
+    _check(lib().mio_ipc_export(C.c_void_p(ptr), buf))
+    return buf.raw
+
+
+def ipc_open(handle: bytes, device: int) -> int:
+    p = lib().mio_ipc_open(handle, device)
+    if not p:
+        raise MioError(MIO_ERR_CUDA, lib().mio_last_error().decode("utf-8", "replace"))
+    return int(p)
+
+
+def ipc_close(ptr: int):
+    _check(lib().mio_ipc_close(C.c_void_p(ptr)))
 
 
 def pinned_empty(n: int, dtype) -> np.ndarray:
@@ -265,6 +303,11 @@ class MioCodec:
         if not p:
             raise MioError(-3, lib().mio_last_error().decode("utf-8", "replace"))
         return int(p), self._total
+
+    def pcm16_to_device(self, dst_ptr: int, cap: int) -> int:
+        """PCM16 of the resident waveform stored into device memory at dst_ptr (may be a peer GPU's); returns the samples."""
+        _check(lib().mio_batch_pcm16_to_device(self._h, C.c_void_p(dst_ptr), cap))
+        return self._total
 
     def kernel_launches(self) -> int:
         return int(lib().mio_batch_kernel_launches(self._h))

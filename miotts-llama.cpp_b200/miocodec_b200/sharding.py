@@ -137,6 +137,116 @@ def gather_waves(local_wave: np.ndarray, local_idx: np.ndarray, lengths, samples
     return [flat[o: o + n] for o, n in utterance_slices(lengths, world, samples_per_code)]
 
 
+def split_groups(lengths, n_groups: int) -> list[np.ndarray]:
+    """Cut a shard (utterance lengths in shard order) into n_groups CONTIGUOUS runs of about equal code count; returns the
+    index arrays (possibly empty).  Deterministic: every rank can compute every rank's groups."""
+    lengths = np.asarray(lengths, dtype=np.int64)
+    n = len(lengths)
+    if n == 0:
+        return [np.arange(0)] * n_groups
+    cum = np.cumsum(lengths)
+    cuts = [0]
+    for g in range(1, n_groups):
+        cuts.append(max(cuts[-1], int(np.searchsorted(cum, cum[-1] * g / n_groups, side="left")) + 0))
+    cuts.append(n)
+    return [np.arange(cuts[g], max(cuts[g], cuts[g + 1])) for g in range(n_groups)]
+
+
+class P2PGather:
+    """The gather of the sharded sweep WITHOUT a transfer step: rank 0 owns one device buffer for the whole job and maps it
+    into every rank (CUDA IPC over the NVLink / NVSwitch fabric); each rank's PCM16 conversion kernel stores its result
+    straight into its slice of that buffer (mio_batch_pcm16_to_device), so the audio crosses NVLink inside the kernel that
+    produces it.  The shard is decoded in `n_groups` groups; after group g every rank passes a tiny stream-ordered
+    all-reduce (no host synchronisation), then rank 0 copies group g's region -- laid out group-major, so it is one
+    contiguous range -- to the pinned host buffer on a side stream while every GPU decodes group g+1.
+
+    Layout of the buffer (device and host): [group 0: rank 0 | rank 1 | ... ][group 1: ...] ...; `slices` maps every
+    utterance of the job to (offset, samples)."""
+
+    def __init__(self, lengths, samples_per_code: int, n_groups: int, local_rank: int, group=None, pin_host: bool = True):
+        import torch
+        import torch.distributed as dist
+        self.dist, self.torch, self.group = dist, torch, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.local, self.G, self.spc = local_rank, n_groups, samples_per_code
+        lengths = np.asarray(lengths, dtype=np.int64)
+        self.shards = [shard_utterances(lengths, self.world, r) for r in range(self.world)]
+        self.groups = [[sh[idx] for idx in split_groups(lengths[sh], n_groups)] for sh in self.shards]   # [rank][group] -> utt ids
+        self.count = [[int(lengths[ids].sum()) * samples_per_code for ids in gr] for gr in self.groups]
+        self.off = [[0] * n_groups for _ in range(self.world)]
+        self.group_range = []
+        self.slices = [None] * len(lengths)
+        o = 0
+        for g in range(n_groups):
+            start = o
+            for r in range(self.world):
+                self.off[r][g] = o
+                oo = o
+                for i in self.groups[r][g]:
+                    n = int(lengths[i]) * samples_per_code
+                    self.slices[int(i)] = (oo, n)
+                    oo += n
+                o += self.count[r][g]
+            self.group_range.append((start, o))
+        self.total = o
+        from . import binding
+        self.binding = binding
+        dev = torch.device("cuda", local_rank)
+        box = [None]
+        self.owner = self.rank == 0
+        if self.owner:
+            self.ptr = binding.device_alloc(local_rank, max(2, self.total * 2))
+            box[0] = binding.ipc_export(self.ptr)              # 64-byte CUDA IPC handle
+        dist.broadcast_object_list(box, src=0, group=group)
+        if not self.owner:
+            self.ptr = binding.ipc_open(box[0], local_rank)    # rank 0's memory mapped here, peer access enabled with it
+        self.flag = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.host = None
+        if self.owner:
+            self.buf = device_tensor(self.ptr, max(1, self.total), "int16", local_rank)
+            self.host = torch.empty(max(1, self.total), dtype=torch.int16)
+            if pin_host:
+                self.host = self.host.pin_memory()
+            self.side = torch.cuda.Stream(device=dev)
+
+    def close(self):
+        self.torch.cuda.synchronize()
+        self.dist.barrier(group=self.group)                    # nobody unmaps while a peer may still be storing ...
+        if not self.owner:
+            self.binding.ipc_close(self.ptr)
+        self.dist.barrier(group=self.group)                    # ... and the owner frees only after every mapping is closed
+        if self.owner:
+            self.buf = None
+            self.binding.device_free(self.ptr)
+        self.ptr = 0
+
+    def my_group(self, g: int) -> np.ndarray:
+        """Utterance ids (of the whole job) this rank decodes in group g."""
+        return self.groups[self.rank][g]
+
+    def put(self, codec, g: int):
+        """After codec.batch_run() of group g: store its PCM16 into the job buffer, then the stream-ordered rendezvous;
+        rank 0 starts the host copy of the whole group's region behind it."""
+        n = self.count[self.rank][g]
+        if n > 0:
+            codec.pcm16_to_device(self.ptr + 2 * self.off[self.rank][g], n)
+        self.dist.all_reduce(self.flag, group=self.group)      # every rank's stores of group g precede this on its stream
+        if self.rank == 0:
+            lo, hi = self.group_range[g]
+            if hi > lo:
+                ev = self.torch.cuda.Event()
+                ev.record(self.torch.cuda.current_stream())
+                with self.torch.cuda.stream(self.side):
+                    self.side.wait_event(ev)
+                    self.host[lo:hi].copy_(self.buf[lo:hi], non_blocking=True)
+
+    def finish(self):
+        """Rank 0: wait for the last host copy; returns the host buffer (None elsewhere)."""
+        if self.rank == 0:
+            self.side.synchronize()
+        return self.host
+
+
 class SharedPinnedBuffer:
     """ONE host buffer for the whole job, written by every rank directly: a /dev/shm file mapped by all ranks, each rank
     page-locking (cudaHostRegister) only the slice its own GPU copies into.  The alternative to gather_to_rank0 when the
