@@ -132,8 +132,8 @@ int  mio_batch_fetch_pcm16(mio_ctx * ctx, int16_t * pcm_out, int64_t pcm_cap);
  * samples_per_token*sum(T); valid until the next upload).  The sharded sweep's one exchange step (the final
  * gather of variable-length waveforms to the collecting rank) sends this buffer peer to peer.  NULL on error. */
 void * mio_batch_pcm16_device(mio_ctx * ctx);
-/* The same conversion stored straight into a caller-supplied DEVICE buffer of at least samples_per_token*sum(T) int16
- * (asynchronous on the context's stream).  The buffer may be ANOTHER GPU's memory mapped into this process (CUDA IPC /
+/* The same conversion stored straight into a caller-supplied, 16-byte aligned DEVICE buffer of at least
+ * samples_per_token*sum(T) int16 (asynchronous on the context's stream).  The buffer may be ANOTHER GPU's memory mapped into this process (CUDA IPC /
  * peer access): the stores then cross NVLink inside the kernel and the gather needs no separate transfer step. */
 int  mio_batch_pcm16_to_device(mio_ctx * ctx, void * dst_device, int64_t cap);
 /* Device buffers shared between the processes of one box (one process per GPU): the collecting rank allocates, exports a

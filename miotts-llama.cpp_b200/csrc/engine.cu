@@ -1339,6 +1339,7 @@ std::string engine::pcm16_device(int16_t ** out) {
 std::string engine::pcm16_to_device(int16_t * dst, int64_t cap) {
     if (!batch_ran) return "mio_batch_pcm16_to_device before mio_batch_run";
     if (!dst || cap < wave_samples) return "bad argument: destination too small";
+    if (((uintptr_t) dst & 15) != 0) return "bad argument: destination must be 16-byte aligned (8 samples)";
     CK(cudaSetDevice(device));
     CKR(CAT_PEAK, (double) wave_samples * 6.0, launch_pcm16(d_wave, dst, 0, wave_samples, stream));
     return {};

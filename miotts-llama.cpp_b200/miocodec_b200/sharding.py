@@ -160,8 +160,8 @@ class P2PGather:
     all-reduce (no host synchronisation), then rank 0 copies group g's region -- laid out group-major, so it is one
     contiguous range -- to the pinned host buffer on a side stream while every GPU decodes group g+1.
 
-    Layout of the buffer (device and host): [group 0: rank 0 | rank 1 | ... ][group 1: ...] ...; `slices` maps every
-    utterance of the job to (offset, samples)."""
+    Layout of the buffer (device and host): [group 0: rank 0 | rank 1 | ... ][group 1: ...] ..., every slice starting on a
+    multiple of 8 samples; `slices` maps every utterance of the job to (offset, samples)."""
 
     def __init__(self, lengths, samples_per_code: int, n_groups: int, local_rank: int, group=None, pin_host: bool = True):
         import torch
@@ -180,6 +180,7 @@ class P2PGather:
         for g in range(n_groups):
             start = o
             for r in range(self.world):
+                o = (o + 7) & ~7                               # slices start on 16 bytes: the conversion kernel stores 8 samples at a time
                 self.off[r][g] = o
                 oo = o
                 for i in self.groups[r][g]:
