@@ -152,6 +152,33 @@ def split_groups(lengths, n_groups: int) -> list[np.ndarray]:
     return [np.arange(cuts[g], max(cuts[g], cuts[g + 1])) for g in range(n_groups)]
 
 
+def p2p_layout(lengths, world: int, samples_per_code: int, n_groups: int) -> dict:
+    """Layout of the job buffer of P2PGather: group-major [group 0: rank 0 | rank 1 | ...][group 1: ...], every
+    (rank, group) slice starting on a multiple of 8 samples (the conversion kernel stores 16 bytes at a time).
+    groups[r][g] = utterance ids rank r decodes in group g; count / off[r][g] = samples / offset of that slice;
+    group_range[g] = (lo, hi) of the whole group (one contiguous host copy); slices[i] = (offset, samples) of utterance i."""
+    lengths = np.asarray(lengths, dtype=np.int64)
+    shards = [shard_utterances(lengths, world, r) for r in range(world)]
+    groups = [[sh[idx] for idx in split_groups(lengths[sh], n_groups)] for sh in shards]
+    count = [[int(lengths[ids].sum()) * samples_per_code for ids in gr] for gr in groups]
+    off = [[0] * n_groups for _ in range(world)]
+    group_range, slices = [], [None] * len(lengths)
+    o = 0
+    for g in range(n_groups):
+        start = o
+        for r in range(world):
+            o = (o + 7) & ~7
+            off[r][g] = o
+            oo = o
+            for i in groups[r][g]:
+                n = int(lengths[i]) * samples_per_code
+                slices[int(i)] = (oo, n)
+                oo += n
+            o += count[r][g]
+        group_range.append((start, o))
+    return dict(groups=groups, count=count, off=off, group_range=group_range, slices=slices, total=o)
+
+
 class P2PGather:
     """The gather of the sharded sweep WITHOUT a transfer step: rank 0 owns one device buffer for the whole job and maps it
     into every rank (CUDA IPC over the NVLink / NVSwitch fabric); each rank's PCM16 conversion kernel stores its result
@@ -169,27 +196,9 @@ class P2PGather:
         self.dist, self.torch, self.group = dist, torch, group
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.local, self.G, self.spc = local_rank, n_groups, samples_per_code
-        lengths = np.asarray(lengths, dtype=np.int64)
-        self.shards = [shard_utterances(lengths, self.world, r) for r in range(self.world)]
-        self.groups = [[sh[idx] for idx in split_groups(lengths[sh], n_groups)] for sh in self.shards]   # [rank][group] -> utt ids
-        self.count = [[int(lengths[ids].sum()) * samples_per_code for ids in gr] for gr in self.groups]
-        self.off = [[0] * n_groups for _ in range(self.world)]
-        self.group_range = []
-        self.slices = [None] * len(lengths)
-        o = 0
-        for g in range(n_groups):
-            start = o
-            for r in range(self.world):
-                o = (o + 7) & ~7                               # slices start on 16 bytes: the conversion kernel stores 8 samples at a time
-                self.off[r][g] = o
-                oo = o
-                for i in self.groups[r][g]:
-                    n = int(lengths[i]) * samples_per_code
-                    self.slices[int(i)] = (oo, n)
-                    oo += n
-                o += self.count[r][g]
-            self.group_range.append((start, o))
-        self.total = o
+        lay = p2p_layout(lengths, self.world, samples_per_code, n_groups)
+        self.groups, self.count, self.off = lay["groups"], lay["count"], lay["off"]
+        self.group_range, self.slices, self.total = lay["group_range"], lay["slices"], lay["total"]
         from . import binding
         self.binding = binding
         dev = torch.device("cuda", local_rank)

@@ -80,3 +80,35 @@ def test_two_devices_in_one_process(assets):
     # interleaved use keeps working (each call selects its own device)
     assert np.array_equal(c0.decode_wave(codes, emb), a) and np.array_equal(c1.decode_wave(codes, emb), b)
     c0.close(); c1.close()
+
+
+def test_pcm16_into_a_caller_supplied_device_buffer(codec):
+    """mio_batch_pcm16_to_device (the store side of sharding.P2PGather): same bytes as the host delivery, written into a
+    caller-owned device allocation at a 16-byte aligned offset; a misaligned destination is refused, not crashed on; the
+    allocation exports a 64-byte IPC handle.  (Opening the handle needs a second process: bench.py --gpus >= 2 does that and
+    checks every rank's bytes.)"""
+    import torch
+    from miocodec_b200 import binding, sharding, synth
+    lens = [33, 17, 60]
+    cu = np.cumsum([0] + lens).astype(np.int32)
+    codes = synth.synth_codes(int(cu[-1]), 77)
+    vt = np.stack([synth.synth_voice(1), synth.synth_voice(2)]).astype(np.float32)
+    vids = np.array([0, 1, 0], dtype=np.int32)
+    want = codec.decode_pcm16_batch(codes, cu, vt, vids)
+    codec.batch_upload(codes, cu, vt, vids)
+    codec.batch_run(False)
+    n = int(cu[-1]) * codec.samples_per_token
+    ptr = binding.device_alloc(0, 2 * (n + 64))
+    try:
+        assert len(binding.ipc_export(ptr)) == 64
+        assert codec.pcm16_to_device(ptr + 2 * 24, n) == n          # 24 samples = 48 bytes in: 16-byte aligned
+        codec.batch_sync()
+        got = sharding.device_tensor(ptr + 2 * 24, n, "int16", 0).cpu().numpy()
+        assert np.array_equal(got, want)
+        with pytest.raises(binding.MioError):
+            codec.pcm16_to_device(ptr + 2 * 3, n)                   # 6 bytes in
+        with pytest.raises(binding.MioError):
+            codec.pcm16_to_device(ptr, n - 1)                       # too small
+    finally:
+        torch.cuda.synchronize()
+        binding.device_free(ptr)

@@ -140,3 +140,33 @@ def test_corrupt_tensor_extents_are_rejected_at_open(tmp_path):
         assert b"corrupt GGUF" in L.mio_last_error()
         out = np.zeros(8, dtype=np.float32)
         assert L.mio_voice_load(str(p).encode(), out.ctypes.data, 8) == binding.MIO_ERR_FORMAT
+
+
+def test_p2p_gather_layout_covers_every_sample_once():
+    """sharding.p2p_layout (the job buffer of the P2P gather): group-major, every (rank, group) slice on a multiple of 8
+    samples, slices disjoint, every utterance exactly once, groups of a rank contiguous in its shard order, and each
+    rank's groups concatenated give its shard back (what lets a rank check its own bytes against its plain decode)."""
+    from miocodec_b200 import sharding
+    rng = np.random.default_rng(11)
+    for world, G, n in ((8, 8, 4096), (2, 4, 37), (3, 5, 4), (1, 3, 10)):
+        lens = rng.integers(1, 751, size=n)
+        L = sharding.p2p_layout(lens, world, 1764, G)
+        seen = np.zeros(L["total"], dtype=np.int8)
+        for i, (o, cnt) in enumerate(L["slices"]):
+            assert cnt == int(lens[i]) * 1764
+            seen[o:o + cnt] += 1
+        assert seen.max() == 1 and int(seen.sum()) == int(lens.sum()) * 1764
+        for r in range(world):
+            shard = sharding.shard_utterances(lens, world, r)
+            assert np.array_equal(np.concatenate([np.asarray(g, dtype=np.int64) for g in L["groups"][r]]) if len(shard) else np.arange(0), shard)
+            for g in range(G):
+                assert L["off"][r][g] % 8 == 0
+                lo, hi = L["group_range"][g]
+                assert lo <= L["off"][r][g] and L["off"][r][g] + L["count"][r][g] <= hi
+        for g in range(G - 1):
+            assert L["group_range"][g][1] <= L["group_range"][g + 1][0] + 0 or L["group_range"][g][1] == L["group_range"][g + 1][0]
+        # balance: no group of a rank carries more than twice the mean once there is enough work
+        if n >= 1000:
+            for r in range(world):
+                c = np.array(L["count"][r], dtype=np.float64)
+                assert c.max() < 1.5 * c.mean()
