@@ -54,6 +54,14 @@ FLOOR_MAXABS = 2.9e-3        # largest per-utterance v3-vs-v4 max-abs measured o
 _floor_refs = {}
 
 
+def both_reference_builds_available():
+    """True when this host can run the AVX2 AND the AVX-512 build of the reference (the measured parity floor)."""
+    from oracle import ref
+    here = os.path.dirname(os.path.abspath(ref.__file__))
+    return all(os.path.exists(os.path.join(here, "_ref", f"libmio_ref_{t}.so")) for t in ("v3", "v4")) and \
+        {"avx512f", "avx512bw", "avx512dq", "avx512vl", "avx512cd"} <= ref._cpu_flags()
+
+
 def reference_floor(gguf, codes, emb):
     """(SNR dB, max-abs) between the two builds of the reference (oracle/_ref v3 = AVX2, v4 = AVX-512) for this utterance,
     or the recorded constants when this host cannot run both."""

@@ -15,7 +15,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import reference_floor, snr_db
+from conftest import both_reference_builds_available, reference_floor, snr_db
 
 pytestmark = pytest.mark.gpu
 
@@ -36,6 +36,13 @@ STORAGE = {
     "F16 matrices, F32 conv kernels": dict(matrices="f16", convs="f32"),
     "BF16 matrices": dict(matrices="bf16"),
 }
+# v3-v4 floors recorded on an AVX-512 host (profiles/r2f), used when this host cannot run both reference builds
+RECORDED_GEOMETRY_FLOOR = {"k=f [3,3]": (59.81, 1.8e-3), "k [7,5]": (59.20, 2.5e-3), "k [5,9]": (59.56, 2.5e-3), "k=5f [15,15]": (60.23, 2.7e-3),
+                           "factors [9,1]": (58.04, 3.9e-3), "factors [1,9]": (60.24, 1.6e-3),
+                           "factors [2,2] (784 samples per code)": (57.63, 3.4e-3), "widths 384/192, out_proj 448": (59.74, 1.8e-3),
+                           "widths 128/64": (58.58, 3.8e-3), "widths 512/512": (61.21, 6.0e-4)}
+RECORDED_FLOOR = {"F16 matrices and conv kernels": (49.38, 7.4e-3), "F16 matrices, F32 conv kernels": (50.45, 5.0e-3),
+                  "BF16 matrices": (34.06, 5.0e-2)}
 
 
 def _decode_pair(tmp_path, kw, T=60, seed=9):
@@ -69,6 +76,8 @@ def _decode_pair(tmp_path, kw, T=60, seed=9):
 @pytest.mark.parametrize("name", list(GEOMETRY))
 def test_upsampler_geometry(tmp_path, name):
     s, m, f_snr, f_max = _decode_pair(tmp_path, GEOMETRY[name])
+    if not both_reference_builds_available():
+        f_snr, f_max = RECORDED_GEOMETRY_FLOOR[name]
     print(f"{name}: SNR {s:.2f} dB (reference v3-v4 floor {f_snr:.2f}), max-abs {m:.2e} (floor {f_max:.2e})")
     # relative to THIS file's floor (a random file with a 1-tap second stage sits at 58.0 dB reference-to-reference)
     assert s > min(f_snr, 60.0) - 1.0 and m < 1.5 * max(f_max, 2.9e-3)
@@ -77,6 +86,8 @@ def test_upsampler_geometry(tmp_path, name):
 @pytest.mark.parametrize("name", list(STORAGE))
 def test_stored_matrix_types_follow_the_reference_arithmetic(tmp_path, name):
     s, m, f_snr, f_max = _decode_pair(tmp_path, STORAGE[name])
+    if not both_reference_builds_available():
+        f_snr, f_max = RECORDED_FLOOR[name]
     print(f"{name}: SNR {s:.2f} dB (reference v3-v4 floor {f_snr:.2f}), max-abs {m:.2e} (floor {f_max:.2e})")
     assert s > f_snr - 1.5 and m < 2.0 * f_max
 
