@@ -1,6 +1,7 @@
 // Launchers of the sm_100a kernels.  Everything here works on the padded row space described in DESIGN.md:
 // activations are row-major [rows][C] (channels contiguous), rows of all utterances of a batch are
-// concatenated, each utterance followed by r zero rows at resolution r in {1, 2, 6, 18}.
+// concatenated, each utterance in a slot of roundup(len + 1, 16) rows (zero rows behind it), times r at resolution r in
+// {1, 2, 2*f0, 2*f0*f1} (the upsampler factors of the file; 1 / 2 / 6 / 18 for [3, 3]).
 #pragma once
 #include <cuda.h>
 #include <cuda_fp16.h>
