@@ -297,8 +297,8 @@ cudaError_t launch_attention_simt(const __half * qkv_hi, const __half * qkv_lo, 
 // partition depends only on the utterance.  Stage 1: one block per (utterance, segment of GN_SEG_CODES codes counted
 // from the utterance's first row); thread (c4, rl) sums one float4 column over the rows rl, rl + RL, ... of the segment
 // in ascending order, the partial sums of a group are combined by an xor-shuffle tree and then over rl in ascending
-// order -> part[segment][group] = (sum, sum of squares) in fp64.  Stage 2 (gn_finalize_kernel): one thread per
-// (utterance, group) adds the segments in ascending order.  No atomics: the same utterance gives the same bits alone,
+// order -> part[segment][group] = (sum, sum of squares) in fp64.  Stage 2 (gn_finalize_kernel): one warp per
+// (utterance, group) adds the segments in a fixed order.  No atomics: the same utterance gives the same bits alone,
 // in any batch, at any position and under any chunking.
 __global__ void __launch_bounds__(256) gn_stats_kernel(const float * __restrict__ x, int C, const int32_t * __restrict__ start,
                                                        const int32_t * __restrict__ len, const int32_t * __restrict__ seg_cu,
@@ -398,18 +398,27 @@ __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x));
 // 1/sqrt(var + eps)) in fp32, once per (utterance, group): keeps the fp64 arithmetic (slow on this part) out of the
 // per-element kernel.  var = sum((x-mean)^2)/n with the float-rounded mean, like the reference's second pass
 // (ops.cpp:3990-4010).
-__global__ void gn_finalize_kernel(const double2 * __restrict__ part, const int32_t * __restrict__ seg_cu,
-                                   const int32_t * __restrict__ len, int n_utts, int row_div,
-                                   int cpg, float eps, float2 * __restrict__ mr) {
+// One WARP per (utterance, group): lane l adds segments l, l + 32, ... in ascending order, a fixed xor-shuffle tree adds
+// the 32 lane sums -- an order that depends on the utterance's own segment count only, so still batch invariant, and
+// 44 segments (a 700-code utterance) cost two dependent loads per lane instead of 44 in a row.
+__global__ void __launch_bounds__(256) gn_finalize_kernel(const double2 * __restrict__ part, const int32_t * __restrict__ seg_cu,
+                                                          const int32_t * __restrict__ len, int n_utts, int row_div,
+                                                          int cpg, float eps, float2 * __restrict__ mr) {
     pdl_sync();
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= n_utts * 32) return;
+    const int idx = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (idx >= n_utts * 32) return;                // whole warps leave together
     const int u = idx >> 5, g = idx & 31;
     double sum = 0.0, sq = 0.0;
-    for (int sg = seg_cu[u]; sg < seg_cu[u + 1]; sg++) {
+    for (int sg = seg_cu[u] + lane; sg < seg_cu[u + 1]; sg += 32) {
         const double2 p = part[(size_t) sg * 32 + g];
         sum += p.x; sq += p.y;
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    }
+    if (lane != 0) return;
     const double n = (double) len[u] * row_div * cpg;
     const float mean = (float) (sum / n);
     const double md = (double) mean;
@@ -504,7 +513,7 @@ cudaError_t launch_gn_apply_silu(const float * x, int rows, int C, const row_map
                                  __half * out, cudaStream_t st, bool rev) {
     if (rows <= 0) return cudaSuccess;
     if (C <= 0 || C % 64 != 0) return cudaErrorInvalidValue;
-    launch_k(gn_finalize_kernel, dim3((rm.n_utts * 32 + 255) / 256), dim3(256), 0, st, part, seg_cu, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
+    launch_k(gn_finalize_kernel, dim3((rm.n_utts * 32 + 7) / 8), dim3(256), 0, st, part, seg_cu, rm.len, rm.n_utts, row_div, C / 32, eps, mr_scratch);
     static int precise_set = -1;
     if (precise_set < 0) {
         const char * ev = getenv("MIO_GN_PRECISE");
