@@ -114,3 +114,36 @@ def test_streams_against_the_reference_orchestrator(codec, assets, N):
     sn = snr_db(out, want)
     print(f"stream N={N}: vs the reference orchestrator SNR {sn:.2f} dB, MAE {err.mean():.2e}, max-abs {err.max():.2e}")
     assert sn > 58.0 and err.max() < 4.5e-3
+
+
+def test_unread_rounds_spill_out_of_the_pinned_pool(codec):
+    """The emitted samples of a round stay in a pinned block that the stream queues reference (no second host copy); at
+    most EMIT_POOL_MAX = 8 blocks may be referenced at once, later rounds are copied into the stream.  A consumer that
+    reads nothing until the end crosses that limit: 13 decode rounds for 300 codes.  Same samples, bit for bit, as the
+    policy port over single decodes, in both regimes, and a second stream that reads every round is not disturbed."""
+    from miocodec_b200 import synth
+    from oracle import port
+    N = 300
+    emb_a, emb_b = synth.synth_voice(3), synth.synth_voice(4)
+    ca, cb = synth.synth_codes(N, 901), synth.synth_codes(N, 902)
+    lazy, eager = codec.open_stream(emb_a), codec.open_stream(emb_b)
+    got_b = []
+    for k in range(N):
+        lazy.push(ca[k]); eager.push(cb[k])
+        if k == N - 1:
+            lazy.finish(); eager.finish()
+        codec.step_streams([lazy, eager])
+        a, last_b = eager.read()
+        got_b.append(a)
+    assert last_b
+    got_a, last_a = [], False
+    while not last_a:
+        a, last_a = lazy.read(1 << 16)             # small reads: slices are consumed across segment boundaries
+        got_a.append(a)
+    st = lazy.stats()
+    lazy.close(); eager.close()
+    assert st["decode_calls"] >= 12
+    for got, codes, emb in ((np.concatenate(got_a), ca, emb_a), (np.concatenate(got_b), cb, emb_b)):
+        want, _ = port.stream_policy(lambda c: codec.decode_wave(c, emb), codes)
+        assert got.shape == want.shape == (1764 * N,)
+        assert np.array_equal(got, want)
