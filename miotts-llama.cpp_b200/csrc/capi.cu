@@ -119,6 +119,10 @@ int mio_ctx_set_option(mio_ctx * c, const char * key, const char * value) {
         else return fail(MIO_ERR_ARG, "bad argument: chunk_acc must be off, prenet or all");
         return MIO_OK;
     }
+    if (!strcmp(key, "fuse_tail")) {
+        c->E.fuse_resblock_tail = strcmp(value, "0") != 0 && strcmp(value, "off") != 0;
+        return MIO_OK;
+    }
     if (!strcmp(key, "max_chunk_codes")) {
         if (c->E.ws_ready) return fail(MIO_ERR_STATE, "max_chunk_codes must be set before the first decode");
         const long v = strtol(value, nullptr, 10);

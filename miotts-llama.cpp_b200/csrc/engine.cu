@@ -536,6 +536,7 @@ std::string engine::load(const std::string & path, int dev) {
     CK(istft_init_device());
     { const char * ev = getenv("MIO_ATTN"); attn_simt = ev && !strcmp(ev, "simt"); }
     { const char * ev = getenv("MIO_SERPENTINE"); if (ev && ev[0] == '0') serpentine = false; }
+    { const char * ev = getenv("MIO_FUSE_TAIL"); if (ev) fuse_resblock_tail = ev[0] != '0'; }
     { const char * ev = getenv("MIO_CHUNK_ACC"); if (ev) chunk_mode = !strcmp(ev, "off") ? 0 : (!strcmp(ev, "all") ? 2 : 1); }
     { const char * ev = getenv("MIO_CHUNK_KB"); if (ev && atoi(ev) >= 1 && atoi(ev) <= 64) chunk_kb = atoi(ev); }
     CK(cudaDeviceSynchronize());
@@ -1013,7 +1014,7 @@ void engine::prof_collect() {
     } while (0)
 
 std::string engine::run_resblock(const resblock_w & R, float * x, float * y, const a_view & vc, int rows, int row_div,
-                                 const std::string & tag) {
+                                 const std::string & tag, const a_view * split_out) {
     const row_map rm = rmap();
     const int C = R.C;
     const int32_t * scu = d_seg_cu + cur_scu0;
@@ -1029,6 +1030,12 @@ std::string engine::run_resblock(const resblock_w & R, float * x, float * y, con
     CKR(CAT_GN_STATS, (double) (rows) * 4.0 * (C), launch_gn_stats(y, C, rm, row_div, scu, cur_n_segs, gn_part, stream, next_dir()));
     CKR(CAT_GN_APPLY, (double) (rows) * 6.0 * (C), launch_gn_apply_silu(y, rows, C, rm, row_div, gn_part, scu, hp.gn_eps, R.n2w, R.n2b, gn_mr, vc.hi, stream, next_dir())); launches++;
     if (taps_on()) tap_f16(tag + "_h2", vc.hi, nullptr, (size_t) rows * C);
+    if (split_out) {   // x + conv2(...) goes straight to the next product's operand buffers, zeros on pad rows
+        p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = split_out->hi; p.out_lo = split_out->lo; p.ld_h = C; p.bias = R.c2b;
+        p.resid = x; p.ld_resid = C; p.row_utt = rm.row_utt; p.row_div = row_div;
+        CKG(gemm(R.c2, vc, rows, p));
+        return {};
+    }
     p = gemm_params(); p.epi = EPI_RESID; p.out_f32 = x; p.ld_out = C; p.bias = R.c2b;
     CKG(gemm(R.c2, vc, rows, p));
     if (taps_on()) tap_f32(tag + "_out", x, rows, C);
@@ -1149,27 +1156,32 @@ std::string engine::run_chunk(const chunk_info & c) {
     }
     if (taps_on()) tap_f32("final_norm", x512, R2, C);
     // 7. post resnet blocks
+    // The last block of a stage feeds only the next product: unless a tap wants the fp32 tensor, its conv2 epilogue adds the
+    // residual and writes the (hi, lo) operand directly (no reduce-add into x, no split pass): fuse_tail
+    const bool fuse_tail = !taps_on() && fuse_resblock_tail;
     for (int b = 0; b < hp.resnet_blocks; b++)
-        if (!(e = run_resblock(w.post[b], x512, y512, vC512, R2, 2, "post" + std::to_string(b))).empty()) return e;
+        if (!(e = run_resblock(w.post[b], x512, y512, vC512, R2, 2, "post" + std::to_string(b),
+                               (fuse_tail && b == hp.resnet_blocks - 1) ? &vA512 : nullptr)).empty()) return e;
+    const bool post_fused = fuse_tail && hp.resnet_blocks > 0;
     if (taps_on()) tap_f32("post", x512, R2, C);
     // 8. upsampler stage 0: ConvT(512 -> c0, kernel k0, stride f0) + bias + trim + Snake, then resblock
-    CKR(CAT_SPLIT, (double) (R2) * 8.0 * (C), launch_split(x512, R2, C, rm, 2, vA512.hi, vA512.lo, stream));
+    if (!post_fused) CKR(CAT_SPLIT, (double) (R2) * 8.0 * (C), launch_split(x512, R2, C, rm, 2, vA512.hi, vA512.lo, stream));
     p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = xu0; p.ld_out = f0 * c0; p.bias = w.upT_b[0]; p.bias_mod = c0;
     p.snake_ea = w.snake_ea[0]; p.snake_eb = w.snake_eb[0];
     CKG(gemm(w.upT[0], vA512, R2, p));
     if (taps_on()) tap_f32("up0_snake", xu0, Ru0, c0);
-    if (!(e = run_resblock(w.up_res[0], xu0, yu0, vCu0, Ru0, rd0, "upres0")).empty()) return e;
+    if (!(e = run_resblock(w.up_res[0], xu0, yu0, vCu0, Ru0, rd0, "upres0", fuse_tail ? &vFFu0 : nullptr)).empty()) return e;
     if (taps_on()) tap_f32("up0", xu0, Ru0, c0);
     //    stage 1: ConvT(c0 -> c1, kernel k1, stride f1)
-    CKR(CAT_SPLIT, (double) (Ru0) * 8.0 * (c0), launch_split(xu0, Ru0, c0, rm, rd0, vFFu0.hi, vFFu0.lo, stream));
+    if (!fuse_tail) CKR(CAT_SPLIT, (double) (Ru0) * 8.0 * (c0), launch_split(xu0, Ru0, c0, rm, rd0, vFFu0.hi, vFFu0.lo, stream));
     p = gemm_params(); p.epi = EPI_SNAKE; p.out_f32 = xu1; p.ld_out = f1 * c1; p.bias = w.upT_b[1]; p.bias_mod = c1;
     p.snake_ea = w.snake_ea[1]; p.snake_eb = w.snake_eb[1];
     CKG(gemm(w.upT[1], vFFu0, Ru0, p));
     if (taps_on()) tap_f32("up1_snake", xu1, Ru1, c1);
-    if (!(e = run_resblock(w.up_res[1], xu1, yu1, vCu1, Ru1, rd1, "upres1")).empty()) return e;
+    if (!(e = run_resblock(w.up_res[1], xu1, yu1, vCu1, Ru1, rd1, "upres1", fuse_tail ? &vFFu1 : nullptr)).empty()) return e;
     if (taps_on()) tap_f32("up1", xu1, Ru1, c1);
     // 8b. out_proj c1 -> P + bias + Snake -> split operand of the head
-    CKR(CAT_SPLIT, (double) (Ru1) * 8.0 * (c1), launch_split(xu1, Ru1, c1, rm, rd1, vFFu1.hi, vFFu1.lo, stream));
+    if (!fuse_tail) CKR(CAT_SPLIT, (double) (Ru1) * 8.0 * (c1), launch_split(xu1, Ru1, c1, rm, rd1, vFFu1.hi, vFFu1.lo, stream));
     p = gemm_params(); p.epi = EPI_SPLIT; p.out_hi = vH.hi; p.out_lo = vH.lo; p.ld_h = P; p.bias = w.out_proj_b;
     p.snake_ea = w.out_snake_ea; p.snake_eb = w.out_snake_eb;
     CKG(gemm(w.out_proj, vFFu1, Ru1, p));

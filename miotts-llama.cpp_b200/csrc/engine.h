@@ -59,6 +59,7 @@ struct engine {
     // 2 = every fp32-class layer.  MIO_CHUNK_ACC=off|prenet|all, option "chunk_acc".
     int chunk_mode = 1;
     int chunk_kb = 3;                // k-blocks (64 of K each) per accumulation chunk: 3 costs no step time and gives 6e-7 (profiles/r2c_chunk_sweep.log; 2: 3.8e-7 at +4.6 %, 4: 8.4e-7); MIO_CHUNK_KB
+    bool fuse_resblock_tail = true;  // MIO_FUSE_TAIL=0 / option "fuse_tail": A/B switch of the residual + split epilogue (engine::run_resblock)
     int num_sms = 148;               // multiProcessorCount of the device (tile-width choice of the GEMM dispatch)
     int max_rows1 = 65536 + 4096;    // workspace rows at code resolution (codes + one pad row per utterance), ~8.5 GB
     bool ws_ready = false;
@@ -149,8 +150,10 @@ struct engine {
     std::string fetch_spec(int utt, float * out, int64_t cap);
     row_map rmap() const;
     std::string run_chunk(const chunk_info & c);
+    // split_out != nullptr (and no taps): the block's result is written as the (hi, lo) operand of the next product only
+    // (conv2 epilogue adds the residual itself and splits); x is then NOT updated
     std::string run_resblock(const resblock_w & R, float * x, float * y, const a_view & vc, int rows, int row_div,
-                             const std::string & tag);
+                             const std::string & tag, const a_view * split_out = nullptr);
     std::string run_istft(const chunk_info & c, const float * spec_dev);
     std::string view512_ff(a_view & v);
     cudaError_t gemm(const gemm_weight & W, const a_view & A, int M, gemm_params p);

@@ -132,6 +132,21 @@ __device__ __forceinline__ void epi3_chunk(const gemm_params & p, int row, int c
         }
         stage_f16_row<8>(stage, lane, 2 * part, hi, lo);
     } else if constexpr (EPI == EPI_SPLIT || EPI == EPI_SNAKE) {
+        if constexpr (EPI == EPI_SPLIT) {
+            if (p.resid != nullptr) {       // resblock tail: h + r (resnet_block, src/miocodec.cpp:403-404); the same fp32 add the TMA reduce did
+                if (aux < 0) {
+#pragma unroll
+                    for (int i = 0; i < 32; i++) v[i] = 0.f;
+                } else {
+                    const float * r = p.resid + (size_t) row * p.ld_resid + col0;
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4) {
+                        const float4 x = __ldg((const float4 *) (r + i));
+                        v[i] += x.x; v[i + 1] += x.y; v[i + 2] += x.z; v[i + 3] += x.w;
+                    }
+                }
+            }
+        }
         if (p.snake_ea != nullptr) {
             // snake(x) = x + sin^2(e^alpha x) / e^beta  (snake_activation, src/miocodec.cpp:410-420, :717-725)
 #pragma unroll
@@ -405,6 +420,8 @@ gemm_tc3_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                     const int u = (row < p.M) ? p.row_utt[row / p.row_div] : -1;
                     if (u >= 0) aux = p.gate_voice[u];
                 }
+            } else if constexpr (EPI == EPI_SPLIT) {
+                if (p.resid != nullptr) aux = (row < p.M) ? p.row_utt[row / p.row_div] : -1;
             }
             if constexpr (CHUNK > 0) {
                 // running sum of this thread's row: CH pieces of 32 columns, in registers

@@ -70,6 +70,12 @@ __device__ __forceinline__ void gemm_epilogue(const gemm_params & p, int row, in
             *(uint2 *) (ol + i) = *(uint2 *) (lo + i);
         }
     } else if constexpr (EPI == EPI_SPLIT || EPI == EPI_SNAKE) {
+        if constexpr (EPI == EPI_SPLIT) {
+            if (p.resid != nullptr) {       // resblock tail: h + r, zeros on pad rows (see gemm3.cu)
+                const bool pad = p.row_utt[row / p.row_div] < 0;
+                for (int i = 0; i < NC && col0 + i < p.N; i++) v[i] = pad ? 0.f : v[i] + p.resid[(size_t) row * p.ld_resid + col0 + i];
+            }
+        }
         if (p.snake_ea != nullptr) {
             // snake(x) = x + sin^2(e^alpha x) / e^beta  (snake_activation, src/miocodec.cpp:410-420, :717-725)
 #pragma unroll

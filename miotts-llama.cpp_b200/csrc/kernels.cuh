@@ -61,6 +61,9 @@ struct gemm_params {
     const int32_t * gate_voice = nullptr;
     const int32_t * row_utt = nullptr; int row_div = 1;   // utt = row_utt[row / row_div] (<0: pad row)
     const float * snake_ea = nullptr; const float * snake_eb = nullptr;   // exp(alpha), exp(beta) [bias_mod]
+    // EPI_SPLIT only: y += resid[row][col] before the split, pad rows (row_utt < 0) written as zeros -- the last conv of a
+    // resblock whose result only feeds the next product: replaces the residual reduce-add into x AND the split pass over x
+    const float * resid = nullptr; int ld_resid = 0;
     // EPI_QKV: rope[pos][32][2] (cos, sin), pos = row - utt_start[utt] * row_div; columns < rope_cols are rotated,
     // columns < q_cols additionally multiplied by q_scale
     const float * rope = nullptr; int rope_max_pos = 0; const int32_t * utt_start = nullptr;

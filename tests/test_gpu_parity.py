@@ -318,3 +318,23 @@ def test_mean_parity_over_32_utterances(assets, codec):
     assert g_snr.mean() > f_snr.mean() - 0.6
     assert g_max.mean() < 1.25 * f_max.mean()
     assert (g_snr > np.minimum(f_snr, 60.0) - 1.0).all() and g_snr.min() > 58.5
+
+
+def test_fused_resblock_tail_is_bit_identical(assets):
+    """The last resblock of a stage writes x + conv2(...) straight into the next product's (hi, lo) operand (EPI_SPLIT with a
+    residual input) instead of a reduce-add into x followed by a split pass: the same fp32 add, so the waveform must not
+    change by a single bit -- ragged batch, pad rows included."""
+    from miocodec_b200 import binding, synth
+    lens = [33, 1, 250, 17]
+    cu = np.cumsum([0] + lens).astype(np.int32)
+    codes = synth.synth_codes(int(cu[-1]), 321)
+    vt = np.stack([synth.synth_voice(v) for v in range(3)]).astype(np.float32)
+    vids = np.array([0, 1, 2, 1], dtype=np.int32)
+    out = {}
+    for tag in ("1", "0"):
+        c = binding.MioCodec(assets[0], 0)
+        c.set_option("fuse_tail", tag)
+        out[tag] = (c.decode_wave_batch(codes, cu, vt, vids), c.kernel_launches())
+        c.close()
+    assert np.array_equal(out["1"][0], out["0"][0])
+    assert out["0"][1] - out["1"][1] == 3          # three split launches gone
