@@ -112,3 +112,14 @@ def test_pcm16_into_a_caller_supplied_device_buffer(codec):
     finally:
         torch.cuda.synchronize()
         binding.device_free(ptr)
+
+
+def test_random_ragged_batches_are_batch_invariant():
+    """tools/fuzz_batches.py: random batches (1-40 utterances of 1-400 codes, random voices, workspace sizes 512 .. 65 536
+    codes, three delivery calls incl. PCM16): every utterance equals its single-utterance decode bit for bit."""
+    import subprocess
+    import sys
+    from conftest import ROOT
+    import os
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "fuzz_batches.py"), "12", "5"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0 and "FUZZ PASSED" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
