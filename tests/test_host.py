@@ -170,3 +170,23 @@ def test_p2p_gather_layout_covers_every_sample_once():
             for r in range(world):
                 c = np.array(L["count"][r], dtype=np.float64)
                 assert c.max() < 1.5 * c.mean()
+
+
+def test_bench_arms_share_one_config_object():
+    """bench.py prints the SAME `config` in the GPU arm and in --impl reference (the driver compares them): both are built by
+    bench_config() from the workload alone."""
+    import importlib.util
+    import os
+    from conftest import ROOT
+    spec = importlib.util.spec_from_file_location("bench_module", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    for name in ("c3", "c2", "c5"):
+        a = bench.bench_config(bench.make_workload(name, 0, 1), 1)
+        b = bench.bench_config(bench.make_workload(name, 0, 1), 1)
+        assert a == b and set(a) == {"workload", "codes_per_gpu_per_step", "audio_s_per_gpu_per_step", "weights", "parallelism", "l2"}
+    c3 = bench.bench_config(bench.make_workload("c3", 0, 1), 1)
+    assert c3["codes_per_gpu_per_step"] == 64000 and c3["audio_s_per_gpu_per_step"] == 2560.0
+    # C5 is ONE sweep sharded over the ranks: the shards of all ranks add up to the 4096 utterances
+    lens = [bench.make_workload("c5", r, 4)["lens"] for r in range(4)]
+    assert sum(len(l) for l in lens) == 4096 and sum(int(l.sum()) for l in lens) == int(bench.make_workload("c5", 0, 1)["lens"].sum())
