@@ -2,7 +2,7 @@
 // kernel (gemm3.cu), computed with plain fp32 FMAs and libdevice transcendentals.  Selected with
 // mio_ctx_set_option("gemm", "simt") / MIO_GEMM=simt.  It is a validator, not a fallback: it runs on the same B200,
 // and the parity tests use it to separate tensor-core plumbing / accumulation effects from model bugs
-// (profiles/r2_parity_attribution.md).
+// (profiles/r2a_parity_attribution.md).
 //
 // Tap-GEMM: D[m][n] = sum_{tap} sum_k A[m + tap - taps/2][k] * B[n][tap*K + k].
 #include "kernels.cuh"

@@ -161,7 +161,7 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t * bar) {
 // Guide "intrinsic functions").  Absolute error ~5e-7 for |x| < 1e3 (-126 dB of a unit-amplitude signal), growing
 // to ~2e-6 at |x| = 1e5; far below the fp32 ulp of such an argument, where cos/sin are ill-conditioned anyway.
 // Deliberately branch-free: a libdevice slow path inlined 32x per chunk thrashed the instruction cache
-// (profiles/r1g: 13 % stall_no_inst in the out_proj epilogue).  inf / NaN propagate to NaN like sinf/cosf.
+// (round-1 ncu capture of the out_proj epilogue: 13 % stall_no_inst).  inf / NaN propagate to NaN like sinf/cosf.
 __device__ __forceinline__ float reduce_2pi(float x) {
     const float k = rintf(x * 0.15915494309189535f);
     float r = fmaf(-k, 6.28125f, x);                       // 2*pi = 6.28125 + 1.9350052e-3 + 3.0199160e-7 + ...
