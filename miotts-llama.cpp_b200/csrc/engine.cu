@@ -927,7 +927,7 @@ cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_pa
 
 // One bare GEMM through the product kernel (mio_debug_gemm): out[M][N] = A[M][K] * B[N][K]^T with the operands split /
 // rounded exactly as the decoder does (npass 3: fp16 hi/lo pairs, npass 1: fp16).  Per-op parity tests and the
-// accumulation study (tools/accuracy_study.py) compare it with an fp64 product of the same operands.
+// accumulation study (tests/accuracy_study.py) compare it with an fp64 product of the same operands.
 std::string engine::debug_gemm(int M, int N, int K, const float * A, const float * B, int npass, float * out) {
     if (M <= 0 || N <= 0 || K <= 0 || K % 64 != 0 || !A || !B || !out || (npass != 1 && npass != 3)) return "bad argument";
     if (istft_only) return "bad argument: this context has no decoder";

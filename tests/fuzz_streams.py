@@ -1,7 +1,7 @@
 """Randomised streaming check: S concurrent streams with random lengths, push bursts, read sizes and read laziness; every
 stream's concatenated output must equal the streaming-policy port (oracle/port.stream_policy, itself pinned bit for bit to
 the reference's orchestrator) driven by single-utterance decodes of the same decoder, bit for bit, and the StreamProfile
-counters must match.  TEST TOOL (imports oracle/).  usage: python tools/fuzz_streams.py [rounds] [seed]"""
+counters must match.  TEST TOOL (imports oracle/).  usage: python tests/fuzz_streams.py [rounds] [seed]"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "miotts-llama.cpp_b200"))

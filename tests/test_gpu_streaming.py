@@ -150,12 +150,12 @@ def test_unread_rounds_spill_out_of_the_pinned_pool(codec):
 
 
 def test_random_stream_sessions_match_the_policy_port():
-    """tools/fuzz_streams.py: random concurrent sessions (1-12 streams of 1-420 codes, push bursts of 1-37 codes, random read
+    """tests/fuzz_streams.py: random concurrent sessions (1-12 streams of 1-420 codes, push bursts of 1-37 codes, random read
     sizes, some consumers that read nothing until the end): every stream bit-identical to the policy port over single
     decodes, StreamProfile counters equal."""
     import os
     import subprocess
     import sys
     from conftest import ROOT
-    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "fuzz_streams.py"), "6", "9"], capture_output=True, text=True, timeout=900)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "fuzz_streams.py"), "6", "9"], capture_output=True, text=True, timeout=900)
     assert r.returncode == 0 and "STREAM FUZZ PASSED" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
