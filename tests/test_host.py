@@ -190,3 +190,25 @@ def test_bench_arms_share_one_config_object():
     # C5 is ONE sweep sharded over the ranks: the shards of all ranks add up to the 4096 utterances
     lens = [bench.make_workload("c5", r, 4)["lens"] for r in range(4)]
     assert sum(len(l) for l in lens) == 4096 and sum(int(l.sum()) for l in lens) == int(bench.make_workload("c5", 0, 1)["lens"].sum())
+
+
+def test_oracle_is_reached_from_test_infrastructure_only():
+    """oracle/ is the checker: the product package and tools/ must not import, link or execute it (bench.py may, in its
+    cpu_baseline / --impl reference legs; __graft_entry__.smoke() may, as the checker)."""
+    import os
+    import re
+    from conftest import ROOT
+    pat = re.compile(r"(from\s+oracle\b|import\s+oracle\b|oracle/_ref|libmio_ref)")
+    offenders = []
+    for top in ("miotts-llama.cpp_b200", "tools", "include"):
+        for d, _, files in os.walk(os.path.join(ROOT, top)):
+            if os.sep + "build" in d or "dropin" in d:
+                continue
+            for f in files:
+                if f.endswith((".py", ".cu", ".cpp", ".h", ".cuh", ".sh")):
+                    p = os.path.join(d, f)
+                    if f.startswith("gpu_job_") or f in ("profile.sh", "profile_gemm_layers.sh"):
+                        continue                                    # GPU job scripts only invoke pytest / bench.py
+                    if pat.search(open(p, errors="replace").read()):
+                        offenders.append(os.path.relpath(p, ROOT))
+    assert offenders == [], offenders
