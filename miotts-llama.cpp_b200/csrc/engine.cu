@@ -781,10 +781,18 @@ std::string engine::upload(const int32_t * codes, const int32_t * cu, int n_utts
     if (!(e = grow(&d_seg_cu, cap_scu, seg_cu_all.size())).empty()) return e;
     if (!(e = grow(&d_voice_table, cap_vt, (size_t) nv * hp.adaln_dim)).empty()) return e;
     if ((int64_t) wave_cap < wave_samples) {
+        // first allocation: exact.  A context whose batches keep growing (a streaming session re-decodes ever longer
+        // prefixes: 18 sizes for a 700-code stream, and freeing + allocating gigabytes stalls the device for tens to
+        // hundreds of ms each time, MIO_STREAM_TIMING=1) grows geometrically instead.
+        const int64_t grown = d_wave ? wave_cap + wave_cap / 2 : 0;
         if (d_wave) cudaFree(d_wave);
         d_wave = nullptr;
-        wave_cap = wave_samples + 64;
-        if (!(e = dev_alloc(&d_wave, (size_t) wave_cap)).empty()) return e;
+        wave_cap = std::max<int64_t>(wave_samples + 64, grown);
+        if (!(e = dev_alloc(&d_wave, (size_t) wave_cap)).empty()) {
+            (void) cudaGetLastError();                 // the failed attempt must not surface at the next launch check
+            wave_cap = wave_samples + 64;              // the headroom did not fit: exact size
+            if (!(e = dev_alloc(&d_wave, (size_t) wave_cap)).empty()) { wave_cap = 0; return e; }
+        }
     }
     // one pinned staging buffer, async copies on the context stream
     const size_t b_codes = (size_t) rows_total * 4, b_utts = (size_t) n_utts * 4, b_off = (size_t) n_utts * 8,

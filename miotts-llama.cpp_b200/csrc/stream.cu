@@ -130,6 +130,9 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
             if (streams[i] && streams[i]->job_head < streams[i]->jobs.size()) act.push_back(streams[i]);
         if (act.empty()) break;
         const auto t_pass0 = std::chrono::steady_clock::now();
+        static const bool timing = getenv("MIO_STREAM_TIMING") != nullptr;      // per-round host timeline on stderr
+        auto since = [&](const std::chrono::steady_clock::time_point & t) { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t).count(); };
+        double ms_prep = 0, ms_upload = 0, ms_run = 0, ms_emit = 0, ms_wait = 0;
         // a round holds at most max_voices streams (one conditioning row each); the rest fire in the next round of this
         // same call (the for(;;) loop runs until no stream has a pending job), so nothing is dropped
         if ((int) act.size() > E.max_voices) act.resize(E.max_voices);
@@ -142,10 +145,14 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
             vid.push_back((int32_t) k);
             vt.insert(vt.end(), act[k]->emb.begin(), act[k]->emb.end());
         }
+        ms_prep = since(t_pass0);
+        auto t1 = std::chrono::steady_clock::now();
         std::string e = E.upload(codes.data(), cu.data(), (int) act.size(), vt.data(), (int) act.size(), vid.data());
         if (!e.empty()) return e;
+        ms_upload = since(t1); t1 = std::chrono::steady_clock::now();
         e = E.run(false);      // streaming never peak-normalises (decode_codes_to_audio(..., false), :546)
         if (!e.empty()) return e;
+        ms_run = since(t1); t1 = std::chrono::steady_clock::now();
         // cut + crossfade on the device
         std::vector<emit_job> jobs(act.size());
         int64_t emit_total = 0;
@@ -188,8 +195,12 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
         if (emit_total > 0 &&
             cudaMemcpyAsync(blk->host, E.d_emit, (size_t) emit_total * sizeof(float), cudaMemcpyDeviceToHost, E.stream) != cudaSuccess)
             return "cudaMemcpyAsync failed (emit D2H)";
+        ms_emit = since(t1); t1 = std::chrono::steady_clock::now();
         e = E.sync();
         if (!e.empty()) return e;
+        ms_wait = since(t1);
+        if (timing) fprintf(stderr, "mio stream round: %zu streams, %zu codes: prep %.2f upload %.2f enqueue %.2f emit-setup %.2f wait %.2f ms\n",
+                            act.size(), codes.size(), ms_prep, ms_upload, ms_run, ms_emit, ms_wait);
         for (size_t k = 0; k < act.size(); k++) {
             stream_state & s = *act[k];
             const emit_job & J = jobs[k];

@@ -41,6 +41,9 @@ session(32, 100)
 if os.environ.get('C4_PROFILE'):
     codec.profile_enable(True)
 e, a, b, c = session(S, N)
+print(f'first session (cold buffers): push {a:.3f} s, step {b:.3f} s, read {c:.3f} s; total {a + b + c:.3f} s')
+print('---- second session', file=sys.stderr, flush=True)
+e, a, b, c = session(S, N)
 prof = codec.profile_read()
 print('device kernel time by category (s):', {k: round(v['ms'] / 1e3, 3) for k, v in prof.items() if v['ms'] > 0}, 'sum', round(sum(v['ms'] for v in prof.values()) / 1e3, 3), 'launches', sum(v['launches'] for v in prof.values()))
 print(f"emitted {e / 44100:.0f} audio-s; push {a:.3f} s, step {b:.3f} s, read {c:.3f} s; total {a + b + c:.3f} s")
