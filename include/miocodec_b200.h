@@ -67,6 +67,11 @@ int  mio_ctx_device(const mio_ctx * ctx);
 int  mio_ctx_set_option(mio_ctx * ctx, const char * key, const char * value);
 /* run all kernels of this context on an existing CUDA stream (cudaStream_t as void*), e.g. torch's */
 int  mio_ctx_set_stream(mio_ctx * ctx, void * cuda_stream);
+/* Pre-size the context for batches of up to max_batch_codes codes in max_utts utterances and for streaming rounds that
+ * emit up to max_emit_samples samples (0 = skip that part): device output / layout buffers, the PCM16 image, the pinned
+ * staging and emit blocks.  Optional -- everything grows on demand -- but a serving process should call it at start-up:
+ * growing by cudaMalloc / cudaMallocHost costs a first streaming session ~2 of its ~7 s. */
+int  mio_ctx_reserve(mio_ctx * ctx, int64_t max_batch_codes, int max_utts, int64_t max_emit_samples);
 
 /* ---- voice embedding: replaces load_voice_embedding (src/miocodec.h:41, src/miocodec.cpp:816-853).
  * Reads the FIRST tensor of the file, F32 only. Returns the number of floats (128) or <0. */

@@ -308,6 +308,14 @@ int mio_batch_fetch_pcm16(mio_ctx * c, int16_t * out, int64_t cap) {
     });
 }
 
+int mio_ctx_reserve(mio_ctx * c, int64_t max_batch_codes, int max_utts, int64_t max_emit_samples) {
+    return guarded([&]() -> int {
+        if (!c) return fail(MIO_ERR_ARG, "bad argument");
+        TRY(c->E.reserve(max_batch_codes, max_utts, max_emit_samples));
+        return MIO_OK;
+    });
+}
+
 void * mio_batch_pcm16_device(mio_ctx * c) {
     if (!c) { fail(MIO_ERR_ARG, "bad argument"); return nullptr; }
     int16_t * p = nullptr;

@@ -1340,6 +1340,41 @@ std::string engine::fetch_pcm16(int16_t * out, int64_t cap) {
     return {};
 }
 
+// Pre-size everything a batch of `total_codes` codes in `n_utts` utterances (and a streaming round emitting `emit_samples`
+// samples) will need, so that the first real call does not pay cudaMalloc / cudaMallocHost of hundreds of MB to GBs
+// (measured: up to 1 s for one pinned block, MIO_STREAM_TIMING=1).  Implemented as the upload of a dummy batch of that
+// shape (no kernels run) plus the streaming emit buffers.
+std::string engine::reserve(int64_t total_codes, int n_utts, int64_t emit_samples) {
+    if (total_codes < 0 || n_utts < 0 || emit_samples < 0) return "bad argument";
+    if (istft_only) return "bad argument: this context has no decoder";
+    CK(cudaSetDevice(device));
+    std::string e;
+    if (total_codes > 0 && n_utts > 0) {
+        n_utts = (int) std::min<int64_t>(n_utts, total_codes);
+        std::vector<int32_t> codes((size_t) total_codes, 0), cu((size_t) n_utts + 1), vid((size_t) n_utts, 0);
+        const int64_t per = total_codes / n_utts;
+        if (per + 1 >= max_rows1) return "bad argument: utterances of that length exceed max_chunk_codes";
+        for (int u = 0; u <= n_utts; u++) cu[u] = (int32_t) (u == n_utts ? total_codes : per * u);
+        std::vector<float> vt((size_t) hp.adaln_dim, 0.f);
+        if (!(e = upload(codes.data(), cu.data(), n_utts, vt.data(), 1, vid.data())).empty()) return e;
+        if (!(e = ensure_pcm()).empty()) return e;
+        if (!(e = sync()).empty()) return e;
+        batch_uploaded = false; batch_ran = false;
+    }
+    if (emit_samples > 0) {
+        if (emit_cap < emit_samples) {
+            if (d_emit) cudaFree(d_emit);
+            d_emit = nullptr; emit_cap = 0;
+            float * p = nullptr;
+            if (!(e = dev_alloc(&p, (size_t) emit_samples)).empty()) return e;
+            d_emit = p; emit_cap = emit_samples;
+        }
+        bool pooled = true;
+        if (!acquire_emit_block(emit_samples, &pooled)) return "cudaMallocHost failed (emit block)";
+    }
+    return {};
+}
+
 // PCM16 image of the resident waveform, left ON THE DEVICE (mio_batch_pcm16_device): converted on the context's stream,
 // valid until the next upload; the multi-GPU gather sends it to the collecting rank over NVLink.
 std::string engine::pcm16_device(int16_t ** out) {

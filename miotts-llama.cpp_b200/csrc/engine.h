@@ -131,6 +131,7 @@ struct engine {
     std::string run(bool peak_normalize, float * host_dst = nullptr, int16_t * host_pcm = nullptr);
     std::string run_impl(bool peak_normalize, float * host_dst, int16_t * host_pcm);
     std::string fetch_pcm16(int16_t * out, int64_t cap);
+    std::string reserve(int64_t total_codes, int n_utts, int64_t emit_samples);
     std::string pcm16_device(int16_t ** out);
     std::string pcm16_to_device(int16_t * dst, int64_t cap);
     int16_t * d_pcm = nullptr; int64_t pcm_cap = 0;       // PCM16 image of d_wave (grown on demand)

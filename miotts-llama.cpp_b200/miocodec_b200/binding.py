@@ -20,7 +20,7 @@ MIO_OK, MIO_ERR_ARG, MIO_ERR_IO, MIO_ERR_FORMAT, MIO_ERR_CUDA, MIO_ERR_RANGE, MI
 # every symbol include/miocodec_b200.h declares (tests check the library exports exactly these)
 EXPORTS = [
     "mio_ctx_create", "mio_istft_ctx_create", "mio_ctx_destroy", "mio_ctx_sample_rate", "mio_ctx_n_fft", "mio_ctx_hop_length",
-    "mio_batch_pcm16_device", "mio_batch_pcm16_to_device", "mio_device_alloc", "mio_device_free",
+    "mio_ctx_reserve", "mio_batch_pcm16_device", "mio_batch_pcm16_to_device", "mio_device_alloc", "mio_device_free",
     "mio_ipc_export", "mio_ipc_open", "mio_ipc_close", "mio_ctx_samples_per_token", "mio_ctx_frames_per_code", "mio_ctx_vocab", "mio_ctx_device", "mio_ctx_set_option",
     "mio_ctx_set_stream", "mio_voice_load", "mio_print_tensors", "mio_decode_spec", "mio_istft", "mio_decode_wave",
     "mio_decode_wave_batch", "mio_batch_upload", "mio_batch_run", "mio_batch_fetch", "mio_batch_sync",
@@ -80,6 +80,7 @@ def lib() -> C.CDLL:
     L.mio_batch_kernel_launches.restype = i64
     L.mio_batch_wave_device.argtypes = [vp]
     L.mio_batch_wave_device.restype = vp
+    L.mio_ctx_reserve.argtypes = [vp, C.c_int64, C.c_int, C.c_int64]
     L.mio_batch_pcm16_device.argtypes = [vp]
     L.mio_batch_pcm16_device.restype = vp
     L.mio_batch_pcm16_to_device.argtypes = [vp, vp, C.c_int64]
@@ -239,6 +240,10 @@ class MioCodec:
 
     def set_option(self, key: str, value: str):
         _check(lib().mio_ctx_set_option(self._h, key.encode(), str(value).encode()))
+
+    def reserve(self, max_batch_codes: int, max_utts: int, max_emit_samples: int = 0):
+        """Pre-size device / pinned buffers (mio_ctx_reserve)."""
+        _check(lib().mio_ctx_reserve(self._h, max_batch_codes, max_utts, max_emit_samples))
 
     def set_stream(self, cuda_stream_ptr: int):
         _check(lib().mio_ctx_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))

@@ -123,3 +123,36 @@ def test_random_ragged_batches_are_batch_invariant():
     import os
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "fuzz_batches.py"), "12", "5"], capture_output=True, text=True, timeout=900)
     assert r.returncode == 0 and "FUZZ PASSED" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_reserve_presizes_without_changing_results(assets, codec):
+    """mio_ctx_reserve: a dummy upload of the requested shape plus the streaming emit buffers; results afterwards are the
+    same bits as on an unreserved context, for a batch and for a stream."""
+    from miocodec_b200 import binding, synth
+    c = binding.MioCodec(assets[0], 0)
+    c.reserve(30000, 48, 1764 * 20 * 8)
+    with pytest.raises(binding.MioError):
+        c.reserve(-1, 1, 0)
+    lens = [120, 7, 64]
+    cu = np.cumsum([0] + lens).astype(np.int32)
+    codes = synth.synth_codes(int(cu[-1]), 55)
+    vt = np.stack([synth.synth_voice(1), synth.synth_voice(2)]).astype(np.float32)
+    vids = np.array([1, 0, 1], dtype=np.int32)
+    assert np.array_equal(c.decode_wave_batch(codes, cu, vt, vids), codec.decode_wave_batch(codes, cu, vt, vids))
+    outs = []
+    for ctx in (c, codec):
+        s = ctx.open_stream(synth.synth_voice(3))
+        got = []
+        sc = synth.synth_codes(90, 56)
+        for k in range(90):
+            s.push(sc[k])
+            if k == 89:
+                s.finish()
+            ctx.step_streams([s])
+            a, last = s.read()
+            got.append(a)
+        assert last
+        s.close()
+        outs.append(np.concatenate(got))
+    assert np.array_equal(outs[0], outs[1])
+    c.close()
