@@ -226,25 +226,34 @@ def run_reference(args):
 def streaming_session(codec, S: int, N: int):
     """S concurrent streams of N codes in lock-step under the reference's streaming policy (full-prefix re-decode at the
     commit cadence, src/test-to-speech.cpp:499-571).  Codes are pushed 20 at a time (the cadence is evaluated per code inside
-    the library, so the decode schedule is the one-code-per-tick schedule of the reference).  Returns (emitted samples,
-    wall seconds, StreamProfile counters of stream 0)."""
+    the library, so the decode schedule is the one-code-per-tick schedule of the reference).  Each round is split into
+    mio_streams_step_begin / _end with the consumer's reads in between (host copies under the GPU's decode).  Returns
+    (emitted samples, wall seconds, StreamProfile counters of stream 0)."""
     from miocodec_b200 import synth
     streams = [codec.open_stream(synth.synth_voice(i % N_VOICES)) for i in range(S)]
     codes = [synth.synth_codes(N, 4000 + i) for i in range(S)]
     t0 = time.perf_counter()
     emitted = 0
+    def drain():
+        n = 0
+        for st in streams:
+            while True:                       # 256k-sample reads: a 16 MB buffer per read costs more than the copy
+                a, _ = st.read(1 << 18)
+                n += a.size
+                if a.size < (1 << 18):
+                    break
+        return n
+
     for k in range(0, N, 20):
         for i, st in enumerate(streams):
             st.push(codes[i][k:k + 20])
             if k + 20 >= N:
                 st.finish()
-        codec.step_streams(streams)
-        for st in streams:
-            while True:                       # 256k-sample reads: a 16 MB buffer per read costs more than the copy
-                a, _ = st.read(1 << 18)
-                emitted += a.size
-                if a.size < (1 << 18):
-                    break
+        # the round is enqueued, then the consumer reads what EARLIER rounds emitted while the GPU decodes this one
+        codec.step_streams_begin(streams)
+        emitted += drain()
+        codec.step_streams_end(streams)
+    emitted += drain()
     dt = time.perf_counter() - t0
     stats = streams[0].stats()
     for st in streams:

@@ -177,6 +177,13 @@ int  mio_stream_push_codes(mio_stream * s, const int32_t * codes, int n);
 int  mio_stream_finish(mio_stream * s);
 /* advance all given streams: one batched decode for those with a pending emit */
 int  mio_streams_step(mio_ctx * ctx, mio_stream ** streams, int n_streams);
+/* The same round split in two so that the host works while the GPU decodes: _begin enqueues the round (upload, decode, cut +
+ * crossfade, the copy of the emitted samples into pinned memory) and returns at once; _end waits for it, hands the samples to
+ * the streams and runs whatever further passes they still need.  Between the two the caller may push codes to and read from
+ * any stream (reads return what earlier rounds emitted) -- e.g. generate the next tokens -- but not close a stream.
+ * mio_streams_step == _begin + _end. */
+int  mio_streams_step_begin(mio_ctx * ctx, mio_stream ** streams, int n_streams);
+int  mio_streams_step_end(mio_ctx * ctx, mio_stream ** streams, int n_streams);
 /* pop emitted audio (already crossfaded, in emission order). Returns samples copied. *is_last is set when
  * the stream has finished and its queue is drained. */
 int64_t mio_stream_read(mio_stream * s, float * out, int64_t cap, int * is_last);

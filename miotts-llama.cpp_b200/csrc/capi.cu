@@ -94,7 +94,10 @@ int mio_istft_ctx_create(int device, mio_ctx ** out_ctx) {
     });
 }
 
-void mio_ctx_destroy(mio_ctx * ctx) { delete ctx; }
+void mio_ctx_destroy(mio_ctx * ctx) {
+    if (ctx && ctx->E.pass.active) (void) streams_drain(ctx->E);
+    delete ctx;
+}
 
 int mio_ctx_sample_rate(const mio_ctx * c) { return c ? c->E.hp.sample_rate : 0; }
 int mio_ctx_n_fft(const mio_ctx * c) { return c ? c->E.hp.n_fft : 0; }
@@ -443,6 +446,7 @@ int mio_stream_open(mio_ctx * c, const float * emb, const mio_stream_config * cf
 }
 void mio_stream_close(mio_stream * s) {
     if (!s) return;
+    if (s->S && s->S->eng && s->S->eng->pass.active) (void) streams_drain(*s->S->eng);   // a round in flight may reference this stream
     delete s->S;
     delete s;
 }
@@ -464,6 +468,24 @@ int mio_streams_step(mio_ctx * c, mio_stream ** streams, int n) {
         std::vector<stream_state *> v(n);
         for (int i = 0; i < n; i++) v[i] = streams[i] ? streams[i]->S : nullptr;
         TRY(streams_step(c->E, v.data(), n));
+        return MIO_OK;
+    });
+}
+int mio_streams_step_begin(mio_ctx * c, mio_stream ** streams, int n) {
+    return guarded([&]() -> int {
+        if (!c || (!streams && n > 0) || n < 0) return fail(MIO_ERR_ARG, "bad argument");
+        std::vector<stream_state *> v(n);
+        for (int i = 0; i < n; i++) v[i] = streams[i] ? streams[i]->S : nullptr;
+        TRY(streams_step_begin(c->E, v.data(), n));
+        return MIO_OK;
+    });
+}
+int mio_streams_step_end(mio_ctx * c, mio_stream ** streams, int n) {
+    return guarded([&]() -> int {
+        if (!c || (!streams && n > 0) || n < 0) return fail(MIO_ERR_ARG, "bad argument");
+        std::vector<stream_state *> v(n);
+        for (int i = 0; i < n; i++) v[i] = streams[i] ? streams[i]->S : nullptr;
+        TRY(streams_step_end(c->E, v.data(), n));
         return MIO_OK;
     });
 }

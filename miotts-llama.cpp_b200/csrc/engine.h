@@ -3,6 +3,7 @@
 // (src/miocodec.cpp:519-810 of the reference) followed by istft() (src/istft.cpp:68-108).
 #pragma once
 #include <map>
+#include <chrono>
 #include <string>
 #include <vector>
 
@@ -113,6 +114,17 @@ struct engine {
     static constexpr int EMIT_POOL_MAX = 8;
     std::vector<emit_block *> emit_pool;
     emit_block * acquire_emit_block(int64_t samples, bool * pooled);
+    // a streaming pass in flight between streams_step_begin and streams_step_end (stream.cu)
+    struct stream_pass {
+        bool active = false, pooled = true;
+        std::vector<void *> act;                      // stream_state * of the pass
+        std::vector<int64_t> begin, end, off;         // cut range and offset in the emit block per stream
+        std::vector<uint8_t> jobs_host;               // the emit job table, alive until the pass ends
+        emit_block * blk = nullptr;
+        int64_t n_codes = 0;
+        std::chrono::steady_clock::time_point t0;
+        double ms_prep = 0, ms_upload = 0, ms_run = 0, ms_emit = 0;
+    } pass;
     // pinned staging
     void * h_stage = nullptr; size_t h_stage_bytes = 0;
     bool batch_uploaded = false, batch_ran = false;

@@ -120,111 +120,167 @@ std::string stream_finish(stream_state & s) {
     return {};
 }
 
-std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
-    cudaSetDevice(E.device);
+// One pass = the oldest pending job of up to max_voices streams as ONE ragged device batch.  pass_begin enqueues the whole
+// pass (upload, decode, cut + crossfade, the D2H copy of the emitted samples into a pinned block) and returns without
+// waiting; pass_end waits and hands the samples to the streams.  Between the two the host is free (the LLM produces the
+// next tokens, the consumer reads what earlier rounds emitted) while the GPU works.
+static std::string pass_begin(engine & E, stream_state ** streams, int n_streams, bool * any) {
+    *any = false;
+    engine::stream_pass & P = E.pass;
+    if (P.active) return "a streaming round is already in flight (mio_streams_step_end first)";
     const int spc = E.hp.samples_per_token;
-    for (;;) {
-        // round: the oldest pending job of every stream (jobs of one stream are ordered through its tail)
-        std::vector<stream_state *> act;
-        for (int i = 0; i < n_streams; i++)
-            if (streams[i] && streams[i]->job_head < streams[i]->jobs.size()) act.push_back(streams[i]);
-        if (act.empty()) break;
-        const auto t_pass0 = std::chrono::steady_clock::now();
-        static const bool timing = getenv("MIO_STREAM_TIMING") != nullptr;      // per-round host timeline on stderr
-        auto since = [&](const std::chrono::steady_clock::time_point & t) { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t).count(); };
-        double ms_prep = 0, ms_upload = 0, ms_run = 0, ms_emit = 0, ms_wait = 0;
-        // a round holds at most max_voices streams (one conditioning row each); the rest fire in the next round of this
-        // same call (the for(;;) loop runs until no stream has a pending job), so nothing is dropped
-        if ((int) act.size() > E.max_voices) act.resize(E.max_voices);
-        std::vector<int32_t> codes, cu(1, 0), vid;
-        std::vector<float> vt;
-        for (size_t k = 0; k < act.size(); k++) {
-            const stream_job & j = act[k]->jobs[act[k]->job_head];
-            codes.insert(codes.end(), act[k]->codes.begin(), act[k]->codes.begin() + j.prefix);
-            cu.push_back((int32_t) codes.size());
-            vid.push_back((int32_t) k);
-            vt.insert(vt.end(), act[k]->emb.begin(), act[k]->emb.end());
-        }
-        ms_prep = since(t_pass0);
-        auto t1 = std::chrono::steady_clock::now();
-        std::string e = E.upload(codes.data(), cu.data(), (int) act.size(), vt.data(), (int) act.size(), vid.data());
-        if (!e.empty()) return e;
-        ms_upload = since(t1); t1 = std::chrono::steady_clock::now();
-        e = E.run(false);      // streaming never peak-normalises (decode_codes_to_audio(..., false), :546)
-        if (!e.empty()) return e;
-        ms_run = since(t1); t1 = std::chrono::steady_clock::now();
-        // cut + crossfade on the device
-        std::vector<emit_job> jobs(act.size());
-        int64_t emit_total = 0;
-        for (size_t k = 0; k < act.size(); k++) {
-            stream_state & s = *act[k];
-            const stream_job & j = s.jobs[s.job_head];
-            const int64_t win = (int64_t) j.prefix * spc;                       // window_audio.size()
-            const double spc_actual = (double) win / (double) j.prefix;          // :554-556
-            const int64_t b = (int64_t) std::llround((double) j.commit_begin * spc_actual);
-            const int64_t en = std::min<int64_t>((int64_t) std::llround((double) j.commit_end * spc_actual), win);
-            emit_job & J = jobs[k];
-            J.wave_off = (int64_t) cu[k] * spc; J.begin = b; J.end = std::max(b, en); J.emit_off = emit_total;
-            J.tail = s.d_tail; J.tail_len = s.d_tail_len; J.chunk = s.cfg.chunk_samples; J.xfade = s.cfg.crossfade_samples;
-            emit_total += J.end - J.begin;
-            s.decode_calls++; s.decoded_codes += (int64_t) j.prefix;
-        }
-        if (E.emit_cap < emit_total || E.emit_jobs_cap < (int64_t) jobs.size()) {
+    // the oldest pending job of every stream (jobs of one stream are ordered through its tail)
+    std::vector<stream_state *> act;
+    for (int i = 0; i < n_streams; i++)
+        if (streams[i] && streams[i]->job_head < streams[i]->jobs.size()) act.push_back(streams[i]);
+    if (act.empty()) return {};
+    P.t0 = std::chrono::steady_clock::now();
+    auto since = [&](const std::chrono::steady_clock::time_point & t) { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t).count(); };
+    // a pass holds at most max_voices streams (one conditioning row each); the rest fire in the next pass of the same
+    // step call, so nothing is dropped
+    if ((int) act.size() > E.max_voices) act.resize(E.max_voices);
+    std::vector<int32_t> codes, cu(1, 0), vid;
+    std::vector<float> vt;
+    for (size_t k = 0; k < act.size(); k++) {
+        const stream_job & j = act[k]->jobs[act[k]->job_head];
+        codes.insert(codes.end(), act[k]->codes.begin(), act[k]->codes.begin() + j.prefix);
+        cu.push_back((int32_t) codes.size());
+        vid.push_back((int32_t) k);
+        vt.insert(vt.end(), act[k]->emb.begin(), act[k]->emb.end());
+    }
+    P.ms_prep = since(P.t0);
+    auto t1 = std::chrono::steady_clock::now();
+    std::string e = E.upload(codes.data(), cu.data(), (int) act.size(), vt.data(), (int) act.size(), vid.data());
+    if (!e.empty()) return e;
+    P.ms_upload = since(t1); t1 = std::chrono::steady_clock::now();
+    e = E.run(false);      // streaming never peak-normalises (decode_codes_to_audio(..., false), :546)
+    if (!e.empty()) return e;
+    P.ms_run = since(t1); t1 = std::chrono::steady_clock::now();
+    // cut + crossfade on the device
+    std::vector<emit_job> jobs(act.size());
+    P.begin.assign(act.size(), 0); P.end.assign(act.size(), 0); P.off.assign(act.size(), 0);
+    int64_t emit_total = 0;
+    for (size_t k = 0; k < act.size(); k++) {
+        stream_state & s = *act[k];
+        const stream_job & j = s.jobs[s.job_head];
+        const int64_t win = (int64_t) j.prefix * spc;                       // window_audio.size()
+        const double spc_actual = (double) win / (double) j.prefix;          // :554-556
+        const int64_t b = (int64_t) std::llround((double) j.commit_begin * spc_actual);
+        const int64_t en = std::min<int64_t>((int64_t) std::llround((double) j.commit_end * spc_actual), win);
+        emit_job & J = jobs[k];
+        J.wave_off = (int64_t) cu[k] * spc; J.begin = b; J.end = std::max(b, en); J.emit_off = emit_total;
+        J.tail = s.d_tail; J.tail_len = s.d_tail_len; J.chunk = s.cfg.chunk_samples; J.xfade = s.cfg.crossfade_samples;
+        P.begin[k] = J.begin; P.end[k] = J.end; P.off[k] = J.emit_off;
+        emit_total += J.end - J.begin;
+        s.decode_calls++; s.decoded_codes += (int64_t) j.prefix;
+    }
+    if (E.emit_cap < emit_total || E.emit_jobs_cap < (int64_t) jobs.size()) {
+        if (E.d_emit) cudaFree(E.d_emit);
+        if (E.d_emit_jobs) cudaFree(E.d_emit_jobs);
+        E.d_emit = E.d_emit_jobs = nullptr;          // a failed allocation below must not leave freed pointers behind
+        const int64_t want_emit = emit_total + emit_total / 4 + 4096, want_jobs = (int64_t) jobs.size() + 64;
+        E.emit_cap = E.emit_jobs_cap = 0;
+        if (cudaMalloc(&E.d_emit, (size_t) want_emit * sizeof(float)) != cudaSuccess ||
+            cudaMalloc(&E.d_emit_jobs, (size_t) want_jobs * sizeof(emit_job)) != cudaSuccess) {
             if (E.d_emit) cudaFree(E.d_emit);
             if (E.d_emit_jobs) cudaFree(E.d_emit_jobs);
-            E.d_emit = E.d_emit_jobs = nullptr;          // a failed allocation below must not leave freed pointers behind
-            const int64_t want_emit = emit_total + emit_total / 4 + 4096, want_jobs = (int64_t) jobs.size() + 64;
-            E.emit_cap = E.emit_jobs_cap = 0;
-            if (cudaMalloc(&E.d_emit, (size_t) want_emit * sizeof(float)) != cudaSuccess ||
-                cudaMalloc(&E.d_emit_jobs, (size_t) want_jobs * sizeof(emit_job)) != cudaSuccess) {
-                if (E.d_emit) cudaFree(E.d_emit);
-                if (E.d_emit_jobs) cudaFree(E.d_emit_jobs);
-                E.d_emit = E.d_emit_jobs = nullptr;
-                return "cudaMalloc failed (emit buffers)";
-            }
-            E.emit_cap = want_emit; E.emit_jobs_cap = want_jobs;
+            E.d_emit = E.d_emit_jobs = nullptr;
+            return "cudaMalloc failed (emit buffers)";
         }
-        bool pooled = true;
-        engine::emit_block * blk = emit_total > 0 ? E.acquire_emit_block(emit_total, &pooled) : nullptr;
-        if (emit_total > 0 && !blk) return "cudaMallocHost failed (emit block)";
-        if (cudaMemcpyAsync(E.d_emit_jobs, jobs.data(), jobs.size() * sizeof(emit_job), cudaMemcpyHostToDevice, E.stream) != cudaSuccess)
-            return "cudaMemcpyAsync failed (emit jobs)";
-        launch_k(stream_emit_kernel, dim3((unsigned) jobs.size()), dim3(256), 0, E.stream, E.d_wave, (float *) E.d_emit, (const emit_job *) E.d_emit_jobs);
-        E.launches++;
-        if (cudaGetLastError() != cudaSuccess) return "stream_emit_kernel launch failed";
-        if (emit_total > 0 &&
-            cudaMemcpyAsync(blk->host, E.d_emit, (size_t) emit_total * sizeof(float), cudaMemcpyDeviceToHost, E.stream) != cudaSuccess)
-            return "cudaMemcpyAsync failed (emit D2H)";
-        ms_emit = since(t1); t1 = std::chrono::steady_clock::now();
-        e = E.sync();
-        if (!e.empty()) return e;
-        ms_wait = since(t1);
-        if (timing) fprintf(stderr, "mio stream round: %zu streams, %zu codes: prep %.2f upload %.2f enqueue %.2f emit-setup %.2f wait %.2f ms\n",
-                            act.size(), codes.size(), ms_prep, ms_upload, ms_run, ms_emit, ms_wait);
-        for (size_t k = 0; k < act.size(); k++) {
-            stream_state & s = *act[k];
-            const emit_job & J = jobs[k];
-            const int64_t n = J.end - J.begin;
-            if (n > 0) {
-                const float * src = blk->host + J.emit_off;
-                s.segs.emplace_back();
-                stream_state::emit_seg & g = s.segs.back();
-                g.n = n;
-                if (pooled) { g.blk = blk; g.p = src; blk->refs++; }       // no second host copy: read straight from the pinned block
-                else { g.own.assign(src, src + n); g.p = g.own.data(); }
-            }
-            s.emitted_samples += n;
-            s.job_head++;
-        }
-        E.stream_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - t_pass0).count();
-        E.stream_passes++;
+        E.emit_cap = want_emit; E.emit_jobs_cap = want_jobs;
     }
+    bool pooled = true;
+    engine::emit_block * blk = emit_total > 0 ? E.acquire_emit_block(emit_total, &pooled) : nullptr;
+    if (emit_total > 0 && !blk) return "cudaMallocHost failed (emit block)";
+    // the job table is copied from a buffer that outlives this function (the copy is asynchronous only for pinned memory,
+    // but the pass state keeps it alive either way)
+    P.jobs_host.assign((const uint8_t *) jobs.data(), (const uint8_t *) jobs.data() + jobs.size() * sizeof(emit_job));
+    if (cudaMemcpyAsync(E.d_emit_jobs, P.jobs_host.data(), P.jobs_host.size(), cudaMemcpyHostToDevice, E.stream) != cudaSuccess)
+        return "cudaMemcpyAsync failed (emit jobs)";
+    launch_k(stream_emit_kernel, dim3((unsigned) jobs.size()), dim3(256), 0, E.stream, E.d_wave, (float *) E.d_emit, (const emit_job *) E.d_emit_jobs);
+    E.launches++;
+    if (cudaGetLastError() != cudaSuccess) return "stream_emit_kernel launch failed";
+    if (emit_total > 0 &&
+        cudaMemcpyAsync(blk->host, E.d_emit, (size_t) emit_total * sizeof(float), cudaMemcpyDeviceToHost, E.stream) != cudaSuccess)
+        return "cudaMemcpyAsync failed (emit D2H)";
+    P.ms_emit = since(t1);
+    P.act.assign(act.begin(), act.end());
+    P.blk = blk; P.pooled = pooled; P.n_codes = (int64_t) codes.size();
+    if (blk) blk->refs++;                             // held by the pass until pass_end has handed out the slices
+    P.active = true;
+    *any = true;
+    return {};
+}
+
+static std::string pass_end(engine & E) {
+    engine::stream_pass & P = E.pass;
+    if (!P.active) return {};
+    static const bool timing = getenv("MIO_STREAM_TIMING") != nullptr;      // per-round host timeline on stderr
+    const auto t1 = std::chrono::steady_clock::now();
+    std::string e = E.sync();
+    P.active = false;
+    engine::emit_block * blk = P.blk;
+    if (blk) blk->refs--;
+    if (!e.empty()) return e;
+    const double ms_wait = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
+    if (timing) fprintf(stderr, "mio stream round: %zu streams, %lld codes: prep %.2f upload %.2f enqueue %.2f emit-setup %.2f wait %.2f ms\n",
+                        P.act.size(), (long long) P.n_codes, P.ms_prep, P.ms_upload, P.ms_run, P.ms_emit, ms_wait);
+    for (size_t k = 0; k < P.act.size(); k++) {
+        stream_state & s = *(stream_state *) P.act[k];
+        const int64_t n = P.end[k] - P.begin[k];
+        if (n > 0) {
+            const float * src = blk->host + P.off[k];
+            s.segs.emplace_back();
+            stream_state::emit_seg & g = s.segs.back();
+            g.n = n;
+            if (P.pooled) { g.blk = blk; g.p = src; blk->refs++; }       // no second host copy: read straight from the pinned block
+            else { g.own.assign(src, src + n); g.p = g.own.data(); }
+        }
+        s.emitted_samples += n;
+        s.job_head++;
+    }
+    E.stream_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - P.t0).count();
+    E.stream_passes++;
+    P.act.clear();
+    return {};
+}
+
+static void mark_done(stream_state ** streams, int n_streams) {
     for (int i = 0; i < n_streams; i++) {
         stream_state * s = streams[i];
         if (s && s->final_queued && s->job_head >= s->jobs.size()) s->done = true;
     }
+}
+
+std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
+    cudaSetDevice(E.device);
+    std::string e = pass_end(E);                      // a round left in flight by streams_step_begin
+    if (!e.empty()) return e;
+    for (;;) {
+        bool any = false;
+        if (!(e = pass_begin(E, streams, n_streams, &any)).empty()) return e;
+        if (!any) break;
+        if (!(e = pass_end(E)).empty()) return e;
+    }
+    mark_done(streams, n_streams);
     return {};
 }
+
+// The asynchronous form: begin enqueues the first pass and returns while the GPU works; end waits for it and runs whatever
+// further passes the streams still need (more than max_voices streams firing at once).  The streams of a pass in flight
+// may be pushed to and read from, not closed.
+std::string streams_step_begin(engine & E, stream_state ** streams, int n_streams) {
+    cudaSetDevice(E.device);
+    bool any = false;
+    return pass_begin(E, streams, n_streams, &any);
+}
+
+std::string streams_step_end(engine & E, stream_state ** streams, int n_streams) {
+    return streams_step(E, streams, n_streams);
+}
+
+// waits for a pass in flight and hands out its samples (before a stream of that pass is closed)
+std::string streams_drain(engine & E) { cudaSetDevice(E.device); return pass_end(E); }
 
 int64_t stream_read(stream_state & s, float * out, int64_t cap, int * is_last) {
     int64_t done = 0;

@@ -25,7 +25,7 @@ EXPORTS = [
     "mio_ctx_set_stream", "mio_voice_load", "mio_print_tensors", "mio_decode_spec", "mio_istft", "mio_decode_wave",
     "mio_decode_wave_batch", "mio_batch_upload", "mio_batch_run", "mio_batch_fetch", "mio_batch_sync",
     "mio_batch_kernel_launches", "mio_batch_wave_device", "mio_stream_default_config", "mio_stream_open",
-    "mio_stream_close", "mio_stream_push_codes", "mio_stream_finish", "mio_streams_step", "mio_stream_read",
+    "mio_stream_close", "mio_stream_push_codes", "mio_stream_finish", "mio_streams_step", "mio_streams_step_begin", "mio_streams_step_end", "mio_stream_read",
     "mio_stream_stats", "mio_debug_read", "mio_last_error", "mio_version", "mio_host_alloc", "mio_host_free",
     "mio_profile_enable", "mio_profile_categories", "mio_profile_name", "mio_profile_read", "mio_batch_h2d_bytes",
     "mio_ctx_stream_seconds", "mio_parse_speech_tokens", "mio_decode_pcm16_batch", "mio_batch_fetch_pcm16", "mio_wav_header", "mio_wav_write_pcm16",
@@ -100,6 +100,8 @@ def lib() -> C.CDLL:
     L.mio_stream_push_codes.argtypes = [vp, i32p, C.c_int]
     L.mio_stream_finish.argtypes = [vp]
     L.mio_streams_step.argtypes = [vp, C.POINTER(vp), C.c_int]
+    L.mio_streams_step_begin.argtypes = [vp, C.POINTER(vp), C.c_int]
+    L.mio_streams_step_end.argtypes = [vp, C.POINTER(vp), C.c_int]
     L.mio_stream_read.argtypes = [vp, f32p, i64, C.POINTER(C.c_int)]
     L.mio_stream_read.restype = i64
     L.mio_stream_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]
@@ -398,6 +400,15 @@ class MioCodec:
     def step_streams(self, streams):
         arr = (C.c_void_p * len(streams))(*[s._h for s in streams])
         _check(lib().mio_streams_step(self._h, arr, len(streams)))
+
+    def step_streams_begin(self, streams):
+        """Enqueue the round and return while the GPU works (mio_streams_step_begin); pair with step_streams_end."""
+        arr = (C.c_void_p * len(streams))(*[s._h for s in streams])
+        _check(lib().mio_streams_step_begin(self._h, arr, len(streams)))
+
+    def step_streams_end(self, streams):
+        arr = (C.c_void_p * len(streams))(*[s._h for s in streams])
+        _check(lib().mio_streams_step_end(self._h, arr, len(streams)))
 
 
 class Stream:

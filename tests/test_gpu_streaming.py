@@ -159,3 +159,51 @@ def test_random_stream_sessions_match_the_policy_port():
     from conftest import ROOT
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "fuzz_streams.py"), "6", "9"], capture_output=True, text=True, timeout=900)
     assert r.returncode == 0 and "STREAM FUZZ PASSED" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_split_rounds_give_the_same_stream(codec):
+    """mio_streams_step_begin / _end with pushes and reads in between (the host works while the GPU decodes) produce the same
+    samples, bit for bit, and the same counters as the synchronous step; a stream of the round in flight can be closed
+    (the library drains the round first)."""
+    from miocodec_b200 import synth
+    from oracle import port
+    N = 230
+    embs = [synth.synth_voice(2), synth.synth_voice(6)]
+    cs = [synth.synth_codes(N, 811), synth.synth_codes(N - 37, 812)]
+    streams = [codec.open_stream(e) for e in embs]
+    got = [[], []]
+    last = [False, False]
+    for k in range(N):
+        for i, s in enumerate(streams):
+            if k < len(cs[i]):
+                s.push(cs[i][k])
+                if k == len(cs[i]) - 1:
+                    s.finish()
+        codec.step_streams_begin(streams)
+        for i, s in enumerate(streams):                 # reads while the round is in flight: earlier rounds only
+            if not last[i]:
+                a, last[i] = s.read(50000)
+                got[i].append(a)
+        codec.step_streams_end(streams)
+    for i, s in enumerate(streams):
+        while not last[i]:
+            a, last[i] = s.read()
+            got[i].append(a)
+        want, st = port.stream_policy(lambda c, e=embs[i]: codec.decode_wave(c, e), cs[i])
+        out = np.concatenate(got[i])
+        mine = s.stats()
+        assert out.shape == want.shape and np.array_equal(out, want)
+        assert mine["decode_calls"] == st["decode_calls"] and mine["decoded_codes"] == st["decoded_codes"]
+    # closing a stream whose round is in flight
+    t = codec.open_stream(embs[0])
+    t.push(cs[0][:60])
+    codec.step_streams_begin([t])
+    t.close()
+    u = codec.open_stream(embs[0])                      # the context is still usable
+    u.push(cs[0][:60]); u.finish()
+    codec.step_streams([u])
+    a, fin = u.read()
+    assert fin and a.size == 60 * 1764
+    u.close()
+    for s in streams:
+        s.close()
