@@ -181,7 +181,7 @@ int  mio_streams_step(mio_ctx * ctx, mio_stream ** streams, int n_streams);
  * crossfade, the copy of the emitted samples into pinned memory) and returns at once; _end waits for it, hands the samples to
  * the streams and runs whatever further passes they still need.  Between the two the caller may push codes to and read from
  * any stream (reads return what earlier rounds emitted) -- e.g. generate the next tokens -- but not close a stream.
- * mio_streams_step == _begin + _end. */
+ * mio_streams_step == _begin + _end.  _begin returns 1 when a round is now in flight, 0 when no stream had work, < 0 on error. */
 int  mio_streams_step_begin(mio_ctx * ctx, mio_stream ** streams, int n_streams);
 int  mio_streams_step_end(mio_ctx * ctx, mio_stream ** streams, int n_streams);
 /* pop emitted audio (already crossfaded, in emission order). Returns samples copied. *is_last is set when

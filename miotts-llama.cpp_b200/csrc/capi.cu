@@ -476,8 +476,9 @@ int mio_streams_step_begin(mio_ctx * c, mio_stream ** streams, int n) {
         if (!c || (!streams && n > 0) || n < 0) return fail(MIO_ERR_ARG, "bad argument");
         std::vector<stream_state *> v(n);
         for (int i = 0; i < n; i++) v[i] = streams[i] ? streams[i]->S : nullptr;
-        TRY(streams_step_begin(c->E, v.data(), n));
-        return MIO_OK;
+        bool in_flight = false;
+        TRY(streams_step_begin(c->E, v.data(), n, &in_flight));
+        return in_flight ? 1 : 0;
     });
 }
 int mio_streams_step_end(mio_ctx * c, mio_stream ** streams, int n) {

@@ -269,10 +269,12 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams) {
 // The asynchronous form: begin enqueues the first pass and returns while the GPU works; end waits for it and runs whatever
 // further passes the streams still need (more than max_voices streams firing at once).  The streams of a pass in flight
 // may be pushed to and read from, not closed.
-std::string streams_step_begin(engine & E, stream_state ** streams, int n_streams) {
+std::string streams_step_begin(engine & E, stream_state ** streams, int n_streams, bool * in_flight) {
     cudaSetDevice(E.device);
     bool any = false;
-    return pass_begin(E, streams, n_streams, &any);
+    std::string e = pass_begin(E, streams, n_streams, &any);
+    if (in_flight) *in_flight = any;
+    return e;
 }
 
 std::string streams_step_end(engine & E, stream_state ** streams, int n_streams) {

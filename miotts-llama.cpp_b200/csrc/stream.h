@@ -46,7 +46,7 @@ std::string stream_open(engine & E, const float * emb, const mio_stream_config *
 std::string stream_push(stream_state & s, const int32_t * codes, int n);
 std::string stream_finish(stream_state & s);
 std::string streams_step(engine & E, stream_state ** streams, int n_streams);
-std::string streams_step_begin(engine & E, stream_state ** streams, int n_streams);
+std::string streams_step_begin(engine & E, stream_state ** streams, int n_streams, bool * in_flight = nullptr);
 std::string streams_step_end(engine & E, stream_state ** streams, int n_streams);
 std::string streams_drain(engine & E);
 int64_t stream_read(stream_state & s, float * out, int64_t cap, int * is_last);

@@ -404,7 +404,7 @@ class MioCodec:
     def step_streams_begin(self, streams):
         """Enqueue the round and return while the GPU works (mio_streams_step_begin); pair with step_streams_end."""
         arr = (C.c_void_p * len(streams))(*[s._h for s in streams])
-        _check(lib().mio_streams_step_begin(self._h, arr, len(streams)))
+        return _check(lib().mio_streams_step_begin(self._h, arr, len(streams))) == 1      # True: a round is in flight
 
     def step_streams_end(self, streams):
         arr = (C.c_void_p * len(streams))(*[s._h for s in streams])

@@ -8,6 +8,7 @@ from miocodec_b200 import binding, synth
 gguf, _ = synth.ensure_assets()
 codec = binding.MioCodec(gguf, 0)
 S, N = 1024, 700
+SPLIT = os.environ.get('C4_SPLIT', '0') == '1'
 
 
 def session(S, N):
@@ -22,7 +23,10 @@ def session(S, N):
             if k + 20 >= N:
                 st.finish()
         t1 = time.perf_counter()
-        codec.step_streams(streams)
+        if SPLIT:
+            codec.step_streams_begin(streams)
+        else:
+            codec.step_streams(streams)
         t2 = time.perf_counter()
         for st in streams:
             while True:
@@ -31,7 +35,19 @@ def session(S, N):
                 if a.size < (1 << 18):
                     break
         t3 = time.perf_counter()
-        t_push += t1 - t0; t_step += t2 - t1; t_read += t3 - t2
+        if SPLIT:
+            codec.step_streams_end(streams)
+        t4 = time.perf_counter()
+        t_push += t1 - t0; t_step += (t2 - t1) + (t4 - t3); t_read += t3 - t2
+    if SPLIT:
+        t3 = time.perf_counter()
+        for st in streams:
+            while True:
+                a, _ = st.read(1 << 18)
+                emitted += a.size
+                if a.size < (1 << 18):
+                    break
+        t_read += time.perf_counter() - t3
     for st in streams:
         st.close()
     return emitted, t_push, t_step, t_read
