@@ -712,34 +712,6 @@ def main():
 
     # ---- the other BASELINE configurations, as blocks of the same line (default run only)
     extra = {}
-    if args.workload == "c3" and not args.no_extra and world == 1:
-        # a serving process keeps the GPU busy by overlapping calls: TWO contexts on this GPU driven by two host threads,
-        # so the upload / tail chunk / D2H of one batch run under the compute of the other (same call, same buffers)
-        import threading
-        codec2 = binding.MioCodec(gguf, local, gemm=args.gemm, max_chunk_codes=args.chunk)
-        h_codes2 = binding.pinned_empty(len(wl["codes"]), np.int32); h_codes2[:] = wl["codes"]
-        h_wave2 = binding.pinned_empty(total_codes * codec.samples_per_token, np.float32)
-        for _ in range(2):
-            codec2.decode_wave_batch(h_codes2, wl["cu"], wl["voice_table"], wl["voice_ids"], out=h_wave2)
-        per = max(1, args.steps // 2 + args.steps % 2)
-
-        def _loop(c, hc, hw):
-            for _ in range(per):
-                c.decode_wave_batch(hc, wl["cu"], wl["voice_table"], wl["voice_ids"], out=hw)
-        th = [threading.Thread(target=_loop, args=a) for a in ((codec, h_codes, h_wave), (codec2, h_codes2, h_wave2))]
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for t in th:
-            t.start()
-        for t in th:
-            t.join()
-        torch.cuda.synchronize()
-        dt2 = time.perf_counter() - t0
-        extra["e2e_two_contexts"] = {"value": audio_s * 2 * per / dt2, "unit": UNIT, "ms_per_batch": dt2 / (2 * per) * 1e3, "batches": 2 * per,
-                                     "how": "two contexts on one GPU, one host thread each, mio_decode_wave_batch with pinned buffers"}
-        assert np.isfinite(h_wave2[:: max(1, len(h_wave2) // 4096)]).all()
-        codec2.close()
-        del h_wave2, h_codes2
     if args.workload == "c3" and not args.no_extra:
         del h_wave
         extra["c5"] = c5_block(codec, stream, rank, world, local, barrier)
