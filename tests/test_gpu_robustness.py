@@ -156,3 +156,34 @@ def test_reserve_presizes_without_changing_results(assets, codec):
         outs.append(np.concatenate(got))
     assert np.array_equal(outs[0], outs[1])
     c.close()
+
+
+def test_two_contexts_from_two_threads(assets, codec):
+    """Different contexts are independent: two host threads, each hammering its own context on the same GPU with a different
+    batch, get the same bits as the shared context does alone."""
+    import threading
+    from miocodec_b200 import binding, synth
+    jobs = []
+    for seed, lens in ((71, [40, 3, 111]), (72, [64, 64])):
+        cu = np.cumsum([0] + lens).astype(np.int32)
+        codes = synth.synth_codes(int(cu[-1]), seed)
+        vt = np.stack([synth.synth_voice(seed % 5), synth.synth_voice(1)]).astype(np.float32)
+        vids = (np.arange(len(lens)) % 2).astype(np.int32)
+        jobs.append((codes, cu, vt, vids, codec.decode_wave_batch(codes, cu, vt, vids).copy()))
+    ctxs = [binding.MioCodec(assets[0], 0) for _ in jobs]
+    bad = []
+
+    def work(c, job):
+        codes, cu, vt, vids, want = job
+        for _ in range(12):
+            if not np.array_equal(c.decode_wave_batch(codes, cu, vt, vids), want):
+                bad.append(1)
+
+    th = [threading.Thread(target=work, args=(c, j)) for c, j in zip(ctxs, jobs)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for c in ctxs:
+        c.close()
+    assert not bad
