@@ -155,6 +155,30 @@ int  mio_wav_header(int sample_rate, int64_t n_samples, uint8_t out44[44]);
  * conversion above (src/wav-writer.cpp:24-45). */
 int  mio_wav_write_pcm16(const char * path, const int16_t * pcm, int64_t n_samples, int sample_rate);
 
+/* ---- peak normalisation without any allocation.  This entry point has no counterpart in the reference.
+ * It exists for callers that must not allocate device memory while they run: a plug-in inside a serving process whose pool
+ * took all of HBM at start-up (our cudaMalloc would fail or spend another tenant's budget), or a real-time audio thread
+ * that may not wait on the driver's allocator lock.  Everything else in this header works on a context whose workspace
+ * grows by cudaMalloc; this call takes no context and calls neither cudaMalloc / cudaFree nor any routine that does.
+ *
+ * Applies the per-utterance gain 0.95 / max|s| (skipped when the peak is <= 1e-8; src/test-to-speech.cpp:289-300 does this
+ * on the host) to a waveform that is already in device memory -- exactly what peak_normalize != 0 does inside
+ * mio_decode_wave_batch, bit for bit.  ALL pointers are DEVICE memory on `device`, supplied by the caller:
+ *   wave_in_device / wave_out_device : float samples; the two may be the same buffer (in place) but must not partly overlap
+ *   sample_offsets_device            : int64[n_utts + 1], utterance u owns samples [offsets[u], offsets[u+1])
+ *                                      (= samples_per_token * cu_seqlens for the output of mio_batch_run)
+ *   cuda_stream                      : cudaStream_t as void* (NULL = the default stream); the call only enqueues work
+ * The one float of scratch per utterance lives in a fixed array inside the library image, so n_utts may not exceed
+ * MIO_NOALLOC_MAX_UTTS (more is refused with MIO_ERR_ARG: split the batch).  Each GPU the library is used on holds those
+ * 16 KiB until the process exits.  Every call on a GPU uses the SAME array: two calls whose kernels can overlap on the GPU
+ * (different streams, different threads) corrupt each other's maxima -- order them on one stream or with events.  The
+ * array keeps the last call's maxima; each call clears the slots it needs itself.  The first call on each device looks up
+ * the array's device address (cudaGetSymbolAddress, which also loads this library's kernels onto that GPU): make that first
+ * call during start-up, before any stream capture begins.  Leaves `device` current, like the other calls of this library. */
+#define MIO_NOALLOC_MAX_UTTS 4096
+int  mio_peak_normalize_device_noalloc(int device, const float * wave_in_device, float * wave_out_device,
+                                       const int64_t * sample_offsets_device, int n_utts, void * cuda_stream);
+
 /* ---- streaming policy on top of the decoder: replaces the LLM-branch of
  * TestToSpeech::synthesize_stream_profiled (src/test-to-speech.cpp:430-625): commit holdback (32 codes),
  * min commit step (24), check cadence (every 20 pushed codes), full-prefix re-decode, llround() sample

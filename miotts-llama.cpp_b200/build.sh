@@ -9,7 +9,7 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 mkdir -p "$OBJ"
 FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -O2 -Xptxas -v)
 pids=()
-for f in gemm_simt gemm3 attention elementwise istft engine stream capi; do
+for f in gemm_simt gemm3 attention elementwise istft engine stream capi noalloc; do
   if [ ! -f "$OBJ/$f.o" ] || [ "$SRC/$f.cu" -nt "$OBJ/$f.o" ] || [ -n "$(find "$SRC" -name '*.h' -newer "$OBJ/$f.o" -o -name '*.cuh' -newer "$OBJ/$f.o" | head -1)" ] || [ "$HERE/../include/miocodec_b200.h" -nt "$OBJ/$f.o" ]; then
     ( "$NVCC" "${FLAGS[@]}" -c "$SRC/$f.cu" -o "$OBJ/$f.o" > "$OBJ/$f.log" 2>&1 || { cat "$OBJ/$f.log"; exit 1; } ) &
     pids+=($!)
@@ -17,7 +17,7 @@ for f in gemm_simt gemm3 attention elementwise istft engine stream capi; do
 done
 g++ -O2 -std=c++17 -fPIC -c "$SRC/gguf_reader.cpp" -o "$OBJ/gguf_reader.o"
 for p in "${pids[@]}"; do wait "$p"; done
-"$NVCC" -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT/libmiocodec_b200.so" "$OBJ"/gemm_simt.o "$OBJ"/gemm3.o "$OBJ"/attention.o "$OBJ"/elementwise.o "$OBJ"/istft.o "$OBJ"/engine.o "$OBJ"/stream.o "$OBJ"/capi.o "$OBJ"/gguf_reader.o -cudart static
+"$NVCC" -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT/libmiocodec_b200.so" "$OBJ"/gemm_simt.o "$OBJ"/gemm3.o "$OBJ"/attention.o "$OBJ"/elementwise.o "$OBJ"/istft.o "$OBJ"/engine.o "$OBJ"/stream.o "$OBJ"/capi.o "$OBJ"/noalloc.o "$OBJ"/gguf_reader.o -cudart static
 echo "built $OUT/libmiocodec_b200.so"
 # C++ drop-in layer (reference-named entry points on top of the C ABI) + its test program
 g++ -O2 -std=c++17 -fPIC -shared -I"$HERE/shim" "$HERE/shim/miocodec_shim.cpp" "$HERE/shim/batch_tts.cpp" -o "$OUT/libmiocodec_shim.so" \

@@ -12,6 +12,10 @@
 
 using namespace mio;
 
+namespace mio {   // csrc/noalloc.cu
+std::string noalloc_peak_normalize(int device, const float * in, float * out, const int64_t * offs, int n_utts, cudaStream_t st);
+}
+
 struct mio_ctx { engine E; };
 struct mio_stream { stream_state * S = nullptr; };
 
@@ -397,6 +401,15 @@ int64_t mio_parse_speech_tokens(const char * text, int64_t text_len, int32_t * o
         }
     }
     return n;
+}
+
+// the one entry point that allocates nothing (csrc/noalloc.cu: scratch in a file-scope __device__ array)
+int mio_peak_normalize_device_noalloc(int device, const float * wave_in, float * wave_out, const int64_t * sample_offsets, int n_utts,
+                                      void * cuda_stream) {
+    return guarded([&]() -> int {
+        TRY(noalloc_peak_normalize(device, wave_in, wave_out, sample_offsets, n_utts, (cudaStream_t) cuda_stream));
+        return MIO_OK;
+    });
 }
 
 int mio_wav_header(int sample_rate, int64_t n_samples, uint8_t * h) {

@@ -29,7 +29,7 @@ EXPORTS = [
     "mio_stream_stats", "mio_debug_read", "mio_last_error", "mio_version", "mio_host_alloc", "mio_host_free",
     "mio_profile_enable", "mio_profile_categories", "mio_profile_name", "mio_profile_read", "mio_batch_h2d_bytes",
     "mio_ctx_stream_seconds", "mio_parse_speech_tokens", "mio_decode_pcm16_batch", "mio_batch_fetch_pcm16", "mio_wav_header", "mio_wav_write_pcm16",
-    "mio_debug_write", "mio_debug_clear", "mio_debug_gemm",
+    "mio_debug_write", "mio_debug_clear", "mio_debug_gemm", "mio_peak_normalize_device_noalloc",
 ]
 
 
@@ -128,8 +128,18 @@ def lib() -> C.CDLL:
     L.mio_debug_write.argtypes = [vp, C.c_char_p, f32p, i64]
     L.mio_debug_clear.argtypes = [vp]
     L.mio_debug_gemm.argtypes = [vp, C.c_int, C.c_int, C.c_int, f32p, f32p, C.c_int, f32p]
+    L.mio_peak_normalize_device_noalloc.argtypes = [C.c_int, vp, vp, vp, C.c_int, vp]
     _lib = L
     return L
+
+
+def peak_normalize_device_noalloc(device: int, wave_in_ptr: int, wave_out_ptr: int, offsets_ptr: int, n_utts: int,
+                                  cuda_stream_ptr: int = 0) -> None:
+    """mio_peak_normalize_device_noalloc: per-utterance 0.95/max|s| on a waveform already in device memory, for callers that
+    may not allocate (no context, no cudaMalloc; at most MIO_NOALLOC_MAX_UTTS = 4096 utterances; calls on one GPU must not
+    overlap).  All three pointers are device addresses; offsets is int64[n_utts + 1] in samples.  Only enqueues work."""
+    _check(lib().mio_peak_normalize_device_noalloc(device, C.c_void_p(wave_in_ptr), C.c_void_p(wave_out_ptr),
+                                                   C.c_void_p(offsets_ptr), n_utts, C.c_void_p(cuda_stream_ptr)))
 
 
 def device_alloc(device: int, nbytes: int) -> int:
