@@ -258,7 +258,13 @@ class MioCodec:
         _check(lib().mio_ctx_reserve(self._h, max_batch_codes, max_utts, max_emit_samples))
 
     def set_stream(self, cuda_stream_ptr: int):
+        """Run this context's kernels on an existing CUDA stream (e.g. torch.cuda.current_stream().cuda_stream).  Until this
+        is called the context works on a private non-blocking stream, which NOTHING else is ordered against."""
         _check(lib().mio_ctx_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
+        self.stream_ptr = int(cuda_stream_ptr or 0)
+
+    #: the stream given to set_stream, or None while the context still runs on its private stream
+    stream_ptr = None
 
     # ---- reference-shaped calls ------------------------------------------------------------
     def decode(self, codes, global_emb) -> np.ndarray:
@@ -315,14 +321,17 @@ class MioCodec:
         return int(lib().mio_batch_wave_device(self._h) or 0), self._total
 
     def pcm16_device(self) -> tuple[int, int]:
-        """(device pointer, samples) of the PCM16 image of the resident waveform, converted on the context's stream."""
+        """(device pointer, samples) of the PCM16 image of the resident waveform, converted ASYNCHRONOUSLY on the context's
+        stream: a consumer on another stream (torch ops, a torch.distributed collective) must be ordered behind it -- make
+        the streams the same (set_stream), or batch_sync() first; sharding.order_after_codec does whichever is needed."""
         p = lib().mio_batch_pcm16_device(self._h)
         if not p:
             raise MioError(-3, lib().mio_last_error().decode("utf-8", "replace"))
         return int(p), self._total
 
     def pcm16_to_device(self, dst_ptr: int, cap: int) -> int:
-        """PCM16 of the resident waveform stored into device memory at dst_ptr (may be a peer GPU's); returns the samples."""
+        """PCM16 of the resident waveform stored into device memory at dst_ptr (may be a peer GPU's); returns the samples.
+        Asynchronous on the context's stream, like pcm16_device: see the ordering note there."""
         _check(lib().mio_batch_pcm16_to_device(self._h, C.c_void_p(dst_ptr), cap))
         return self._total
 

@@ -61,6 +61,19 @@ def device_tensor(ptr: int, n: int, dtype: str = "float32", device: int = 0):
     return torch.as_tensor(_DevicePointer(ptr, n, typestr), device=torch.device("cuda", device))
 
 
+def order_after_codec(codec, consumer_stream_ptr: int) -> bool:
+    """Make work enqueued on the CUDA stream `consumer_stream_ptr` (torch's current stream when a collective is about to be
+    issued) run after everything the codec has enqueued so far.  mio_batch_pcm16_device / mio_batch_pcm16_to_device only
+    ENQUEUE the conversion on the context's stream, and torch.distributed orders a collective against torch's current stream
+    alone: if the two differ -- a codec left on its private stream, or set to some other stream -- the collective could read or
+    announce a buffer whose stores have not landed.  Same stream: stream order already does it, nothing happens.  Otherwise
+    the host waits for the codec (batch_sync).  Returns True when it had to wait."""
+    if getattr(codec, "stream_ptr", None) is not None and int(codec.stream_ptr) == int(consumer_stream_ptr or 0):
+        return False
+    codec.batch_sync()
+    return True
+
+
 def _wire(t):
     """Bytes on the wire: NCCL's torch binding has no int16, and a gather only moves bytes."""
     import torch
@@ -71,7 +84,9 @@ def gather_to_rank0(local, counts: list[int], host_out=None, group=None):
     """The one exchange step of the sharded path: the variable-length shards of the waveform go to rank 0,
     SIZE-EXACT (every rank knows every count, so nothing is padded to the largest shard and no size exchange is needed).
 
-    local:    this rank's shard: a torch tensor (CUDA for the nccl backend -- e.g. device_tensor(*codec.pcm16_device()) --,
+    local:    this rank's shard: a torch tensor (CUDA for the nccl backend -- e.g. device_tensor(*codec.pcm16_device()),
+              which is filled asynchronously on the codec's stream: call order_after_codec(codec,
+              torch.cuda.current_stream().cuda_stream) before this function unless the codec runs on torch's stream --,
               CPU for gloo) holding counts[rank] elements.
     host_out: rank 0 only, optional: a host tensor (pinned for full-speed copies) of sum(counts) elements; shard r is
               copied device->host on a second stream while shard r+1 is still arriving over NVLink.
@@ -240,6 +255,10 @@ class P2PGather:
         n = self.count[self.rank][g]
         if n > 0:
             codec.pcm16_to_device(self.ptr + 2 * self.off[self.rank][g], n)
+            # the stores above are only enqueued, on the CODEC's stream; the rendezvous below is ordered against torch's
+            # current stream: free when the two are one (codec.set_stream(torch.cuda.current_stream().cuda_stream)), a host
+            # wait otherwise
+            order_after_codec(codec, self.torch.cuda.current_stream().cuda_stream)
         self.dist.all_reduce(self.flag, group=self.group)      # every rank's stores of group g precede this on its stream
         if self.rank == 0:
             lo, hi = self.group_range[g]

@@ -67,3 +67,26 @@ def test_two_rank_sharding_and_gather():
     assert all(ok for _, ok, _ in res)
     got = sorted(i for _, _, idx in res for i in idx)
     assert got == list(range(len(lens)))
+
+
+def test_collectives_are_ordered_behind_the_codec_stream():
+    """sharding.order_after_codec: the PCM16 conversion is only enqueued on the codec's stream, a torch.distributed
+    collective is ordered against torch's current stream -- when the two differ (private codec stream, or another stream)
+    the host must wait for the codec first; when they are the same stream nothing is needed."""
+    from miocodec_b200 import sharding
+
+    class FakeCodec:
+        def __init__(self, stream_ptr):
+            self.stream_ptr, self.syncs = stream_ptr, 0
+
+        def batch_sync(self):
+            self.syncs += 1
+
+    private = FakeCodec(None)                         # never given a stream: runs on its own non-blocking stream
+    assert sharding.order_after_codec(private, 0) and private.syncs == 1
+    other = FakeCodec(0x7000)
+    assert sharding.order_after_codec(other, 0x9000) and other.syncs == 1
+    same = FakeCodec(0x7000)
+    assert not sharding.order_after_codec(same, 0x7000) and same.syncs == 0
+    default = FakeCodec(0)                            # set_stream(0): the legacy default stream, which is torch's default too
+    assert not sharding.order_after_codec(default, 0) and default.syncs == 0
