@@ -37,6 +37,9 @@ typedef struct mio_stream mio_stream;
  * to HBM once (pre-split for the tensor-core kernels) and builds the ISTFT tables (istft_cache,
  * src/istft.cpp:7-32).  `device` is a CUDA ordinal. */
 int  mio_ctx_create(const char * gguf_path, int device, mio_ctx ** out_ctx);
+/* Waits for a streaming round still in flight.  Streams of this context that are still open are detached, not destroyed:
+ * they keep the samples they have not handed out yet (mio_stream_read, mio_stream_stats and mio_stream_close keep working)
+ * but can no longer be stepped.  Closing the streams first is the tidy order; the other order is safe. */
 void mio_ctx_destroy(mio_ctx * ctx);
 /* A context that can only run mio_istft: replaces constructing an istft_cache (src/istft.h:6-30,
  * src/istft.cpp:7-32) when no codec is loaded — the reference's istft() is a free function that needs no

@@ -99,7 +99,9 @@ int mio_istft_ctx_create(int device, mio_ctx ** out_ctx) {
 }
 
 void mio_ctx_destroy(mio_ctx * ctx) {
-    if (ctx && ctx->E.pass.active) (void) streams_drain(ctx->E);
+    if (!ctx) return;
+    if (ctx->E.pass.active) (void) streams_drain(ctx->E);
+    streams_detach_all(ctx->E);      // streams that outlive their context keep their unread samples and stay closable
     delete ctx;
 }
 

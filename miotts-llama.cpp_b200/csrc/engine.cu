@@ -1371,6 +1371,14 @@ std::string engine::reserve(int64_t total_codes, int n_utts, int64_t emit_sample
         }
         bool pooled = true;
         if (!acquire_emit_block(emit_samples, &pooled)) return "cudaMallocHost failed (emit block)";
+        // the job table of a round: one entry per firing stream, at most max_voices streams per pass
+        const int64_t want_jobs = (int64_t) std::max(max_voices, n_utts) + 64;
+        if (emit_jobs_cap < want_jobs) {
+            if (d_emit_jobs) cudaFree(d_emit_jobs);
+            d_emit_jobs = nullptr; emit_jobs_cap = 0;
+            if (cudaMalloc(&d_emit_jobs, (size_t) want_jobs * EMIT_JOB_BYTES) != cudaSuccess) { d_emit_jobs = nullptr; return "cudaMalloc failed (emit job table)"; }
+            emit_jobs_cap = want_jobs;
+        }
     }
     return {};
 }

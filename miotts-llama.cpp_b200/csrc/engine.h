@@ -105,7 +105,8 @@ struct engine {
     double stream_seconds = 0.0; int64_t stream_passes = 0;   // wall time / device passes inside streams_step
     // streaming emit buffers (stream.cu)
     void * d_emit = nullptr; void * d_emit_jobs = nullptr;
-    int64_t emit_cap = 0, emit_jobs_cap = 0;
+    int64_t emit_cap = 0, emit_jobs_cap = 0;         // samples / job-table entries; each grows on its own and never shrinks
+    static constexpr size_t EMIT_JOB_BYTES = 64;     // allocation size of one job-table entry (>= sizeof(emit_job), stream.cu)
     // Pinned host blocks the emitted samples of a streaming round land in (one D2H copy per round).  The streams' queues
     // REFERENCE slices of the block (refs counts unread slices) instead of copying them again; a block returns to the pool
     // when its last slice has been read.  At most EMIT_POOL_MAX blocks are kept referenced: beyond that a round's samples
@@ -114,11 +115,15 @@ struct engine {
     static constexpr int EMIT_POOL_MAX = 8;
     std::vector<emit_block *> emit_pool;
     emit_block * acquire_emit_block(int64_t samples, bool * pooled);
+    // every stream_state opened on this context and not yet closed (stream.cu): mio_ctx_destroy detaches them so that a
+    // stream closed or read AFTER its context never touches freed engine state
+    std::vector<void *> open_streams;
     // a streaming pass in flight between streams_step_begin and streams_step_end (stream.cu)
     struct stream_pass {
         bool active = false, pooled = true;
         std::vector<void *> act;                      // stream_state * of the pass
         std::vector<int64_t> begin, end, off;         // cut range and offset in the emit block per stream
+        std::vector<int64_t> prefix;                  // codes decoded per stream (booked into its counters when the pass ends well)
         std::vector<uint8_t> jobs_host;               // the emit job table, alive until the pass ends
         emit_block * blk = nullptr;
         int64_t n_codes = 0;

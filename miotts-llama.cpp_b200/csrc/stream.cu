@@ -65,7 +65,12 @@ void stream_default_config(const engine & E, mio_stream_config * cfg) {
 }
 
 stream_state::~stream_state() {
-    for (emit_seg & g : segs) if (g.blk) g.blk->refs--;
+    // eng == nullptr: the context went first (streams_detach_all) and the segments already own their samples
+    for (emit_seg & g : segs) if (g.blk && eng) g.blk->refs--;
+    if (eng) {
+        auto & v = eng->open_streams;
+        v.erase(std::remove(v.begin(), v.end(), (void *) this), v.end());
+    }
     if (d_tail) cudaFree(d_tail);
     if (d_tail_len) cudaFree(d_tail_len);
 }
@@ -85,8 +90,28 @@ std::string stream_open(engine & E, const float * emb, const mio_stream_config *
     cudaSetDevice(E.device);
     if (cudaMalloc(&s->d_tail, MIO_TAIL_CAP * sizeof(float)) != cudaSuccess || cudaMalloc(&s->d_tail_len, sizeof(int)) != cudaSuccess ||
         cudaMemset(s->d_tail_len, 0, sizeof(int)) != cudaSuccess) { delete s; return "cudaMalloc failed (stream tail)"; }
+    E.open_streams.push_back(s);
     *out = s;
     return {};
+}
+
+// mio_ctx_destroy with streams still open (e.g. a Python caller closing the codec before its Stream objects are collected):
+// the engine's pinned emit blocks are about to be freed, so every unread slice becomes the stream's own copy and the
+// stream forgets the engine.  Such a stream can still be read, queried and closed; stepping it needs a context and fails
+// in the caller's hands, not here.
+void streams_detach_all(engine & E) {
+    for (void * v : E.open_streams) {
+        stream_state & s = *(stream_state *) v;
+        for (stream_state::emit_seg & g : s.segs) {
+            if (!g.blk) continue;
+            g.own.assign(g.p, g.p + g.n);
+            g.p = g.own.data();
+            g.blk->refs--;
+            g.blk = nullptr;
+        }
+        s.eng = nullptr;
+    }
+    E.open_streams.clear();
 }
 
 // maybe_emit(is_final) evaluated with the prefix length `n` (src/test-to-speech.cpp:507-571)
@@ -104,6 +129,7 @@ static void maybe_emit(stream_state & s, size_t n, bool is_final) {
 }
 
 std::string stream_push(stream_state & s, const int32_t * codes, int n) {
+    if (s.failed) return "stream failed in an earlier round (close it)";
     if (s.finished) return "stream already finished";
     for (int i = 0; i < n; i++) {
         s.codes.push_back(codes[i]);
@@ -155,10 +181,13 @@ static std::string pass_begin(engine & E, stream_state ** streams, int n_streams
     P.ms_upload = since(t1); t1 = std::chrono::steady_clock::now();
     e = E.run(false);      // streaming never peak-normalises (decode_codes_to_audio(..., false), :546)
     if (!e.empty()) return e;
+    // from here on GPU work is queued: an error below waits for it before returning, so that the caller is never handed an
+    // error with kernels still running on buffers it may free next; the streams' counters are booked in pass_end only
+    auto bail = [&](const char * msg) { (void) E.sync(); return std::string(msg); };
     P.ms_run = since(t1); t1 = std::chrono::steady_clock::now();
     // cut + crossfade on the device
     std::vector<emit_job> jobs(act.size());
-    P.begin.assign(act.size(), 0); P.end.assign(act.size(), 0); P.off.assign(act.size(), 0);
+    P.begin.assign(act.size(), 0); P.end.assign(act.size(), 0); P.off.assign(act.size(), 0); P.prefix.assign(act.size(), 0);
     int64_t emit_total = 0;
     for (size_t k = 0; k < act.size(); k++) {
         stream_state & s = *act[k];
@@ -172,37 +201,38 @@ static std::string pass_begin(engine & E, stream_state ** streams, int n_streams
         J.tail = s.d_tail; J.tail_len = s.d_tail_len; J.chunk = s.cfg.chunk_samples; J.xfade = s.cfg.crossfade_samples;
         P.begin[k] = J.begin; P.end[k] = J.end; P.off[k] = J.emit_off;
         emit_total += J.end - J.begin;
-        s.decode_calls++; s.decoded_codes += (int64_t) j.prefix;
+        P.prefix[k] = (int64_t) j.prefix;
     }
-    if (E.emit_cap < emit_total || E.emit_jobs_cap < (int64_t) jobs.size()) {
+    // the two buffers grow independently and never shrink (a reservation made by mio_ctx_reserve survives every round)
+    static_assert(sizeof(emit_job) <= engine::EMIT_JOB_BYTES, "engine::reserve sizes the job table with EMIT_JOB_BYTES per entry");
+    if (E.emit_cap < emit_total) {
         if (E.d_emit) cudaFree(E.d_emit);
+        E.d_emit = nullptr; E.emit_cap = 0;          // a failed allocation below must not leave a freed pointer behind
+        const int64_t want_emit = emit_total + emit_total / 4 + 4096;
+        if (cudaMalloc(&E.d_emit, (size_t) want_emit * sizeof(float)) != cudaSuccess) { E.d_emit = nullptr; return bail("cudaMalloc failed (emit buffer)"); }
+        E.emit_cap = want_emit;
+    }
+    if (E.emit_jobs_cap < (int64_t) jobs.size()) {
         if (E.d_emit_jobs) cudaFree(E.d_emit_jobs);
-        E.d_emit = E.d_emit_jobs = nullptr;          // a failed allocation below must not leave freed pointers behind
-        const int64_t want_emit = emit_total + emit_total / 4 + 4096, want_jobs = (int64_t) jobs.size() + 64;
-        E.emit_cap = E.emit_jobs_cap = 0;
-        if (cudaMalloc(&E.d_emit, (size_t) want_emit * sizeof(float)) != cudaSuccess ||
-            cudaMalloc(&E.d_emit_jobs, (size_t) want_jobs * sizeof(emit_job)) != cudaSuccess) {
-            if (E.d_emit) cudaFree(E.d_emit);
-            if (E.d_emit_jobs) cudaFree(E.d_emit_jobs);
-            E.d_emit = E.d_emit_jobs = nullptr;
-            return "cudaMalloc failed (emit buffers)";
-        }
-        E.emit_cap = want_emit; E.emit_jobs_cap = want_jobs;
+        E.d_emit_jobs = nullptr; E.emit_jobs_cap = 0;
+        const int64_t want_jobs = (int64_t) jobs.size() + 64;
+        if (cudaMalloc(&E.d_emit_jobs, (size_t) want_jobs * engine::EMIT_JOB_BYTES) != cudaSuccess) { E.d_emit_jobs = nullptr; return bail("cudaMalloc failed (emit job table)"); }
+        E.emit_jobs_cap = want_jobs;
     }
     bool pooled = true;
     engine::emit_block * blk = emit_total > 0 ? E.acquire_emit_block(emit_total, &pooled) : nullptr;
-    if (emit_total > 0 && !blk) return "cudaMallocHost failed (emit block)";
+    if (emit_total > 0 && !blk) return bail("cudaMallocHost failed (emit block)");
     // the job table is copied from a buffer that outlives this function (the copy is asynchronous only for pinned memory,
     // but the pass state keeps it alive either way)
     P.jobs_host.assign((const uint8_t *) jobs.data(), (const uint8_t *) jobs.data() + jobs.size() * sizeof(emit_job));
     if (cudaMemcpyAsync(E.d_emit_jobs, P.jobs_host.data(), P.jobs_host.size(), cudaMemcpyHostToDevice, E.stream) != cudaSuccess)
-        return "cudaMemcpyAsync failed (emit jobs)";
+        return bail("cudaMemcpyAsync failed (emit jobs)");
     launch_k(stream_emit_kernel, dim3((unsigned) jobs.size()), dim3(256), 0, E.stream, E.d_wave, (float *) E.d_emit, (const emit_job *) E.d_emit_jobs);
     E.launches++;
-    if (cudaGetLastError() != cudaSuccess) return "stream_emit_kernel launch failed";
+    if (cudaGetLastError() != cudaSuccess) return bail("stream_emit_kernel launch failed");
     if (emit_total > 0 &&
         cudaMemcpyAsync(blk->host, E.d_emit, (size_t) emit_total * sizeof(float), cudaMemcpyDeviceToHost, E.stream) != cudaSuccess)
-        return "cudaMemcpyAsync failed (emit D2H)";
+        return bail("cudaMemcpyAsync failed (emit D2H)");
     P.ms_emit = since(t1);
     P.act.assign(act.begin(), act.end());
     P.blk = blk; P.pooled = pooled; P.n_codes = (int64_t) codes.size();
@@ -221,7 +251,17 @@ static std::string pass_end(engine & E) {
     P.active = false;
     engine::emit_block * blk = P.blk;
     if (blk) blk->refs--;
-    if (!e.empty()) return e;
+    if (!e.empty()) {
+        // the emit kernel may or may not have rewritten these streams' device tails: a retry of the same job would crossfade
+        // against an undefined tail, so the streams of the pass end here (readable, closable, no longer decodable)
+        for (void * v : P.act) {
+            stream_state & s = *(stream_state *) v;
+            s.failed = true; s.done = true; s.final_queued = true;
+            s.job_head = s.jobs.size();
+        }
+        P.act.clear();
+        return e;
+    }
     const double ms_wait = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
     if (timing) fprintf(stderr, "mio stream round: %zu streams, %lld codes: prep %.2f upload %.2f enqueue %.2f emit-setup %.2f wait %.2f ms\n",
                         P.act.size(), (long long) P.n_codes, P.ms_prep, P.ms_upload, P.ms_run, P.ms_emit, ms_wait);
@@ -237,6 +277,7 @@ static std::string pass_end(engine & E) {
             else { g.own.assign(src, src + n); g.p = g.own.data(); }
         }
         s.emitted_samples += n;
+        s.decode_calls++; s.decoded_codes += P.prefix[k];
         s.job_head++;
     }
     E.stream_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - P.t0).count();

@@ -26,6 +26,7 @@ struct stream_state {
     std::vector<stream_job> jobs;
     size_t job_head = 0;
     bool finished = false, final_queued = false, done = false;
+    bool failed = false;          // a device pass of this stream failed: its tail on the device is undefined, the stream is over
     float * d_tail = nullptr;
     int * d_tail_len = nullptr;
     // emitted samples not yet read: slices of the engine's pinned round blocks (blk != nullptr, p points into it) or, when
@@ -49,6 +50,7 @@ std::string streams_step(engine & E, stream_state ** streams, int n_streams);
 std::string streams_step_begin(engine & E, stream_state ** streams, int n_streams, bool * in_flight = nullptr);
 std::string streams_step_end(engine & E, stream_state ** streams, int n_streams);
 std::string streams_drain(engine & E);
+void streams_detach_all(engine & E);   // before the engine is destroyed: open streams keep their unread samples, lose the engine
 int64_t stream_read(stream_state & s, float * out, int64_t cap, int * is_last);
 
 }  // namespace mio

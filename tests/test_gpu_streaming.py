@@ -207,3 +207,46 @@ def test_split_rounds_give_the_same_stream(codec):
     u.close()
     for s in streams:
         s.close()
+
+
+def test_context_destroyed_before_its_streams(assets):
+    """mio_ctx_destroy with streams still open (Python: codec.close() before the Stream objects are closed or collected):
+    the streams are detached, keep the samples they had not been read yet as their own copies, and can be read, queried
+    and closed afterwards -- no use of freed engine state, no read from freed pinned memory.  Also with a split round still
+    in flight when the context goes."""
+    from miocodec_b200 import binding, synth
+    emb = synth.synth_voice(3)
+    codes = synth.synth_codes(120, 909)
+
+    def session(destroy_first, in_flight):
+        c = binding.MioCodec(assets[0], 0)
+        s, t = c.open_stream(emb), c.open_stream(emb)
+        for st in (s, t):
+            st.push(codes)
+            st.finish()
+        if in_flight:
+            assert c.step_streams_begin([s, t]) == 1       # the round is enqueued, not waited for
+        else:
+            c.step_streams([s, t])
+        if destroy_first:
+            c.close()                                       # drains the round, detaches s and t
+        a, last = s.read()
+        if in_flight and not destroy_first:
+            assert a.size == 0
+            c.step_streams_end([s, t])
+            a, last = s.read()
+        st_ = s.stats()
+        s.close(); t.close()                                # t still holds unread samples when it is closed
+        if not destroy_first:
+            c.close()
+        return a, st_
+
+    want, stats = session(False, False)
+    assert want.size == 120 * 1764 and stats["emitted_samples"] == want.size
+    got, st_ = session(True, False)
+    assert np.array_equal(got, want) and st_ == stats
+    # destroyed with the FIRST pass of the round in flight: that pass is drained and delivered (the commit of the cadence at
+    # 60 codes: samples of codes [0, 28)); the later passes never ran
+    got, st_ = session(True, True)
+    assert got.size == 28 * 1764 and np.array_equal(got, want[:got.size])
+    assert st_["decode_calls"] == 1 and st_["decoded_codes"] == 60 and st_["emitted_samples"] == got.size
