@@ -201,6 +201,8 @@ struct loader {
     // store 1 / 2 (F16 / BF16-stored matrix): one pass on operands of that type; the values are exactly representable
     bool pack(gemm_weight & W, const std::vector<float> & B, int N, int K, int taps, int npass, int store = 0) {
         if (store != 0) npass = 1;
+        // refused here, at load time, with a message -- not as a bare cudaErrorInvalidValue from gemm() in the middle of a decode
+        if (store == 2 && taps != 1) { err = "unsupported: a BF16-stored matrix cannot be a " + std::to_string(taps) + "-tap convolution kernel (F32 or F16 only)"; return false; }
         W.N = N; W.K = K; W.taps = taps; W.npass = npass; W.store = store;
         const size_t n = (size_t) N * K * taps;
         if (B.size() != n) { err = "internal: weight size mismatch"; return false; }
