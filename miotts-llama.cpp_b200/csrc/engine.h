@@ -58,6 +58,7 @@ struct engine {
     // chunked tensor-core accumulation (gemm3.cu): 0 = off, 1 = the fp32-class layers in front of the first conv1d
     // (default: the only place where the tensor core's truncating adder is audible, profiles/r2a_parity_attribution.md),
     // 2 = every fp32-class layer.  MIO_CHUNK_ACC=off|prenet|all, option "chunk_acc".
+    bool exp_skip_norms = false; int64_t exp_runs = 0; int exp_slot_align = 0;   // measurement-only switches (MIO_EXP_*), see engine.cu
     int chunk_mode = 1;
     int chunk_kb = 3;                // k-blocks (64 of K each) per accumulation chunk: 3 costs no step time and gives 6e-7 (profiles/r2c/r2c_chunk_sweep.log; 2: 3.8e-7 at +4.6 %, 4: 8.4e-7); MIO_CHUNK_KB
     bool fuse_resblock_tail = true;  // MIO_FUSE_TAIL=0 / option "fuse_tail": A/B switch of the residual + split epilogue (engine::run_resblock)

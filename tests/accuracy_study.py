@@ -125,6 +125,8 @@ VARIANTS = {
     "tc": {},
     "tc_unchunked": {"MIO_CHUNK_ACC": "off"},
     "tc_chunk_all": {"MIO_CHUNK_ACC": "all"},
+    "tc_kb4": {"MIO_CHUNK_KB": "4"},
+    "tc_kb6": {"MIO_CHUNK_KB": "6"},
     "simt": {"MIO_GEMM": "simt"},
     "attn_simt": {"MIO_ATTN": "simt"},
     "gn_precise": {"MIO_GN_PRECISE": "1"},

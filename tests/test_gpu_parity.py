@@ -295,8 +295,9 @@ def test_delivery_pipeline_splits_do_not_change_the_result(codec):
 
 def test_mean_parity_over_32_utterances(assets, codec):
     """the GPU path against the live reference on 32 utterances (40-120 codes, 16 voices), next to the
-    reference's own cross-build floor on the SAME utterances.  Bars: mean SNR within 0.6 dB of the mean floor, mean
-    max-abs within 1.25 x, no utterance more than 1 dB under its own floor."""
+    reference's own cross-build floor on the SAME utterances.  Bars: mean SNR within 0.5 dB of the mean floor (measured gap
+    0.42 dB with a standard error of 0.05, profiles/r3/summary.md section 3: a chunk length of 4 instead of 3 in the chunked
+    accumulation, gap 0.55, already fails), mean max-abs within 1.25 x, no utterance more than 1 dB under its own floor."""
     from conftest import reference_floor
     from miocodec_b200 import synth
     from oracle import ref
@@ -315,7 +316,7 @@ def test_mean_parity_over_32_utterances(assets, codec):
     g_snr, g_max, f_snr, f_max = map(np.array, (g_snr, g_max, f_snr, f_max))
     print(f"32 utterances: GPU {g_snr.mean():.2f} +- {g_snr.std():.2f} dB [min {g_snr.min():.2f}], max-abs {g_max.mean():.2e} [{g_max.max():.2e}]; "
           f"floor {f_snr.mean():.2f} +- {f_snr.std():.2f} dB [min {f_snr.min():.2f}], max-abs {f_max.mean():.2e} [{f_max.max():.2e}]")
-    assert g_snr.mean() > f_snr.mean() - 0.6
+    assert g_snr.mean() > f_snr.mean() - 0.5
     assert g_max.mean() < 1.25 * f_max.mean()
     assert (g_snr > np.minimum(f_snr, 60.0) - 1.0).all() and g_snr.min() > 58.5
 
