@@ -771,7 +771,7 @@ def main():
                          "bound": "tensor", "achieved": ach_tf, "peak": peaks["tf_sus"], "unit": "TFLOP/s",
                          "frac": ach_tf / peaks["tf_sus"], "traffic": traffic,
                          "executed_mma_frac": 3.0 * ach_tf / peaks["tf_sus"], "traffic_source": traffic_src,
-                         "note": f"algorithmic FLOPs 2*M*N*K*taps per launch (3 MMA passes executed per algorithmic FLOP; executed_mma_frac can "
+                         "note": f"algorithmic FLOPs 2*M*N*K*taps per launch over the LIVE rows (the pad rows of the 16-row utterance slots are computed but not counted; 3 MMA passes executed per algorithmic FLOP; executed_mma_frac can "
                                  f"pass 1.0 because the peak is cuBLAS's measured sustained bf16 rate, not a hardware bound); "
                                  f"peak = {peaks['src']} sustained dense bf16; avg launch {g['ms'] / max(1, g['launches']):.3f} ms "
                                  f"over {int(g['launches'])} launches (separate event-instrumented pass of {prof_steps} steps, {prof_ms / prof_steps:.1f} ms/step); "
@@ -794,6 +794,13 @@ def main():
                     line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref unavailable on this host"}
             except Exception as e:  # noqa: BLE001
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"failed: {e}"}
+        # the figures a reader of a truncated log needs, as the LAST key of the line (a 1 500-byte tail of the output keeps it)
+        c5, c2, c4 = line.get("c5") or {}, line.get("c2") or {}, line.get("c4") or {}
+        line["summary"] = {"n_gpus": world, "value": value, "ms_per_step": dev_ms_max / args.steps, "e2e": e2e_value,
+                           "e2e_pcm16": line["e2e_pcm16"]["value"], "roofline_frac": line["roofline"]["frac"],
+                           "c5": c5.get("value"),
+                           "c5_e2e": {k: v.get("value") for k, v in (c5.get("e2e") or {}).items() if isinstance(v, dict) and "value" in v},
+                           "c2_device_ms": c2.get("device_ms"), "c4": c4.get("value")}
         print(json.dumps(line))
     codec.close()
     if world > 1:

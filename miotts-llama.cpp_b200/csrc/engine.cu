@@ -901,7 +901,8 @@ cudaError_t engine::gemm(const gemm_weight & W, const a_view & A, int M, gemm_pa
         p.bf16 = 1;
     }
     launches++;
-    prof_begin(W.npass == 3 ? CAT_GEMM_SPLIT : CAT_GEMM_F16, 2.0 * M * (double) W.N * W.K * W.taps, 0.0);
+    // algorithmic FLOPs: M counts the slot rows (16-row alignment + the zero row behind every utterance); pad rows are not work
+    prof_begin(W.npass == 3 ? CAT_GEMM_SPLIT : CAT_GEMM_F16, 2.0 * M * cur_live_frac * (double) W.N * W.K * W.taps, 0.0);
     cudaError_t ce;
     if (use_simt) ce = launch_gemm_simt(p, stream);
     else {
@@ -946,6 +947,7 @@ std::string engine::debug_gemm(int M, int N, int K, const float * A, const float
     if (M <= 0 || N <= 0 || K <= 0 || K % 64 != 0 || !A || !B || !out || (npass != 1 && npass != 3)) return "bad argument";
     if (istft_only) return "bad argument: this context has no decoder";
     CK(cudaSetDevice(device));
+    cur_live_frac = 1.0;             // a bare product has no pad rows
     gguf_file none;
     loader L(*this, none);
     gemm_weight W;
@@ -1089,6 +1091,11 @@ std::string engine::run_attention(int rows, int D, int n_head, int window, int r
 
 std::string engine::run_chunk(const chunk_info & c) {
     cur_row0 = c.row0; cur_utt0 = c.utt0; cur_rows1 = c.rows1; cur_n_utts = c.n_utts; cur_scu0 = c.scu0; cur_n_segs = c.n_segs;
+    {
+        int64_t live = 0;
+        for (int u = 0; u < c.n_utts; u++) live += lay.len[c.utt0 + u];
+        cur_live_frac = c.rows1 > 0 ? (double) live / (double) c.rows1 : 1.0;
+    }
     const row_map rm = rmap();
     const int R1 = c.rows1, R2 = 2 * R1, rd0 = hp.up_res[0], rd1 = hp.up_res[1], Ru0 = rd0 * R1, Ru1 = rd1 * R1;
     const int c0 = hp.up_ch[0], c1 = hp.up_ch[1], P = hp.out_proj_dim, f0 = hp.up_factor[0], f1 = hp.up_factor[1];

@@ -93,6 +93,7 @@ struct engine {
     batch_layout lay;
     std::vector<chunk_info> chunks;
     int cur_row0 = 0, cur_utt0 = 0, cur_rows1 = 0, cur_n_utts = 0, cur_scu0 = 0, cur_n_segs = 0;
+    double cur_live_frac = 1.0;      // live codes / slot rows of the current chunk: the profile books FLOPs of live rows only
     size_t cap_rows = 0, cap_rows_ru = 0, cap_utts = 0, cap_ccu = 0, cap_scu = 0, cap_vt = 0;
     size_t h2d_bytes = 0;
     int32_t *d_codes = nullptr, *d_row_utt = nullptr, *d_start = nullptr, *d_len = nullptr, *d_voice = nullptr,
